@@ -1,0 +1,128 @@
+// oracle/ref_shim.cpp -- TEST INFRASTRUCTURE. C-ABI harness around the REFERENCE'S OWN sources,
+// compiled where they lie under /root/reference (never copied into this repo):
+//   src/custom/mi.cpp            (whole file, separate TU)          -> ref_mi
+//   src/custom/ops.h             (templates instantiated here)      -> ref_mean_std, ref_all_less_than
+//   src/custom/sd.h, sample_film.{h,cpp} (whole files)              -> SampleData / SamplingFilm
+//   src/custom/rpf.cpp:302-733   (FillMeanAndStddev, ComputeCFWeights, ApplyRPFFilter; the Makefile
+//                                 streams exactly those lines into a temp file, RPF_REF_EXTRACT)
+// pbrt core is replaced by oracle/ref_stubs (plumbing only). Two deviations from a stock pbrt run,
+// both outside the arithmetic: exit(1) at rpf.cpp:704 becomes a flag, and the
+// STAT/ReportValue bookkeeping is a no-op.
+#include "pbrt.h"
+
+#include "custom/mi.h"
+#include "custom/ops.h"
+#include "custom/sd.h"
+#include "custom/sample_film.h"
+
+namespace pbrt {
+int ref_stub_threads = 1;
+static std::atomic<int> ref_nan_exit_flag{0};
+double ref_sigma_fc_seed = 0.002;  // rpf.cpp:533 literal; only the REF_DEFINED build reads this variable
+#define REF_RATIO(num, den) ((den) == 0 ? 0 : (num) / (den))
+
+// Declaration mirror of rpf.h:28-96 restricted to what rpf.cpp:302-733 defines and uses.
+class RPFIntegrator {
+  public:
+    explicit RPFIntegrator(std::shared_ptr<const Camera> camera) : camera(camera) {}
+    std::shared_ptr<const Camera> camera;
+    void FillMeanAndStddev(const SamplingFilm &samplingFilm, SampleFMatrix &pixelFmeanMatrix,
+                           SampleFMatrix &pixelFstdDevMatrix, const int tileSize);
+    void ComputeCFWeights(const SampleDataSet &neighborhood, SampleC &Alpha_k, SampleF &Beta_k, double &W_r_c);
+    void ApplyRPFFilter(SamplingFilm &samplingFilm, const int tileSize, int box_size);
+};
+
+#define exit(code) (::pbrt::ref_nan_exit_flag.store(1))
+#ifdef RPF_REF_EXTRACT
+#include RPF_REF_EXTRACT
+#endif
+#undef exit
+}  // namespace pbrt
+
+using namespace pbrt;
+
+extern "C" {
+
+double ref_mi(const double *x, const double *y, int n) {
+    std::vector<double> a(x, x + n), b(y, y + n);
+    return MutualInformation(a, b);
+}
+
+// ops.h:111-144 on one channel
+void ref_mean_std(const double *v, int n, double *mean, double *sd) {
+    std::vector<std::array<double, 1>> vs(n);
+    for (int i = 0; i < n; ++i) vs[i][0] = v[i];
+    auto m = getMean(vs);
+    auto s = getStdDev(vs, m);
+    *mean = m[0];
+    *sd = s[0];
+}
+
+// rpf.cpp:575-580 acceptance test for one sample's 12 features against pixel mean / sigma
+int ref_within_3sigma(const double *f, const double *mean, const double *sd) {
+    SampleF a, m, s;
+    for (int i = 0; i < 12; ++i) { a[i] = f[i]; m[i] = mean[i]; s[i] = sd[i]; }
+    return allLessThan(absArray(subtractArrays(a, m)), multiplyArray(s, 3)) ? 1 : 0;
+}
+
+#ifdef RPF_REF_EXTRACT
+int ref_has_filter(void) { return 1; }
+
+// rpf.cpp:356-488 on a neighbourhood given as z[n][19]
+void ref_cf_weights(const double *z, int n, double *alpha, double *beta, double *wrc) {
+    SampleDataSet nb(n);
+    for (int i = 0; i < n; ++i)
+        for (int c = 0; c < 19; ++c) nb[i].data[c] = z[static_cast<size_t>(i) * 19 + c];
+    Film film;
+    auto cam = std::make_shared<Camera>();
+    cam->film = &film;
+    RPFIntegrator integ(cam);
+    SampleC A;
+    SampleF B;
+    double W;
+    integ.ComputeCFWeights(nb, A, B, W);
+    for (int i = 0; i < 3; ++i) alpha[i] = A[i];
+    for (int i = 0; i < 12; ++i) beta[i] = B[i];
+    *wrc = W;
+}
+
+// rpf.cpp:497-733 over a whole frame. planes [19][W*H*P] float, colours in/out [3][W*H*P] double.
+// Returns 1 if the reference would have called exit(1) on a NaN colour, else 0.
+int ref_apply_rpf_filter(int W, int H, int P, const float *planes, double *colors, int box_size, int n_threads,
+                         double sigma_fc_seed /* ignored by the verbatim build */) {
+    ref_stub_threads = n_threads > 0 ? n_threads : 1;
+    ref_nan_exit_flag.store(0);
+    ref_sigma_fc_seed = sigma_fc_seed;
+    Film film;
+    film.sampleBounds = Bounds2i(Point2i(0, 0), Point2i(W, H));
+    auto cam = std::make_shared<Camera>();
+    cam->film = &film;
+    RPFIntegrator integ(cam);
+    SamplingFilm sf(film.sampleBounds);
+    const size_t S = static_cast<size_t>(W) * H * P;
+    for (int y = 0; y < H; ++y)
+        for (int x = 0; x < W; ++x)
+            for (int s = 0; s < P; ++s) {
+                const size_t i = (static_cast<size_t>(y) * W + x) * P + s;
+                SampleData sd;
+                for (int c = 0; c < 19; ++c) sd.data[c] = planes[c * S + i];
+                for (int k = 0; k < 3; ++k) sd.data[2 + k] = colors[k * S + i];
+                sd.rayWeight = 1;
+                sf.AddSample(Point2i(x, y), sd);
+            }
+    std::cout.setstate(std::ios_base::failbit);  // the reference prints progress text to stdout
+    integ.ApplyRPFFilter(sf, 16, box_size);
+    std::cout.clear();
+    for (int y = 0; y < H; ++y)
+        for (int x = 0; x < W; ++x)
+            for (int s = 0; s < P; ++s) {
+                const size_t i = (static_cast<size_t>(y) * W + x) * P + s;
+                const SampleData &sd = sf.samples[x][y][s];
+                for (int k = 0; k < 3; ++k) colors[k * S + i] = sd.data[2 + k];
+            }
+    return ref_nan_exit_flag.load();
+}
+#else
+int ref_has_filter(void) { return 0; }
+#endif
+}

@@ -1,0 +1,142 @@
+"""ctypes bindings to the CPU oracle (oracle/liboracle_rpf.so) and, when present, to the reference's own
+sources compiled in place (oracle/_ref/libref_rpf.so). Test infrastructure only."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+P1, P2, P3, DEFINED = 1, 2, 4, 7
+NCH = 19
+
+
+class OracleArgs(C.Structure):
+    _fields_ = [
+        ("width", C.c_int), ("height", C.c_int), ("spp", C.c_int),
+        ("planes", C.c_void_p), ("colors", C.c_void_p), ("box_sizes", C.c_void_p),
+        ("n_iter", C.c_int), ("sigma_fc_seed", C.c_double), ("flags", C.c_int), ("n_threads", C.c_int),
+        ("y0", C.c_int), ("y1", C.c_int), ("x0", C.c_int), ("x1", C.c_int),
+        ("nbh_size", C.c_void_p), ("alpha", C.c_void_p), ("beta", C.c_void_p), ("wrc", C.c_void_p),
+        ("nan_count", C.c_longlong),
+    ]
+
+
+_oracle = None
+_ref = None
+
+
+def build_oracle():
+    subprocess.run(["make", "-s", "-C", ORACLE_DIR], check=True, stdout=subprocess.DEVNULL)
+
+
+def oracle():
+    global _oracle
+    if _oracle is None:
+        path = os.path.join(ORACLE_DIR, "liboracle_rpf.so")
+        if not os.path.exists(path):
+            build_oracle()
+        lib = C.CDLL(path)
+        lib.rpf_oracle_filter.argtypes = [C.POINTER(OracleArgs)]
+        lib.rpf_oracle_filter.restype = C.c_int
+        lib.rpf_oracle_mi.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+        lib.rpf_oracle_mi.restype = C.c_double
+        lib.rpf_oracle_mean_std.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        lib.rpf_oracle_cf_weights.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        _oracle = lib
+    return _oracle
+
+
+def ref():
+    """The reference's own code (None when oracle/_ref was not built, e.g. never on a box without it)."""
+    global _ref
+    if _ref is None:
+        path = os.path.join(ORACLE_DIR, "_ref", "libref_rpf.so")
+        if not os.path.exists(path):
+            return None
+        lib = C.CDLL(path)
+        lib.ref_mi.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+        lib.ref_mi.restype = C.c_double
+        lib.ref_mean_std.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        lib.ref_within_3sigma.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.ref_within_3sigma.restype = C.c_int
+        lib.ref_has_filter.restype = C.c_int
+        if lib.ref_has_filter():
+            lib.ref_cf_weights.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+            lib.ref_apply_rpf_filter.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+            lib.ref_apply_rpf_filter.restype = C.c_int
+        _ref = lib
+    return _ref
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def oracle_filter(planes, W, H, P, boxes, seed=0.002, flags=DEFINED, colors=None, threads=0,
+                  rows=None, cols=None, debug=False):
+    """planes: float32 [19, W*H*P]. Returns dict(colors=[3,S] float64, N, alpha, beta, wrc, nan_count)."""
+    planes = np.ascontiguousarray(planes, dtype=np.float32)
+    S = W * H * P
+    assert planes.shape == (NCH, S)
+    col = np.ascontiguousarray(planes[2:5].astype(np.float64) if colors is None else colors, dtype=np.float64).copy()
+    bx = np.asarray(boxes, dtype=np.int32)
+    a = OracleArgs()
+    a.width, a.height, a.spp = W, H, P
+    a.planes, a.colors, a.box_sizes = _p(planes), _p(col), _p(bx)
+    a.n_iter, a.sigma_fc_seed, a.flags, a.n_threads = len(bx), seed, flags, threads
+    a.y0, a.y1 = rows if rows else (0, 0)
+    a.x0, a.x1 = cols if cols else (0, 0)
+    out = {}
+    if debug:
+        out["N"] = np.zeros(W * H, np.int32)
+        out["alpha"] = np.zeros((W * H, 3))
+        out["beta"] = np.zeros((W * H, 12))
+        out["wrc"] = np.zeros(W * H)
+        a.nbh_size, a.alpha, a.beta, a.wrc = _p(out["N"]), _p(out["alpha"]), _p(out["beta"]), _p(out["wrc"])
+    rc = oracle().rpf_oracle_filter(C.byref(a))
+    assert rc == 0
+    out["colors"] = col
+    out["nan_count"] = a.nan_count
+    return out
+
+
+def oracle_mi(x, y):
+    x = np.ascontiguousarray(x, np.float64)
+    y = np.ascontiguousarray(y, np.float64)
+    return oracle().rpf_oracle_mi(_p(x), _p(y), len(x))
+
+
+def ref_mi(x, y):
+    x = np.ascontiguousarray(x, np.float64)
+    y = np.ascontiguousarray(y, np.float64)
+    return ref().ref_mi(_p(x), _p(y), len(x))
+
+
+def mean_std(lib_fn, v):
+    v = np.ascontiguousarray(v, np.float64)
+    m, s = C.c_double(), C.c_double()
+    lib_fn(_p(v), len(v), C.byref(m), C.byref(s))
+    return m.value, s.value
+
+
+def oracle_cf(z, flags=DEFINED):
+    z = np.ascontiguousarray(z, np.float64)
+    al, be, w = np.zeros(3), np.zeros(12), C.c_double()
+    oracle().rpf_oracle_cf_weights(_p(z), z.shape[0], flags, _p(al), _p(be), C.byref(w))
+    return al, be, w.value
+
+
+def ref_cf(z):
+    z = np.ascontiguousarray(z, np.float64)
+    al, be, w = np.zeros(3), np.zeros(12), C.c_double()
+    ref().ref_cf_weights(_p(z), z.shape[0], _p(al), _p(be), C.byref(w))
+    return al, be, w.value
+
+
+def ref_filter(planes, W, H, P, box, colors=None, threads=1):
+    planes = np.ascontiguousarray(planes, dtype=np.float32)
+    col = np.ascontiguousarray(planes[2:5].astype(np.float64) if colors is None else colors, dtype=np.float64).copy()
+    flag = ref().ref_apply_rpf_filter(W, H, P, _p(planes), _p(col), box, threads)
+    return col, flag
