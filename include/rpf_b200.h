@@ -1,0 +1,122 @@
+/* include/rpf_b200.h -- C ABI of the B200-native Random Parameter Filtering sample filter.
+ *
+ * This is the drop-in boundary for the one hot path of tux550/RayTracer-RPF:
+ *   void RPFIntegrator::ApplyRPFFilter(SamplingFilm&, const int tileSize, int box_size)
+ *       reference: src/custom/rpf.h:91-95, src/custom/rpf.cpp:497-733, called per box size from
+ *       RPFIntegrator::Render at src/custom/rpf.cpp:767-775.
+ * The replacement host integrator (raytracer-rpf_b200/host/rpf_integrator.cpp) packs the SamplingFilm
+ * into structure-of-arrays planes and calls the entry points below instead of ApplyRPFFilter.
+ *
+ * Conventions: plain pointers and sizes only; every call returns RPF_OK (0) or a negative rpf_status and
+ * leaves a message retrievable with rpf_last_error(). A context is bound to one CUDA device and is not
+ * re-entrant. There is no CPU fallback: without a usable sm_100 device rpf_create fails.
+ *
+ * Sample layout: channel c of sample s of pixel (x,y) lives at plane[c][(y*width + x)*spp + s].
+ * Channel order is SampleData::data (src/custom/sd.h:62-94):
+ *   0-1 pFilm.xy | 2-4 L.rgb | 5-6 pLens.xy | 7-9 n0 | 10-12 p0 | 13-15 n1 | 16-18 p1
+ */
+#ifndef RPF_B200_H
+#define RPF_B200_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RPF_NUM_CHANNELS 19
+
+typedef enum rpf_status {
+    RPF_OK = 0,
+    RPF_ERR_INVALID = -1,     /* bad argument */
+    RPF_ERR_CUDA = -2,        /* CUDA runtime error (message has the CUDA string) */
+    RPF_ERR_NO_DEVICE = -3,   /* no CUDA device / not an sm_100 part */
+    RPF_ERR_UNSUPPORTED = -4, /* neighbourhood too large for this build (see message) */
+    RPF_ERR_STATE = -5        /* call order (e.g. filter before upload) */
+} rpf_status;
+
+/* Behaviour switches relative to the verbatim reference ("REF_DEFINED" = all three):
+ * the reference reads out of bounds at rpf.cpp:464 and divides 0/0 at rpf.cpp:464-470. */
+#define RPF_FLAG_P1_BETA_AXIS 1   /* W_c_fk[j] uses D_c_f[j] = sum_i MI(c_i,f_j) (rpf.cpp:459 comment, :464 bug) */
+#define RPF_FLAG_P2_ZERO_GUARD 2  /* den==0 ? 0 : num/den in W_c_fk, W_r_fk, W_r_ck (rpf.cpp:464,465,470) */
+#define RPF_FLAG_P3_CLAMP_VAR 4   /* neighbourhood sigma = sqrt(max(0,var)) (ops.h:141) */
+#define RPF_FLAGS_DEFINED 7
+#define RPF_FLAGS_VERBATIM 0x100    /* none of P1-P3: beta[3..11] is NaN (the reference value is undefined there) */
+
+typedef struct rpf_ctx rpf_ctx;
+
+typedef struct rpf_config {
+    int width;   /* sampleBounds extent x (rpf.cpp:503-504) */
+    int height;  /* rows held by THIS context (a row band plus its halo rows when sharded) */
+    int spp;     /* samples per pixel, constant */
+    int device;  /* CUDA device ordinal */
+    int flags;   /* RPF_FLAG_* bits; 0 selects RPF_FLAGS_DEFINED, RPF_FLAGS_VERBATIM selects none */
+    int debug;   /* 1: keep per-pixel N, alpha, beta, W_r_c of the last iteration for rpf_download_debug */
+} rpf_config;
+
+typedef struct rpf_stats_t {
+    long long pixels_filtered;   /* pixel-iterations since create/reset */
+    long long nbh_sum;           /* sum of neighbourhood sizes N over those pixel-iterations ("RPF/Neighborhood Size", rpf.cpp:588) */
+    int nbh_min, nbh_max;
+    long long nan_channels;      /* NaN colour channels written (rpf.cpp:702-705 would exit(1); here: counted) */
+    long long kernel_launches;   /* device kernels launched by this context */
+    double last_filter_ms;       /* device time of the last rpf_filter / rpf_filter_rows call (CUDA events) */
+} rpf_stats_t;
+
+/* Replaces the SamplingFilm container (sample_film.h:28-45): allocate device planes for width*height*spp samples. */
+int rpf_create(rpf_ctx **out, const rpf_config *cfg);
+void rpf_destroy(rpf_ctx *ctx);
+const char *rpf_last_error(const rpf_ctx *ctx); /* ctx may be NULL: last error of a failed rpf_create */
+
+/* Replaces SamplingFilm::AddSample / MergeSamplingTile (sample_film.cpp:48-66): copy 19 host planes
+ * (each width*height*spp floats) to the device. planes[2..4] seed the working colours. */
+int rpf_upload(rpf_ctx *ctx, const float *const planes[RPF_NUM_CHANNELS]);
+/* Same, from device-resident planes (synthetic benchmarks, multi-GPU bands). */
+int rpf_upload_device(rpf_ctx *ctx, const float *const d_planes[RPF_NUM_CHANNELS]);
+/* Optional: overwrite the working colours with doubles (the reference keeps filtered colours in double
+ * between iterations, sd.h:205-207). rgb = [3][width*height*spp]. */
+int rpf_upload_colors_f64(rpf_ctx *ctx, const double *rgb);
+
+/* Replaces the loop at rpf.cpp:767-775: one ApplyRPFFilter pass per entry of box_sizes over the whole
+ * context, Jacobi style (rpf.cpp:527,732). sigma_fc_seed is the literal of rpf.cpp:533 (0.002). */
+int rpf_filter(rpf_ctx *ctx, const int *box_sizes, int n_iter, double sigma_fc_seed);
+
+/* One ApplyRPFFilter pass restricted to pixel rows [y0,y1) of this context (row-band sharding). Reads the
+ * current colours, writes the next colours for those rows; rpf_swap_colors makes them current. Rows outside
+ * [y0,y1) of the next buffer are whatever the caller puts there (halo exchange) or stale. */
+int rpf_filter_rows(rpf_ctx *ctx, int box_size, double sigma_fc_seed, int y0, int y1);
+int rpf_swap_colors(rpf_ctx *ctx);
+/* Device pointers to the colour planes, [3][width*height*spp] doubles: which = 0 current, 1 next.
+ * For halo exchange by the host (NCCL send/recv or peer copies between row bands). */
+int rpf_color_device_ptr(rpf_ctx *ctx, int which, double **out);
+/* The CUDA stream (cudaStream_t as void*) the context launches on, so callers can order their copies. */
+int rpf_stream(rpf_ctx *ctx, void **out);
+int rpf_synchronize(rpf_ctx *ctx);
+
+/* Replaces reading samplingFilm.samples back at rpf.cpp:780-786. Any pointer may be NULL. */
+int rpf_download_colors(rpf_ctx *ctx, float *r, float *g, float *b);
+int rpf_download_colors_f64(rpf_ctx *ctx, double *rgb); /* [3][width*height*spp] */
+/* Per-pixel (index y*width+x) diagnostics of the last pass; needs cfg.debug. Any pointer may be NULL.
+ * nbh = N (rpf.cpp:588), alpha [..][3] (rpf.cpp:475), beta [..][12] (rpf.cpp:479), wrc (rpf.cpp:483-487). */
+int rpf_download_debug(rpf_ctx *ctx, int *nbh, double *alpha, double *beta, double *wrc);
+
+/* Film reconstruction for pbrt's default box filter of radius 0.5 (filters/box.cpp:43-47, film.h:121-161):
+ * per-pixel mean of the current colours weighted by nothing but rayWeight==1; rgb = [height*width][3] floats. */
+int rpf_reconstruct_box(rpf_ctx *ctx, float *rgb);
+
+int rpf_get_stats(rpf_ctx *ctx, rpf_stats_t *out);
+int rpf_reset_stats(rpf_ctx *ctx);
+
+/* Largest neighbourhood (box*box*spp samples) this build can filter, for error messages and tests. */
+int rpf_max_neighbourhood(void);
+
+/* Deterministic synthetic feature buffer, host side, float32 values.
+ * kind 0: all-noisy; kind 1: degenerate (flat normals, black background, duplicated samples).
+ * (x_off,y_off) shift the generator so a row band of a larger frame can be generated on its own. */
+int rpf_synth_planes(int width, int height, int spp, unsigned long long seed, int kind, int x_off, int y_off,
+                     float *planes /* [19][width*height*spp] */);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,436 @@
+// rpf_api.cu -- the C ABI of include/rpf_b200.h on top of the sm_100a kernels.
+// Replaces the call site RPFIntegrator::Render -> ApplyRPFFilter (reference src/custom/rpf.cpp:767-775).
+#include "../../include/rpf_b200.h"
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "rpf_pixel_kernel.cuh"
+
+using namespace rpf;
+
+struct rpf_ctx {
+    rpf_config cfg{};
+    size_t S = 0;
+    int npix = 0;
+    float *d_planes = nullptr;      // [19][S]
+    double *d_col[2] = {nullptr, nullptr};  // [3][S] each: current / next
+    int cur = 0;
+    double *d_pstat = nullptr;      // [npix][24]
+    int pstat_y0 = 0, pstat_y1 = 0; // rows with valid per-pixel statistics
+    double *d_gtab = nullptr, *d_gpre = nullptr;
+    int gtab_n = 0;
+    unsigned long long *d_counters = nullptr;  // 4
+    int *d_dbg_n = nullptr;
+    double *d_dbg_alpha = nullptr, *d_dbg_beta = nullptr, *d_dbg_wrc = nullptr;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool uploaded = false;
+    bool timing_pending = false;
+    long long pixels_filtered = 0, launches = 0;
+    double last_ms = 0.0;
+    int max_dyn_smem = 0;
+    std::string err;
+};
+
+static thread_local std::string g_create_err;
+
+static int fail(rpf_ctx *ctx, int code, const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (ctx) ctx->err = buf; else g_create_err = buf;
+    return code;
+}
+
+#define CU(ctx, call)                                                                         \
+    do {                                                                                      \
+        cudaError_t e_ = (call);                                                              \
+        if (e_ != cudaSuccess)                                                                \
+            return fail(ctx, RPF_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e_));   \
+    } while (0)
+
+static int bins_for(int n) {
+    int b = static_cast<int>(std::sqrt(static_cast<double>(n)));
+    return b < 1 ? 1 : b;
+}
+static int align16(int v) { return (v + 15) & ~15; }
+
+// Shared-memory plan for one pixel CTA. Returns false if the neighbourhood cannot fit.
+static bool plan_smem(long long ncap, int spp, int limit, SmemLayout &L) {
+    if (ncap > 65535) return false;  // u16 histogram cells, u8 bins (nb <= 255)
+    L.ncap = static_cast<int>(ncap);
+    L.nstride = L.ncap | 1;
+    const int nb = bins_for(L.ncap);
+    L.wpl = (nb * nb + nb + 1) / 2;  // joint cells + nb slack cells (column marginals of the exact path)
+    int off = 0;
+    L.off_idx = off; off = align16(off + 4 * L.ncap);
+    L.off_bins = off; off = align16(off + 20 * L.ncap);
+    L.off_gtab = off; off = align16(off + 8 * (L.ncap + 1));
+    L.off_small = off;
+    L.off_big = off;
+    const long long raw = 1ll * L.nstride * (NC * 8 + 16 * 4);
+    const long long wgt = (20ll * L.ncap + 18ll * spp) * 8;
+    for (int mw = 4; mw >= 1; mw >>= 1) {
+        const long long hist = 1ll * mw * L.wpl * 128;
+        long long big = raw > wgt ? raw : wgt;
+        if (hist > big) big = hist;
+        if (off + big <= limit) {
+            L.mi_warps = mw;
+            L.total = static_cast<int>(off + big);
+            return true;
+        }
+    }
+    return false;
+}
+
+static const int kSmemLimit = 227 * 1024 - 6 * 1024;  // minus static PixelSmall and the per-CTA reserve
+
+extern "C" int rpf_max_neighbourhood(void) {
+    int best = 0;
+    SmemLayout L;
+    for (int n = 1; n <= 65535; n += 1)
+        if (plan_smem(n, 8, kSmemLimit, L)) best = n; else break;
+    return best;
+}
+
+extern "C" const char *rpf_last_error(const rpf_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
+
+extern "C" void rpf_destroy(rpf_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->cfg.device);
+    cudaFree(ctx->d_planes);
+    cudaFree(ctx->d_col[0]);
+    cudaFree(ctx->d_col[1]);
+    cudaFree(ctx->d_pstat);
+    cudaFree(ctx->d_gtab);
+    cudaFree(ctx->d_gpre);
+    cudaFree(ctx->d_counters);
+    cudaFree(ctx->d_dbg_n);
+    cudaFree(ctx->d_dbg_alpha);
+    cudaFree(ctx->d_dbg_beta);
+    cudaFree(ctx->d_dbg_wrc);
+    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+    if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+static int reset_counters(rpf_ctx *ctx) {
+    const unsigned long long init[4] = {0ull, 0ull, ~0ull, 0ull};
+    CU(ctx, cudaMemcpyAsync(ctx->d_counters, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->pixels_filtered = 0;
+    return RPF_OK;
+}
+
+// g[k] = (k+1)ln(k+1) - k ln k in extended precision, and its sequentially summed prefix.
+static int ensure_gtab(rpf_ctx *ctx, int n) {
+    if (n + 2 <= ctx->gtab_n) return RPF_OK;
+    const int m = n + 2;
+    std::vector<double> g(m), pre(m + 1);
+    for (int k = 0; k < m; ++k) {
+        const long double a = k + 1, b = k;
+        g[k] = static_cast<double>(a * logl(a) - (k ? b * logl(b) : 0.0L));
+    }
+    double acc = 0.0;
+    pre[0] = 0.0;
+    for (int k = 0; k < m; ++k) {
+        acc += g[k];
+        pre[k + 1] = acc;
+    }
+    cudaFree(ctx->d_gtab);
+    cudaFree(ctx->d_gpre);
+    ctx->d_gtab = ctx->d_gpre = nullptr;
+    CU(ctx, cudaMalloc(&ctx->d_gtab, m * sizeof(double)));
+    CU(ctx, cudaMalloc(&ctx->d_gpre, (m + 1) * sizeof(double)));
+    CU(ctx, cudaMemcpy(ctx->d_gtab, g.data(), m * sizeof(double), cudaMemcpyHostToDevice));
+    CU(ctx, cudaMemcpy(ctx->d_gpre, pre.data(), (m + 1) * sizeof(double), cudaMemcpyHostToDevice));
+    ctx->gtab_n = m;
+    return RPF_OK;
+}
+
+extern "C" int rpf_create(rpf_ctx **out, const rpf_config *cfg) {
+    if (!out || !cfg) return fail(nullptr, RPF_ERR_INVALID, "rpf_create: null argument");
+    *out = nullptr;
+    if (cfg->width <= 0 || cfg->height <= 0 || cfg->spp <= 0)
+        return fail(nullptr, RPF_ERR_INVALID, "rpf_create: width/height/spp must be positive");
+    if (1ull * cfg->width * cfg->height * cfg->spp >= (1ull << 32))
+        return fail(nullptr, RPF_ERR_INVALID, "rpf_create: more than 2^32 samples per context");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail(nullptr, RPF_ERR_NO_DEVICE, "rpf_create: no CUDA device (this library has no CPU fallback)");
+    if (cfg->device < 0 || cfg->device >= ndev) return fail(nullptr, RPF_ERR_INVALID, "rpf_create: bad device ordinal");
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, cfg->device) != cudaSuccess || prop.major != 10)
+        return fail(nullptr, RPF_ERR_NO_DEVICE, "rpf_create: device %d is not an sm_100 part (kernels are built for sm_100a only)",
+                    cfg->device);
+    rpf_ctx *ctx = new rpf_ctx;
+    ctx->cfg = *cfg;
+    if (ctx->cfg.flags == 0) ctx->cfg.flags = RPF_FLAGS_DEFINED;
+    ctx->S = 1ull * cfg->width * cfg->height * cfg->spp;
+    ctx->npix = cfg->width * cfg->height;
+    ctx->max_dyn_smem = kSmemLimit;
+#define CUC(call)                                                                                        \
+    do {                                                                                                 \
+        cudaError_t e_ = (call);                                                                         \
+        if (e_ != cudaSuccess) {                                                                         \
+            fail(nullptr, RPF_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e_));                 \
+            rpf_destroy(ctx);                                                                            \
+            return RPF_ERR_CUDA;                                                                         \
+        }                                                                                                \
+    } while (0)
+    CUC(cudaSetDevice(cfg->device));
+    CUC(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    CUC(cudaEventCreate(&ctx->ev0));
+    CUC(cudaEventCreate(&ctx->ev1));
+    CUC(cudaMalloc(&ctx->d_planes, NCH * ctx->S * sizeof(float)));
+    CUC(cudaMalloc(&ctx->d_col[0], 3 * ctx->S * sizeof(double)));
+    CUC(cudaMalloc(&ctx->d_col[1], 3 * ctx->S * sizeof(double)));
+    CUC(cudaMalloc(&ctx->d_pstat, 24ull * ctx->npix * sizeof(double)));
+    CUC(cudaMalloc(&ctx->d_counters, 4 * sizeof(unsigned long long)));
+    if (cfg->debug) {
+        CUC(cudaMalloc(&ctx->d_dbg_n, ctx->npix * sizeof(int)));
+        CUC(cudaMalloc(&ctx->d_dbg_alpha, 3ull * ctx->npix * sizeof(double)));
+        CUC(cudaMalloc(&ctx->d_dbg_beta, 12ull * ctx->npix * sizeof(double)));
+        CUC(cudaMalloc(&ctx->d_dbg_wrc, 1ull * ctx->npix * sizeof(double)));
+        CUC(cudaMemset(ctx->d_dbg_n, 0, ctx->npix * sizeof(int)));
+    }
+    CUC(cudaFuncSetAttribute(rpf_pixel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
+#undef CUC
+    int rc = reset_counters(ctx);
+    if (rc != RPF_OK) {
+        g_create_err = ctx->err;
+        rpf_destroy(ctx);
+        return rc;
+    }
+    *out = ctx;
+    return RPF_OK;
+}
+
+static int after_upload(rpf_ctx *ctx) {
+    const size_t n = 3 * ctx->S;
+    colors_to_f64_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_planes, ctx->S,
+                                                                                          ctx->d_col[ctx->cur]);
+    ctx->launches++;
+    CU(ctx, cudaGetLastError());
+    ctx->pstat_y0 = ctx->pstat_y1 = 0;
+    ctx->uploaded = true;
+    return RPF_OK;
+}
+
+extern "C" int rpf_upload(rpf_ctx *ctx, const float *const planes[RPF_NUM_CHANNELS]) {
+    if (!ctx || !planes) return fail(ctx, RPF_ERR_INVALID, "rpf_upload: null argument");
+    CU(ctx, cudaSetDevice(ctx->cfg.device));
+    for (int c = 0; c < NCH; ++c) {
+        if (!planes[c]) return fail(ctx, RPF_ERR_INVALID, "rpf_upload: plane %d is null", c);
+        CU(ctx, cudaMemcpyAsync(ctx->d_planes + c * ctx->S, planes[c], ctx->S * sizeof(float), cudaMemcpyHostToDevice,
+                                ctx->stream));
+    }
+    return after_upload(ctx);
+}
+
+extern "C" int rpf_upload_device(rpf_ctx *ctx, const float *const d_planes[RPF_NUM_CHANNELS]) {
+    if (!ctx || !d_planes) return fail(ctx, RPF_ERR_INVALID, "rpf_upload_device: null argument");
+    CU(ctx, cudaSetDevice(ctx->cfg.device));
+    for (int c = 0; c < NCH; ++c) {
+        if (!d_planes[c]) return fail(ctx, RPF_ERR_INVALID, "rpf_upload_device: plane %d is null", c);
+        CU(ctx, cudaMemcpyAsync(ctx->d_planes + c * ctx->S, d_planes[c], ctx->S * sizeof(float),
+                                cudaMemcpyDeviceToDevice, ctx->stream));
+    }
+    return after_upload(ctx);
+}
+
+extern "C" int rpf_upload_colors_f64(rpf_ctx *ctx, const double *rgb) {
+    if (!ctx || !rgb) return fail(ctx, RPF_ERR_INVALID, "rpf_upload_colors_f64: null argument");
+    if (!ctx->uploaded) return fail(ctx, RPF_ERR_STATE, "rpf_upload_colors_f64: call rpf_upload first");
+    CU(ctx, cudaSetDevice(ctx->cfg.device));
+    CU(ctx, cudaMemcpyAsync(ctx->d_col[ctx->cur], rgb, 3 * ctx->S * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    return RPF_OK;
+}
+
+static int launch_rows(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
+    if (!ctx->uploaded) return fail(ctx, RPF_ERR_STATE, "rpf_filter: no samples uploaded");
+    if (box < 1 || (box & 1) == 0) return fail(ctx, RPF_ERR_INVALID, "box size %d must be odd and positive (rpf.cpp:561)", box);
+    if (y0 < 0 || y1 > ctx->cfg.height || y0 >= y1) return fail(ctx, RPF_ERR_INVALID, "bad row range [%d,%d)", y0, y1);
+    if (!(seed > 0.0)) return fail(ctx, RPF_ERR_INVALID, "sigma_fc_seed must be positive");
+    FilterParams p{};
+    if (!plan_smem(1ll * box * box * ctx->cfg.spp, ctx->cfg.spp, ctx->max_dyn_smem, p.sm))
+        return fail(ctx, RPF_ERR_UNSUPPORTED,
+                    "neighbourhood of box %d x %d spp = %lld samples exceeds the shared-memory resident kernel (max %d)", box,
+                    ctx->cfg.spp, 1ll * box * box * ctx->cfg.spp, rpf_max_neighbourhood());
+    int rc = ensure_gtab(ctx, p.sm.ncap);
+    if (rc != RPF_OK) return rc;
+    p.f = FrameView{ctx->d_planes, ctx->S, ctx->cfg.width, ctx->cfg.height, ctx->cfg.spp};
+    if (!(ctx->pstat_y0 <= y0 && y1 <= ctx->pstat_y1)) {
+        // features never change between iterations (rpf.cpp:715 writes colours only): computed once per upload
+        const long long n = 1ll * (y1 - y0) * ctx->cfg.width * NF;
+        pixel_stats_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, ctx->stream>>>(p.f, y0, y1, ctx->d_pstat);
+        ctx->launches++;
+        CU(ctx, cudaGetLastError());
+        if (ctx->pstat_y1 <= ctx->pstat_y0) { ctx->pstat_y0 = y0; ctx->pstat_y1 = y1; }
+        else { ctx->pstat_y0 = y0 < ctx->pstat_y0 ? y0 : ctx->pstat_y0; ctx->pstat_y1 = y1 > ctx->pstat_y1 ? y1 : ctx->pstat_y1; }
+    }
+    p.col_in = ctx->d_col[ctx->cur];
+    p.col_out = ctx->d_col[ctx->cur ^ 1];
+    p.pstat = ctx->d_pstat;
+    p.gtab = ctx->d_gtab;
+    p.gpre = ctx->d_gpre;
+    p.box = box;
+    p.y0 = y0;
+    p.y1 = y1;
+    p.flags = ctx->cfg.flags;
+    p.seed = seed;
+    p.dbg_n = ctx->d_dbg_n;
+    p.dbg_alpha = ctx->d_dbg_alpha;
+    p.dbg_beta = ctx->d_dbg_beta;
+    p.dbg_wrc = ctx->d_dbg_wrc;
+    p.counters = ctx->d_counters;
+    const unsigned grid = static_cast<unsigned>((y1 - y0) * ctx->cfg.width);
+    rpf_pixel_kernel<<<grid, THREADS, p.sm.total, ctx->stream>>>(p);
+    ctx->launches++;
+    CU(ctx, cudaGetLastError());
+    ctx->pixels_filtered += grid;
+    return RPF_OK;
+}
+
+static int finish_timing(rpf_ctx *ctx) {
+    if (ctx->timing_pending) {
+        CU(ctx, cudaEventSynchronize(ctx->ev1));
+        float ms = 0.f;
+        CU(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+        ctx->last_ms = ms;
+        ctx->timing_pending = false;
+    }
+    return RPF_OK;
+}
+
+extern "C" int rpf_filter_rows(rpf_ctx *ctx, int box_size, double sigma_fc_seed, int y0, int y1) {
+    if (!ctx) return RPF_ERR_INVALID;
+    CU(ctx, cudaSetDevice(ctx->cfg.device));
+    int rc = finish_timing(ctx);
+    if (rc != RPF_OK) return rc;
+    CU(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    rc = launch_rows(ctx, box_size, sigma_fc_seed, y0, y1);
+    if (rc != RPF_OK) return rc;
+    CU(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    ctx->timing_pending = true;
+    return RPF_OK;
+}
+
+extern "C" int rpf_swap_colors(rpf_ctx *ctx) {
+    if (!ctx) return RPF_ERR_INVALID;
+    ctx->cur ^= 1;
+    return RPF_OK;
+}
+
+extern "C" int rpf_filter(rpf_ctx *ctx, const int *box_sizes, int n_iter, double sigma_fc_seed) {
+    if (!ctx || (n_iter > 0 && !box_sizes) || n_iter < 0) return fail(ctx, RPF_ERR_INVALID, "rpf_filter: bad arguments");
+    CU(ctx, cudaSetDevice(ctx->cfg.device));
+    int rc = finish_timing(ctx);
+    if (rc != RPF_OK) return rc;
+    CU(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    for (int i = 0; i < n_iter; ++i) {
+        rc = launch_rows(ctx, box_sizes[i], sigma_fc_seed, 0, ctx->cfg.height);
+        if (rc != RPF_OK) return rc;
+        ctx->cur ^= 1;  // rpf.cpp:732
+    }
+    CU(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    ctx->timing_pending = true;
+    return RPF_OK;
+}
+
+extern "C" int rpf_color_device_ptr(rpf_ctx *ctx, int which, double **out) {
+    if (!ctx || !out || which < 0 || which > 1) return fail(ctx, RPF_ERR_INVALID, "rpf_color_device_ptr: bad arguments");
+    *out = ctx->d_col[ctx->cur ^ which];
+    return RPF_OK;
+}
+
+extern "C" int rpf_stream(rpf_ctx *ctx, void **out) {
+    if (!ctx || !out) return RPF_ERR_INVALID;
+    *out = ctx->stream;
+    return RPF_OK;
+}
+
+extern "C" int rpf_synchronize(rpf_ctx *ctx) {
+    if (!ctx) return RPF_ERR_INVALID;
+    CU(ctx, cudaSetDevice(ctx->cfg.device));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    return finish_timing(ctx);
+}
+
+extern "C" int rpf_download_colors_f64(rpf_ctx *ctx, double *rgb) {
+    if (!ctx || !rgb) return fail(ctx, RPF_ERR_INVALID, "rpf_download_colors_f64: null argument");
+    CU(ctx, cudaSetDevice(ctx->cfg.device));
+    CU(ctx, cudaMemcpyAsync(rgb, ctx->d_col[ctx->cur], 3 * ctx->S * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    return rpf_synchronize(ctx);
+}
+
+extern "C" int rpf_download_colors(rpf_ctx *ctx, float *r, float *g, float *b) {
+    if (!ctx) return RPF_ERR_INVALID;
+    CU(ctx, cudaSetDevice(ctx->cfg.device));
+    // the "next" colour buffer is dead between passes: use its first 3*S floats as conversion scratch
+    float *tmp = reinterpret_cast<float *>(ctx->d_col[ctx->cur ^ 1]);
+    const size_t n = 3 * ctx->S;
+    colors_to_f32_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_col[ctx->cur], n, tmp);
+    ctx->launches++;
+    CU(ctx, cudaGetLastError());
+    float *dst[3] = {r, g, b};
+    for (int k = 0; k < 3; ++k)
+        if (dst[k])
+            CU(ctx, cudaMemcpyAsync(dst[k], tmp + k * ctx->S, ctx->S * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    return rpf_synchronize(ctx);
+}
+
+extern "C" int rpf_download_debug(rpf_ctx *ctx, int *nbh, double *alpha, double *beta, double *wrc) {
+    if (!ctx) return RPF_ERR_INVALID;
+    if (!ctx->d_dbg_n) return fail(ctx, RPF_ERR_STATE, "rpf_download_debug: context created without cfg.debug");
+    CU(ctx, cudaSetDevice(ctx->cfg.device));
+    const size_t n = ctx->npix;
+    if (nbh) CU(ctx, cudaMemcpyAsync(nbh, ctx->d_dbg_n, n * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    if (alpha) CU(ctx, cudaMemcpyAsync(alpha, ctx->d_dbg_alpha, 3 * n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    if (beta) CU(ctx, cudaMemcpyAsync(beta, ctx->d_dbg_beta, 12 * n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    if (wrc) CU(ctx, cudaMemcpyAsync(wrc, ctx->d_dbg_wrc, n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    return rpf_synchronize(ctx);
+}
+
+extern "C" int rpf_reconstruct_box(rpf_ctx *ctx, float *rgb) {
+    if (!ctx || !rgb) return fail(ctx, RPF_ERR_INVALID, "rpf_reconstruct_box: null argument");
+    CU(ctx, cudaSetDevice(ctx->cfg.device));
+    float *tmp = reinterpret_cast<float *>(ctx->d_col[ctx->cur ^ 1]);
+    const int n = ctx->npix * 3;
+    reconstruct_box_kernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(ctx->d_col[ctx->cur], ctx->S, ctx->npix, ctx->cfg.spp, tmp);
+    ctx->launches++;
+    CU(ctx, cudaGetLastError());
+    CU(ctx, cudaMemcpyAsync(rgb, tmp, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    return rpf_synchronize(ctx);
+}
+
+extern "C" int rpf_get_stats(rpf_ctx *ctx, rpf_stats_t *out) {
+    if (!ctx || !out) return RPF_ERR_INVALID;
+    int rc = rpf_synchronize(ctx);
+    if (rc != RPF_OK) return rc;
+    unsigned long long c[4];
+    CU(ctx, cudaMemcpy(c, ctx->d_counters, sizeof c, cudaMemcpyDeviceToHost));
+    out->pixels_filtered = ctx->pixels_filtered;
+    out->nbh_sum = static_cast<long long>(c[0]);
+    out->nan_channels = static_cast<long long>(c[1]);
+    out->nbh_min = ctx->pixels_filtered ? static_cast<int>(c[2]) : 0;
+    out->nbh_max = static_cast<int>(c[3]);
+    out->kernel_launches = ctx->launches;
+    out->last_filter_ms = ctx->last_ms;
+    return RPF_OK;
+}
+
+extern "C" int rpf_reset_stats(rpf_ctx *ctx) {
+    if (!ctx) return RPF_ERR_INVALID;
+    CU(ctx, cudaSetDevice(ctx->cfg.device));
+    ctx->launches = 0;
+    return reset_counters(ctx);
+}

@@ -1,0 +1,189 @@
+"""ctypes binding of include/rpf_b200.h (lib/librpf_b200.so) for tests and bench.py.
+
+The product is the C ABI; this file only marshals numpy arrays / device pointers into it. There is no
+fallback of any kind: if the CUDA library is missing or no sm_100 device is present, calls raise RPFError.
+Names mirror the reference's seam: RPFFilter.apply() is the loop `for box_size in box_sizes: ApplyRPFFilter(...)`
+of reference src/custom/rpf.cpp:767-775.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "lib", "librpf_b200.so")
+NCH = 19
+FLAGS_DEFINED = 7
+FLAGS_VERBATIM = 0x100
+
+# every symbol include/rpf_b200.h declares
+ABI_SYMBOLS = [
+    "rpf_create", "rpf_destroy", "rpf_last_error", "rpf_upload", "rpf_upload_device", "rpf_upload_colors_f64",
+    "rpf_filter", "rpf_filter_rows", "rpf_swap_colors", "rpf_color_device_ptr", "rpf_stream", "rpf_synchronize",
+    "rpf_download_colors", "rpf_download_colors_f64", "rpf_download_debug", "rpf_reconstruct_box",
+    "rpf_get_stats", "rpf_reset_stats", "rpf_max_neighbourhood", "rpf_synth_planes",
+]
+
+
+class RPFError(RuntimeError):
+    pass
+
+
+class Config(C.Structure):
+    _fields_ = [("width", C.c_int), ("height", C.c_int), ("spp", C.c_int), ("device", C.c_int),
+                ("flags", C.c_int), ("debug", C.c_int)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("pixels_filtered", C.c_longlong), ("nbh_sum", C.c_longlong), ("nbh_min", C.c_int),
+                ("nbh_max", C.c_int), ("nan_channels", C.c_longlong), ("kernel_launches", C.c_longlong),
+                ("last_filter_ms", C.c_double)]
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RPFError(f"{LIB_PATH} is not built (run `python -c 'import __graft_entry__ as g; g.build()'`); "
+                           "there is no CPU fallback")
+        L = C.CDLL(LIB_PATH)
+        vp, i, d = C.c_void_p, C.c_int, C.c_double
+        L.rpf_create.argtypes = [C.POINTER(vp), C.POINTER(Config)]
+        L.rpf_destroy.argtypes = [vp]
+        L.rpf_destroy.restype = None
+        L.rpf_last_error.argtypes = [vp]
+        L.rpf_last_error.restype = C.c_char_p
+        L.rpf_upload.argtypes = [vp, C.POINTER(vp)]
+        L.rpf_upload_device.argtypes = [vp, C.POINTER(vp)]
+        L.rpf_upload_colors_f64.argtypes = [vp, vp]
+        L.rpf_filter.argtypes = [vp, vp, i, d]
+        L.rpf_filter_rows.argtypes = [vp, i, d, i, i]
+        L.rpf_swap_colors.argtypes = [vp]
+        L.rpf_color_device_ptr.argtypes = [vp, i, C.POINTER(vp)]
+        L.rpf_stream.argtypes = [vp, C.POINTER(vp)]
+        L.rpf_synchronize.argtypes = [vp]
+        L.rpf_download_colors.argtypes = [vp, vp, vp, vp]
+        L.rpf_download_colors_f64.argtypes = [vp, vp]
+        L.rpf_download_debug.argtypes = [vp, vp, vp, vp, vp]
+        L.rpf_reconstruct_box.argtypes = [vp, vp]
+        L.rpf_get_stats.argtypes = [vp, C.POINTER(Stats)]
+        L.rpf_reset_stats.argtypes = [vp]
+        L.rpf_max_neighbourhood.argtypes = []
+        L.rpf_synth_planes.argtypes = [i, i, i, C.c_ulonglong, i, i, i, vp]
+        _lib = L
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def synth_planes(width, height, spp, seed=1234, kind=0, x_off=0, y_off=0, out=None):
+    """Synthetic feature buffer of SURVEY.md 8(d): float32 [19, W*H*spp] (host side, deterministic)."""
+    planes = out if out is not None else np.empty((NCH, width * height * spp), np.float32)
+    assert planes.dtype == np.float32 and planes.flags.c_contiguous and planes.size == NCH * width * height * spp
+    rc = lib().rpf_synth_planes(width, height, spp, seed, kind, x_off, y_off, _p(planes))
+    if rc != 0:
+        raise RPFError(f"rpf_synth_planes failed ({rc})")
+    return planes
+
+
+class RPFFilter:
+    """One device context = one SamplingFilm (reference src/custom/sample_film.h:28-45) resident in HBM."""
+
+    def __init__(self, width, height, spp, device=0, flags=FLAGS_DEFINED, debug=False):
+        self.W, self.H, self.P = width, height, spp
+        self.S = width * height * spp
+        self._h = C.c_void_p()
+        cfg = Config(width, height, spp, device, flags, 1 if debug else 0)
+        rc = lib().rpf_create(C.byref(self._h), C.byref(cfg))
+        if rc != 0:
+            raise RPFError(f"rpf_create failed ({rc}): {lib().rpf_last_error(None).decode()}")
+
+    def _check(self, rc):
+        if rc != 0:
+            raise RPFError(f"rpf call failed ({rc}): {lib().rpf_last_error(self._h).decode()}")
+
+    def close(self):
+        if self._h:
+            lib().rpf_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- data movement --------------------------------------------------------------------------
+    def upload(self, planes):
+        """planes: float32 [19, S] host array (pinned or pageable)."""
+        assert planes.dtype == np.float32 and planes.shape == (NCH, self.S) and planes.flags.c_contiguous
+        ptrs = (C.c_void_p * NCH)(*[planes[c].ctypes.data for c in range(NCH)])
+        self._check(lib().rpf_upload(self._h, ptrs))
+
+    def upload_device(self, dev_ptr):
+        """dev_ptr: integer device address of a contiguous float32 [19, S] buffer."""
+        ptrs = (C.c_void_p * NCH)(*[dev_ptr + 4 * self.S * c for c in range(NCH)])
+        self._check(lib().rpf_upload_device(self._h, ptrs))
+
+    def upload_colors_f64(self, rgb):
+        rgb = np.ascontiguousarray(rgb, np.float64)
+        assert rgb.shape == (3, self.S)
+        self._check(lib().rpf_upload_colors_f64(self._h, _p(rgb)))
+
+    def download_colors(self, out=None):
+        out = out if out is not None else np.empty((3, self.S), np.float32)
+        self._check(lib().rpf_download_colors(self._h, _p(out[0]), _p(out[1]), _p(out[2])))
+        return out
+
+    def download_colors_f64(self):
+        out = np.empty((3, self.S), np.float64)
+        self._check(lib().rpf_download_colors_f64(self._h, _p(out)))
+        return out
+
+    def download_debug(self):
+        n = self.W * self.H
+        N, al, be, w = np.zeros(n, np.int32), np.zeros((n, 3)), np.zeros((n, 12)), np.zeros(n)
+        self._check(lib().rpf_download_debug(self._h, _p(N), _p(al), _p(be), _p(w)))
+        return dict(N=N, alpha=al, beta=be, wrc=w)
+
+    def reconstruct_box(self):
+        out = np.empty((self.H, self.W, 3), np.float32)
+        self._check(lib().rpf_reconstruct_box(self._h, _p(out)))
+        return out
+
+    # -- the filter --------------------------------------------------------------------------------
+    def apply(self, box_sizes=(7,), sigma_fc_seed=0.002):
+        bx = np.asarray(box_sizes, np.int32)
+        self._check(lib().rpf_filter(self._h, _p(bx), len(bx), sigma_fc_seed))
+
+    def filter_rows(self, box, y0, y1, sigma_fc_seed=0.002):
+        self._check(lib().rpf_filter_rows(self._h, box, sigma_fc_seed, y0, y1))
+
+    def swap_colors(self):
+        self._check(lib().rpf_swap_colors(self._h))
+
+    def color_ptr(self, which=0):
+        p = C.c_void_p()
+        self._check(lib().rpf_color_device_ptr(self._h, which, C.byref(p)))
+        return p.value
+
+    def stream(self):
+        p = C.c_void_p()
+        self._check(lib().rpf_stream(self._h, C.byref(p)))
+        return p.value or 0
+
+    def synchronize(self):
+        self._check(lib().rpf_synchronize(self._h))
+
+    def stats(self):
+        s = Stats()
+        self._check(lib().rpf_get_stats(self._h, C.byref(s)))
+        return {k: getattr(s, k) for k, _ in Stats._fields_}
+
+    def reset_stats(self):
+        self._check(lib().rpf_reset_stats(self._h))
