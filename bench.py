@@ -1,0 +1,272 @@
+#!/usr/bin/env python
+"""bench.py -- RPF filter throughput on B200 (metric of BASELINE.json: Msamples/s, % of HBM roofline).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+  N>1: python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A step is one rpf_filter pass schedule (all configured box sizes) over one synthetic frame. Row bands are sharded
+across ranks with halo exchange of the filtered colours between passes (NCCL point-to-point); total work is fixed
+as N grows ("strong" scaling of one frame). Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "raytracer-rpf_b200"))
+
+METRIC = "rpf_filter_msamples_per_s"
+UNIT = "Msamples/s"
+ALG_BYTES_PER_SAMPLE_ITER = 88  # 19 fp32 channels read + 3 fp32 colours written
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--width", type=int, default=1280)
+    ap.add_argument("--height", type=int, default=720)
+    ap.add_argument("--spp", type=int, default=8)
+    ap.add_argument("--boxes", default=os.environ.get("RPF_BENCH_BOXES", "7"))
+    ap.add_argument("--seed", type=float, default=0.002, help="sigma_fc_seed, reference literal rpf.cpp:533")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """Samples nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([c.strip() for c in out.strip().split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def crop_for_cpu(boxes, cores, W, H, target_s=15.0):
+    cost_px = 1.2e-3 * sum(b * b for b in boxes) / 49.0  # core-seconds per pixel (SURVEY.md section 6 probe)
+    side = int((target_s * cores / cost_px) ** 0.5) // 16 * 16
+    side = max(48, min(256, side))
+    return min(side, W), min(side, H)
+
+
+def cpu_reference_run(args, boxes, steps, warmup):
+    """Times the reference's own filter code (oracle/_ref REF_DEFINED build of rpf.cpp:497-733 + mi.cpp), or the oracle
+    port when that library is absent, on a bounded crop of the workload with all host cores."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import ctypes as C
+    import oracle_bind as ob
+    import rpf_b200
+    cores = os.cpu_count() or 1
+    cw, ch = crop_for_cpu(boxes, cores, args.width, args.height)
+    planes = rpf_b200.synth_planes(cw, ch, args.spp, seed=1234, kind=0, x_off=(args.width - cw) // 2,
+                                   y_off=(args.height - ch) // 2)
+    S = cw * ch * args.spp
+    path = os.path.join(ROOT, "oracle", "_ref", "libref_rpf_defined.so")
+    kind = "reference" if os.path.exists(path) else "port"
+    if kind == "reference":
+        lib = C.CDLL(path)
+        lib.ref_apply_rpf_filter.argtypes = [C.c_int] * 3 + [C.c_void_p] * 2 + [C.c_int] * 2 + [C.c_double]
+
+        def run():
+            col = planes[2:5].astype(np.float64)
+            for b in boxes:
+                lib.ref_apply_rpf_filter(cw, ch, args.spp, planes.ctypes.data, col.ctypes.data, b, cores, args.seed)
+    else:
+        ob.build_oracle()
+
+        def run():
+            ob.oracle_filter(planes, cw, ch, args.spp, boxes, seed=args.seed, threads=cores)
+    for _ in range(warmup):
+        run()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        run()
+    dt = (time.perf_counter() - t0) / steps
+    return {"value": S / dt / 1e6, "unit": UNIT, "cores": cores, "kind": kind,
+            "sample": f"{cw}x{ch} px centre crop of the {args.width}x{args.height}x{args.spp}spp frame, boxes {boxes}, "
+                      f"{dt:.2f} s per pass schedule"}, dt
+
+
+def main():
+    args = parse()
+    boxes = [int(b) for b in args.boxes.split(",")]
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    workload = f"synthetic all-noisy feature buffer {args.width}x{args.height} {args.spp} spp, boxes {boxes}, sigma seed {args.seed}"
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        base, dt = cpu_reference_run(args, boxes, max(1, args.steps), min(args.warmup, 1))
+        print(json.dumps({
+            "impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload}, "cpu_baseline": base,
+            "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
+
+    import torch
+    import bands
+    import rpf_b200
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    torch.cuda.set_device(local_rank)
+    W, H, P = args.width, args.height, args.spp
+    band = bands.make_band(rank, world, H, boxes)
+    lh = band.local_height
+    S_loc = W * lh * P
+    row = W * P
+    host = torch.empty((19, S_loc), dtype=torch.float32, pin_memory=True)
+    planes = host.numpy()
+    rpf_b200.synth_planes(W, lh, P, seed=1234, kind=0, x_off=0, y_off=band.buf0, out=planes)
+    out_host = torch.empty((3, S_loc), dtype=torch.float32, pin_memory=True)
+    ctx = rpf_b200.RPFFilter(W, lh, P, device=local_rank)
+    ctx.upload(planes)
+    ctx.synchronize()
+    o0, o1 = band.local_own
+
+    class DevView:  # zero-copy torch view of the context's colour planes for the halo exchange
+        def __init__(self, ptr):
+            self.__cuda_array_interface__ = {"shape": (3, S_loc), "typestr": "<f8", "data": (ptr, False), "version": 2}
+
+    kernel_ms = []
+
+    def step(record=False):
+        for i, b in enumerate(boxes):
+            ctx.filter_rows(b, o0, o1, args.seed)
+            if world > 1 and i + 1 < len(boxes):
+                ctx.synchronize()
+                nxt = torch.as_tensor(DevView(ctx.color_ptr(1)), device=f"cuda:{local_rank}")
+                bands.exchange_halos(dist, band, boxes[i + 1], nxt, row)
+                torch.cuda.synchronize()
+            elif record:
+                ctx.synchronize()
+            if record:
+                kernel_ms.append(ctx.stats()["last_filter_ms"])
+            ctx.swap_colors()
+
+    def barrier():
+        ctx.synchronize()
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    ctx.reset_stats()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    stream = torch.cuda.ExternalStream(ctx.stream(), device=local_rank)
+    t0 = time.perf_counter()
+    ev0.record(stream)
+    for _ in range(args.steps):
+        step(record=True)
+    ev1.record(stream)
+    barrier()
+    wall = time.perf_counter() - t0
+    sampler.stop_flag = True
+    dev_s = ev0.elapsed_time(ev1) / 1e3
+    st = ctx.stats()
+    t = torch.tensor([dev_s, wall], dtype=torch.float64, device=f"cuda:{local_rank}")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_s, wall = t.tolist()
+    total_samples = W * H * P
+    # with per-launch stats reads the device-event bracket includes host gaps; both are reported, value uses the bracket
+    value = total_samples * args.steps / dev_s / 1e6
+
+    # e2e: host planes -> device, all passes, colours back to the host, every step (through the public C ABI)
+    e2e = None
+    if not args.no_e2e:
+        def e2e_step():
+            ctx.upload(planes)
+            step()
+            ctx.download_colors(out_host.numpy())
+        e2e_step()
+        barrier()
+        n_e2e = max(1, min(args.steps, 3))
+        t0 = time.perf_counter()
+        for _ in range(n_e2e):
+            e2e_step()
+        barrier()
+        e2e_s = torch.tensor([(time.perf_counter() - t0) / n_e2e], dtype=torch.float64, device=f"cuda:{local_rank}")
+        if dist is not None:
+            dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+        e2e = {"value": total_samples / e2e_s.item() / 1e6, "unit": UNIT,
+               "h2d_bytes_per_step": 19 * S_loc * 4 * world, "d2h_bytes_per_step": 3 * S_loc * 4 * world}
+
+    peak, peak_src = peaks()
+    k_ms = float(np.mean(kernel_ms)) if kernel_ms else None
+    own_samples = W * (band.own1 - band.own0) * P
+    roof = None
+    if k_ms:
+        achieved = ALG_BYTES_PER_SAMPLE_ITER * own_samples / (k_ms * 1e-3) / 1e9
+        roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "peak_source": peak_src, "kernel": "rpf_pixel_kernel",
+                "kernel_ms_per_launch": k_ms, "launches_timed": len(kernel_ms),
+                "note": "path is bound by shared-memory read-modify-write and FP64 issue, not HBM (DESIGN.md)"}
+    res = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dev_s / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload, "sharding": f"{world} row band(s), halo {band.own0 - band.buf0}/{band.buf1 - band.own1} rows",
+                   "l2": "inputs (0.9 GB per 1280x720x8 frame) exceed the 126 MB L2", "mean_neighbourhood":
+                       st["nbh_sum"] / max(1, st["pixels_filtered"])},
+        "wall_ms_per_step": wall / args.steps * 1e3, "gpu_launches": st["kernel_launches"], "nan_channels": st["nan_channels"],
+        "clocks": sampler.summary(), "roofline": roof, "e2e": e2e,
+    }
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        res["cpu_baseline"], _ = cpu_reference_run(args, boxes, 1, 0)
+    ctx.close()
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(res))
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,89 @@
+"""Row-band sharding of the RPF filter across ranks.
+
+Pixels are independent within one ApplyRPFFilter pass (Jacobi: reference src/custom/rpf.cpp:527,732), so the image is
+split into contiguous row bands, one per rank. Features, positions and random parameters never change
+(rpf.cpp:715 writes colours only): each rank holds its band plus `halo` rows of all 19 channels once. Between passes
+only the 3 colour planes of the rows within b_delta(next box) of a band edge move to the neighbouring rank
+(point-to-point send/recv; there is no collective). This module is backend agnostic: torch.distributed with NCCL on
+GPUs, gloo in the CPU tests.
+"""
+from dataclasses import dataclass
+
+
+def b_delta(box):
+    return (box - 1) // 2  # rpf.cpp:561
+
+
+@dataclass
+class Band:
+    rank: int
+    world: int
+    height: int      # global image height
+    own0: int        # first owned global row
+    own1: int        # one past the last owned global row
+    buf0: int        # first global row held in the local buffer (own0 - halo, clipped)
+    buf1: int        # one past the last global row held
+
+    @property
+    def local_height(self):
+        return self.buf1 - self.buf0
+
+    @property
+    def local_own(self):
+        """Owned rows in local buffer coordinates."""
+        return self.own0 - self.buf0, self.own1 - self.buf0
+
+
+def make_band(rank, world, height, box_sizes):
+    """Equal-height bands; halo = largest b_delta over all passes (feature rows are needed at that depth)."""
+    halo = max(b_delta(b) for b in box_sizes)
+    own0 = rank * height // world
+    own1 = (rank + 1) * height // world
+    return Band(rank, world, height, own0, own1, max(0, own0 - halo), min(height, own1 + halo))
+
+
+def halo_plan(band, next_box):
+    """Transfers after a pass so that the NEXT pass (box next_box) sees up-to-date colours.
+
+    Returns a list of (peer, send_rows, recv_rows) with row ranges in LOCAL buffer coordinates:
+    send_rows are owned rows this rank ships to `peer`, recv_rows are halo rows it receives from `peer`."""
+    d = b_delta(next_box)
+    plan = []
+    if d == 0:
+        return plan
+    lo0, lo1 = band.local_own
+    if band.rank > 0 and band.own1 > band.own0:
+        n_recv = min(d, band.own0 - band.buf0)
+        n_send = min(d, band.own1 - band.own0)
+        plan.append((band.rank - 1, (lo0, lo0 + n_send), (lo0 - n_recv, lo0)))
+    if band.rank < band.world - 1 and band.own1 > band.own0:
+        n_recv = min(d, band.buf1 - band.own1)
+        n_send = min(d, band.own1 - band.own0)
+        plan.append((band.rank + 1, (lo1 - n_send, lo1), (lo1, lo1 + n_recv)))
+    return plan
+
+
+def exchange_halos(dist, band, next_box, color_next, row_elems):
+    """color_next: torch tensor [3, local_height*row_elems] (the NEXT colour buffer, owned rows just written).
+    Sends/receives the halo rows for the next pass with batched point-to-point ops. row_elems = width*spp."""
+    ops, keep = [], []
+    for peer, (s0, s1), (r0, r1) in halo_plan(band, next_box):
+        for k in range(3):
+            if s1 > s0:
+                t = color_next[k, s0 * row_elems:s1 * row_elems]
+                ops.append(dist.P2POp(dist.isend, t, peer))
+            if r1 > r0:
+                t = color_next[k, r0 * row_elems:r1 * row_elems]
+                ops.append(dist.P2POp(dist.irecv, t, peer))
+        keep.append(peer)
+    if ops:
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+    return len(ops)
+
+
+def halo_bytes(band, next_box, row_elems, itemsize=8):
+    n = 0
+    for _, (s0, s1), _ in halo_plan(band, next_box):
+        n += 3 * (s1 - s0) * row_elems * itemsize
+    return n

@@ -64,7 +64,7 @@ def ref():
         lib.ref_has_filter.restype = C.c_int
         if lib.ref_has_filter():
             lib.ref_cf_weights.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
-            lib.ref_apply_rpf_filter.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+            lib.ref_apply_rpf_filter.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_double]
             lib.ref_apply_rpf_filter.restype = C.c_int
         _ref = lib
     return _ref
@@ -138,5 +138,5 @@ def ref_cf(z):
 def ref_filter(planes, W, H, P, box, colors=None, threads=1):
     planes = np.ascontiguousarray(planes, dtype=np.float32)
     col = np.ascontiguousarray(planes[2:5].astype(np.float64) if colors is None else colors, dtype=np.float64).copy()
-    flag = ref().ref_apply_rpf_filter(W, H, P, _p(planes), _p(col), box, threads)
+    flag = ref().ref_apply_rpf_filter(W, H, P, _p(planes), _p(col), box, threads, 0.002)
     return col, flag

@@ -1,0 +1,78 @@
+"""CPU: the C-ABI library loads and exports every symbol include/rpf_b200.h declares; host-side logic (synthetic
+generator, band planning, error behaviour without a GPU). No device compute here."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _lib_or_skip():
+    import rpf_b200
+    if not os.path.exists(rpf_b200.LIB_PATH):
+        import __graft_entry__
+        __graft_entry__.build()
+    return rpf_b200
+
+
+def test_header_symbols_are_exported():
+    rpf_b200 = _lib_or_skip()
+    hdr = open(os.path.join(ROOT, "include", "rpf_b200.h")).read()
+    declared = set(re.findall(r"\b(rpf_[a-z0-9_]+)\s*\(", hdr))
+    declared -= {"rpf_ctx"}
+    assert declared == set(rpf_b200.ABI_SYMBOLS), declared ^ set(rpf_b200.ABI_SYMBOLS)
+    L = C.CDLL(rpf_b200.LIB_PATH)
+    for s in declared:
+        assert hasattr(L, s), s
+
+
+def test_no_cpu_fallback_without_device():
+    rpf_b200 = _lib_or_skip()
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(rpf_b200.RPFError, match="no CUDA device|no CPU fallback"):
+        rpf_b200.RPFFilter(8, 8, 8)
+
+
+def test_synth_is_deterministic_and_band_consistent():
+    rpf_b200 = _lib_or_skip()
+    W, H, P = 12, 10, 4
+    a = rpf_b200.synth_planes(W, H, P, seed=9, kind=0)
+    b = rpf_b200.synth_planes(W, H, P, seed=9, kind=0)
+    assert np.array_equal(a, b) and a.dtype == np.float32
+    band = rpf_b200.synth_planes(W, 4, P, seed=9, kind=0, y_off=3)   # rows 3..6 generated on their own
+    assert np.array_equal(band.reshape(19, 4, W, P), a.reshape(19, H, W, P)[:, 3:7])
+    xs = a[0].reshape(H, W, P)
+    assert np.all(np.floor(xs) == np.arange(W)[None, :, None])        # pFilm.x = pixel + [0,1)
+    d = rpf_b200.synth_planes(W, H, P, seed=9, kind=1)
+    assert (d[7:19] == 0).mean() > 0.3                                # degenerate kind has flat / zero features
+    assert rpf_b200.lib().rpf_synth_planes(0, 1, 1, 1, 0, 0, 0, None) < 0
+
+
+def test_max_neighbourhood_covers_reference_box():
+    rpf_b200 = _lib_or_skip()
+    assert rpf_b200.lib().rpf_max_neighbourhood() >= 7 * 7 * 16      # box 7 (rpf.cpp:767) up to 16 spp
+
+
+def test_band_planning():
+    import bands
+    boxes = [55, 35, 17, 7]
+    H = 1080
+    bs = [bands.make_band(r, 8, H, boxes) for r in range(8)]
+    assert bs[0].own0 == 0 and bs[-1].own1 == H
+    assert all(bs[i].own1 == bs[i + 1].own0 for i in range(7))
+    assert bs[3].buf0 == bs[3].own0 - 27 and bs[0].buf0 == 0 and bs[7].buf1 == H
+    # sends of one rank match the receives of its neighbour, row for row (in global coordinates)
+    for nb in (35, 17, 7):
+        for r in range(7):
+            lo, hi = bs[r], bs[r + 1]
+            s = [(p, sr, rr) for p, sr, rr in bands.halo_plan(lo, nb) if p == r + 1][0]
+            t = [(p, sr, rr) for p, sr, rr in bands.halo_plan(hi, nb) if p == r][0]
+            g = lambda band, rows: (rows[0] + band.buf0, rows[1] + band.buf0)
+            assert g(lo, s[1]) == g(hi, t[2]) and g(hi, t[1]) == g(lo, s[2])
+            assert s[1][1] - s[1][0] == bands.b_delta(nb)
+    assert bands.halo_plan(bands.make_band(0, 1, H, boxes), 7) == []
