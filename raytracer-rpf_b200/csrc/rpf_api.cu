@@ -64,11 +64,14 @@ static int align16(int v) { return (v + 15) & ~15; }
 
 // Shared-memory plan for one pixel CTA. Returns false if the neighbourhood cannot fit.
 static bool plan_smem(long long ncap, int spp, int limit, SmemLayout &L) {
-    if (ncap > 65535) return false;  // u16 histogram cells, u8 bins (nb <= 255)
+    if (ncap > 1279) return false;  // u8 histogram cells with at most 4 remembered wraps (N >> 8 <= 4)
     L.ncap = static_cast<int>(ncap);
     L.nstride = L.ncap | 1;
     const int nb = bins_for(L.ncap);
-    L.wpl = (nb * nb + nb + 1) / 2;  // joint cells + nb slack cells (column marginals of the exact path)
+    // words per lane of a joint histogram (4 u8 cells per word); also large enough for the exact path's
+    // contiguous u16 table of nb*nb+nb entries spread over the warp's 32 columns
+    L.wpl = (nb * nb + 3) / 4;
+    while (L.wpl * 128 < 2 * (nb * nb + nb)) ++L.wpl;
     int off = 0;
     L.off_idx = off; off = align16(off + 4 * L.ncap);
     L.off_bins = off; off = align16(off + 20 * L.ncap);
@@ -76,9 +79,10 @@ static bool plan_smem(long long ncap, int spp, int limit, SmemLayout &L) {
     L.off_small = off;
     L.off_big = off;
     const long long raw = 1ll * L.nstride * (NC * 8 + 16 * 4);
-    const long long wgt = (20ll * L.ncap + 18ll * spp) * 8;
+    const long long wgt = 18ll * spp * 8;
     for (int mw = 4; mw >= 1; mw >>= 1) {
-        const long long hist = 1ll * mw * L.wpl * 128;
+        // with four histogram warps the last one only holds the 19 marginals (nb cells per lane)
+        const long long hist = mw == 4 ? (3ll * L.wpl + (nb + 3) / 4) * 128 : 1ll * mw * L.wpl * 128;
         long long big = raw > wgt ? raw : wgt;
         if (hist > big) big = hist;
         if (off + big <= limit) {
@@ -95,7 +99,7 @@ static const int kSmemLimit = 227 * 1024 - 6 * 1024;  // minus static PixelSmall
 extern "C" int rpf_max_neighbourhood(void) {
     int best = 0;
     SmemLayout L;
-    for (int n = 1; n <= 65535; n += 1)
+    for (int n = 1; n <= 1279; n += 1)
         if (plan_smem(n, 8, kSmemLimit, L)) best = n; else break;
     return best;
 }

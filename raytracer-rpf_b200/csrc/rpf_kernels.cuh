@@ -85,7 +85,9 @@ struct PixelSmall {
     double S[N_TASK];                // sum over cells of n ln n, per task
     double mi[N_JOINT];              // mutual information per pair
     double alpha[NC], beta[NF], wrc;
-    double red[4][36];               // cross-warp reduction scratch for the blend
+    double wrf[NF], dcf[NF], dsum[9], wrck[NC];   // phase-6 intermediates
+    double scl[NWZ], mz[NWZ];        // phase-7 per-channel scale and mean
+    double red[4][16];               // cross-warp reduction scratch for the blend
     int wcnt[2][4];
     int N, nb;
 };

@@ -12,7 +12,61 @@
 
 namespace rpf {
 
-__global__ void __launch_bounds__(THREADS) rpf_pixel_kernel(const FilterParams p) {
+// Histogram cell address: lane-private column of a [words][32 lanes] array, four u8 cells per 32-bit word.
+__device__ __forceinline__ uint8_t *cell_u8(unsigned char *colbase, int c) { return colbase + (c >> 2) * 128 + (c & 3); }
+
+// Phase-5 accumulation for one lane. Cells are u8; a cell that passes 255 wraps and its index is remembered in one of
+// K registers (at most N/256 wraps can happen), so the true count is low + 256 * (#remembered wraps of that cell).
+template <int K>
+__device__ __forceinline__ double accumulate_task(unsigned char *colbase, const uint8_t *ba, const uint8_t *bb, int sa, int sb,
+                                                  int N, const double *gtab) {
+    int ov[K > 0 ? K : 1];
+#pragma unroll
+    for (int k = 0; k < K; ++k) ov[k] = -1;
+    int nov = 0;
+    auto true_count = [&](int c, int low) {
+#pragma unroll
+        for (int k = 0; k < K; ++k) low += (ov[k] == c) ? 256 : 0;
+        return low;
+    };
+    auto wrapped = [&](int c) {
+#pragma unroll
+        for (int k = 0; k < K; ++k)
+            if (k == nov) ov[k] = c;
+        ++nov;
+    };
+    double acc = 0.0;
+    int j = 0;
+    for (; j + 1 < N; j += 2) {
+        const int c0 = ba[j * 20] * sa + bb[j * 20] * sb;
+        const int c1 = ba[j * 20 + 20] * sa + bb[j * 20 + 20] * sb;
+        uint8_t *p0 = cell_u8(colbase, c0), *p1 = cell_u8(colbase, c1);
+        const int l0 = *p0;
+        int l1 = *p1;
+        if (c0 == c1) l1 = (l0 + 1) & 255;  // both samples fall in one cell: the second sees the first's increment
+        *p0 = static_cast<uint8_t>(l0 + 1);
+        *p1 = static_cast<uint8_t>(l1 + 1);
+        int o0 = l0, o1 = l1;
+        if (K > 0) {
+            o0 = true_count(c0, l0);
+            if (l0 == 255) wrapped(c0);
+            o1 = true_count(c1, l1);
+            if (l1 == 255) wrapped(c1);
+        }
+        acc += gtab[o0];
+        acc += gtab[o1];
+    }
+    if (j < N) {
+        const int c0 = ba[j * 20] * sa + bb[j * 20] * sb;
+        uint8_t *p0 = cell_u8(colbase, c0);
+        const int l0 = *p0;
+        *p0 = static_cast<uint8_t>(l0 + 1);
+        acc += gtab[K > 0 ? true_count(c0, l0) : l0];
+    }
+    return acc;
+}
+
+__global__ void __launch_bounds__(THREADS, 4) rpf_pixel_kernel(const FilterParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ PixelSmall ps;
 
@@ -152,23 +206,41 @@ __global__ void __launch_bounds__(THREADS) rpf_pixel_kernel(const FilterParams p
     __syncthreads();
 
     // ---- phase 4: normalise + bin (mi.cpp:14-16) ------------------------------------------------------
+    // The reference bin is trunc(((x-M)/SD - lo)/(hi-lo) * nb) with every operation rounded. A reciprocal-multiply
+    // estimate of that value is within ~1e-15*nb of it; only when the estimate is closer than 1e-9 to an integer
+    // (or is NaN) can truncation differ, and only then are the exact divisions executed. Extremes are handled by
+    // identity: the minimum gives exactly 0 and the maximum exactly nb, which clamps to nb-1.
     {
         const double dnb = static_cast<double>(nb);
-        const int items = NCH * N;
-        for (int it = tid; it < items; it += THREADS) {
-            const int c = it / N, n = it - c * N;
+        for (int c = 0; c < NCH; ++c) {
             const bool isc = c >= CH_COL && c < CH_COL + NC;
-            const double x = isc ? rawc[(c - CH_COL) * nstride + n] : static_cast<double>(rawf[channel_slot(c) * nstride + n]);
-            const double lo = ps.lo[c], hi = ps.hi[c];
-            int b = 0;
-            if (!(hi == lo)) {
-                const double z = normalise(x, ps.M[c], ps.SD[c]);
-                const double t = __dmul_rn(__ddiv_rn(__dsub_rn(z, lo), __dsub_rn(hi, lo)), dnb);
-                b = __double2int_rz(t);
-                b = min(b, nb - 1);
-                b = max(b, 0);
+            const double lo = ps.lo[c], hi = ps.hi[c], m = ps.M[c], sd = ps.SD[c];
+            const double rlo = ps.rawlo[c], rhi = ps.rawhi[c];
+            const bool flat = hi == lo;
+            const bool ordered = hi > lo;  // false when sigma is NaN: everything takes the exact path
+            const double rsd = 1.0 / sd, rr = dnb / (hi - lo);
+            const double *pd = rawc + (isc ? c - CH_COL : 0) * nstride;
+            const float *pf = rawf + (isc ? 0 : channel_slot(c)) * nstride;
+            for (int n = tid; n < N; n += THREADS) {
+                const double x = isc ? pd[n] : static_cast<double>(pf[n]);
+                int b = 0;
+                if (!flat) {
+                    if (ordered && x == rlo) b = 0;
+                    else if (ordered && x == rhi) b = nb - 1;
+                    else {
+                        const double te = ((x - m) * rsd - lo) * rr;
+                        const double r = rint(te);
+                        if (ordered && fabs(te - r) > 1e-9 * (fabs(te) + 1.0)) {
+                            b = static_cast<int>(te);
+                        } else {
+                            const double z = normalise(x, m, sd);
+                            b = __double2int_rz(__dmul_rn(__ddiv_rn(__dsub_rn(z, lo), __dsub_rn(hi, lo)), dnb));
+                        }
+                        b = max(min(b, nb - 1), 0);
+                    }
+                }
+                bins[n * 20 + c] = static_cast<uint8_t>(b);
             }
-            bins[n * 20 + c] = static_cast<uint8_t>(b);
         }
     }
     __syncthreads();
@@ -191,32 +263,17 @@ __global__ void __launch_bounds__(THREADS) rpf_pixel_kernel(const FilterParams p
             int sa = nb, sb = 1;
             if (b < 0) { b = a; sa = 1; sb = 0; }
             const int ncell = grp == N_GROUP - 1 ? nb : nb * nb;
-            const int nwords = (ncell + 1) >> 1;
+            const int nwords = (ncell + 3) >> 2;
             for (int w = 0; w < nwords; ++w) hw[w * 32 + lane] = 0u;
             __syncwarp();
             if (active) {
-                double acc = 0.0;
                 const uint8_t *ba = bins + a, *bb = bins + b;
-                int j = 0;
-                for (; j + 1 < N; j += 2) {
-                    const int c0 = ba[j * 20] * sa + bb[j * 20] * sb;
-                    const int c1 = ba[j * 20 + 20] * sa + bb[j * 20 + 20] * sb;
-                    unsigned short *p0 = reinterpret_cast<unsigned short *>(colbase + (c0 >> 1) * 128 + (c0 & 1) * 2);
-                    unsigned short *p1 = reinterpret_cast<unsigned short *>(colbase + (c1 >> 1) * 128 + (c1 & 1) * 2);
-                    const int o0 = *p0;
-                    int o1 = *p1;
-                    if (c0 == c1) o1 = o0 + 1;   // both samples fall in one cell: second sees the first's increment
-                    *p0 = static_cast<unsigned short>(o0 + 1);
-                    *p1 = static_cast<unsigned short>(o1 + 1);
-                    acc += gtab[o0];
-                    acc += gtab[o1];
-                }
-                if (j < N) {
-                    const int c0 = ba[j * 20] * sa + bb[j * 20] * sb;
-                    unsigned short *p0 = reinterpret_cast<unsigned short *>(colbase + (c0 >> 1) * 128 + (c0 & 1) * 2);
-                    const int o0 = *p0;
-                    *p0 = static_cast<unsigned short>(o0 + 1);
-                    acc += gtab[o0];
+                double acc;
+                switch (N >> 8) {
+                    case 0: acc = accumulate_task<0>(colbase, ba, bb, sa, sb, N, gtab); break;
+                    case 1: acc = accumulate_task<1>(colbase, ba, bb, sa, sb, N, gtab); break;
+                    case 2: acc = accumulate_task<2>(colbase, ba, bb, sa, sb, N, gtab); break;
+                    default: acc = accumulate_task<4>(colbase, ba, bb, sa, sb, N, gtab); break;
                 }
                 ps.S[t] = acc;
             }
@@ -230,45 +287,51 @@ __global__ void __launch_bounds__(THREADS) rpf_pixel_kernel(const FilterParams p
     // exactly independent yet not constant it leaves rounding noise where mi.cpp may produce an exact 0 (every
     // p_xy/(p_x p_y) == 1.0, common for N = 8 with two bins). The P2 guards `den == 0 ? 0 : num/den` branch on
     // such zeros, so any pair whose MI is suspiciously small is recomputed cell by cell with the reference's own
-    // expression and rounding (mi.cpp:66-87). Rare, and always correct when taken.
+    // expression and rounding (mi.cpp:66-87). Rare; the flagged lanes of a warp take turns using the warp's whole
+    // histogram region as one contiguous u16 table.
     {
         const double dn = static_cast<double>(N);
         const double Stot = p.gpre[N];
         const double thr = 1e-4 / (dn * dn);
         if (warp < p.sm.mi_warps) {
-            uint32_t *hw = reinterpret_cast<uint32_t *>(big) + static_cast<size_t>(warp) * p.sm.wpl * 32;
-            unsigned char *colbase = reinterpret_cast<unsigned char *>(hw) + lane * 4;
-            auto cell = [&](int c) { return reinterpret_cast<unsigned short *>(colbase + (c >> 1) * 128 + (c & 1) * 2); };
+            unsigned short *tab = reinterpret_cast<unsigned short *>(reinterpret_cast<uint32_t *>(big) +
+                                                                      static_cast<size_t>(warp) * p.sm.wpl * 32);
             for (int grp = warp; grp < N_GROUP - 1; grp += p.sm.mi_warps) {
                 const int t = grp * 32 + lane;
                 int a, b;
                 task_channels(t, a, b);
                 // grouping keeps MI exactly 0 when either channel is constant (as mi.cpp yields exactly 0 there)
                 double mi = ((ps.S[t] - ps.S[N_JOINT + a]) - (ps.S[N_JOINT + b] - Stot)) / dn;
-                if (mi != 0.0 && fabs(mi) < thr) {
-                    const int ncell = nb * nb + nb;
-                    for (int w = 0; w < ((ncell + 1) >> 1); ++w) hw[w * 32 + lane] = 0u;
-                    const uint8_t *ba = bins + a, *bb = bins + b;
-                    for (int j = 0; j < N; ++j) *cell(ba[j * 20] * nb + bb[j * 20]) += 1;
-                    for (int j = 0; j < nb; ++j) {  // column marginals into the slack cells
-                        int sum = 0;
-                        for (int i = 0; i < nb; ++i) sum += *cell(i * nb + j);
-                        *cell(nb * nb + j) = static_cast<unsigned short>(sum);
-                    }
-                    mi = 0.0;
-                    for (int i = 0; i < nb; ++i) {
-                        int ni = 0;
-                        for (int j = 0; j < nb; ++j) ni += *cell(i * nb + j);
-                        if (ni == 0) continue;
-                        const double px = __ddiv_rn(static_cast<double>(ni), dn);
-                        for (int j = 0; j < nb; ++j) {
-                            const int n = *cell(i * nb + j);
-                            if (n == 0) continue;
-                            const double pxy = __ddiv_rn(static_cast<double>(n), dn);
-                            const double pp = __dmul_rn(px, __ddiv_rn(static_cast<double>(*cell(nb * nb + j)), dn));
-                            if (pp != 0.0) mi = __dadd_rn(mi, __dmul_rn(pxy, log(__ddiv_rn(pxy, pp))));
+                unsigned todo = __ballot_sync(0xffffffffu, mi != 0.0 && fabs(mi) < thr);
+                while (todo) {
+                    const int l = __ffs(todo) - 1;
+                    todo &= todo - 1;
+                    if (lane == l) {
+                        const int ncell = nb * nb + nb;
+                        for (int c = 0; c < ncell; ++c) tab[c] = 0;
+                        const uint8_t *ba = bins + a, *bb = bins + b;
+                        for (int j = 0; j < N; ++j) tab[ba[j * 20] * nb + bb[j * 20]] += 1;
+                        for (int j = 0; j < nb; ++j) {  // column marginals
+                            int sum = 0;
+                            for (int i = 0; i < nb; ++i) sum += tab[i * nb + j];
+                            tab[nb * nb + j] = static_cast<unsigned short>(sum);
+                        }
+                        mi = 0.0;
+                        for (int i = 0; i < nb; ++i) {
+                            int ni = 0;
+                            for (int j = 0; j < nb; ++j) ni += tab[i * nb + j];
+                            if (ni == 0) continue;
+                            const double px = __ddiv_rn(static_cast<double>(ni), dn);
+                            for (int j = 0; j < nb; ++j) {
+                                const int n = tab[i * nb + j];
+                                if (n == 0) continue;
+                                const double pxy = __ddiv_rn(static_cast<double>(n), dn);
+                                const double pp = __dmul_rn(px, __ddiv_rn(static_cast<double>(tab[nb * nb + j]), dn));
+                                if (pp != 0.0) mi = __dadd_rn(mi, __dmul_rn(pxy, log(__ddiv_rn(pxy, pp))));
+                            }
                         }
                     }
+                    __syncwarp();
                 }
                 ps.mi[t] = mi;
             }
@@ -277,67 +340,60 @@ __global__ void __launch_bounds__(THREADS) rpf_pixel_kernel(const FilterParams p
     __syncthreads();
 
     // ---- phase 6: dependencies -> alpha, beta, W_r_c (rpf.cpp:416-487) -----------------------------------
-    if (tid == 0) {
-        auto MI = [&](int t, int, int) { return ps.mi[t]; };
-        double D_r_f[NF], D_p_f[NF], D_c_f[NF], D_r_c[NC], D_p_c[NC], D_f_c[NC];
-        for (int i = 0; i < NF; ++i) {
-            const int a = CH_FEAT + i, t = 4 * i;
-            D_r_f[i] = (0.0 + MI(t, a, CH_RND)) + MI(t + 1, a, CH_RND + 1);
-            D_p_f[i] = (0.0 + MI(t + 2, a, CH_POS)) + MI(t + 3, a, CH_POS + 1);
-            D_c_f[i] = 0.0;
-        }
-        for (int i = 0; i < NC; ++i) {
-            const int a = CH_COL + i, t = 48 + 16 * i;
-            D_r_c[i] = (0.0 + MI(t, a, CH_RND)) + MI(t + 1, a, CH_RND + 1);
-            D_p_c[i] = (0.0 + MI(t + 2, a, CH_POS)) + MI(t + 3, a, CH_POS + 1);
-            double d = 0.0;
-            for (int j = 0; j < NF; ++j) {
-                const double m = MI(t + 4 + j, a, CH_FEAT + j);
-                d += m;
-                D_c_f[j] += m;
-            }
-            D_f_c[i] = d;
-        }
-        double Dfc = 0.0, Drc = 0.0, Dpc = 0.0;
-        for (int i = 0; i < NC; ++i) { Dfc += D_f_c[i]; Drc += D_r_c[i]; Dpc += D_p_c[i]; }
-        const bool p1 = p.flags & FLAG_P1, p2 = p.flags & FLAG_P2;
+    // mi[] order: 4*i + {r0,r1,p0,p1} for feature i; 48 + 16*i + {r0,r1,p0,p1,f0..f11} for colour i.
+    {
+        const bool p2 = p.flags & FLAG_P2;
         auto ratio = [&](double num, double den) { return (p2 && den == 0.0) ? 0.0 : num / den; };
-        double wrc = 0.0;
-        for (int i = 0; i < NC; ++i) {
-            const double w = ratio(D_r_c[i], D_r_c[i] + D_p_c[i]);
-            ps.alpha[i] = 1.0 - w;
-            wrc += w;
+        if (tid < NF) {
+            const int i = tid;
+            const double drf = (0.0 + ps.mi[4 * i]) + ps.mi[4 * i + 1];          // rpf.cpp:421
+            const double dpf = (0.0 + ps.mi[4 * i + 2]) + ps.mi[4 * i + 3];      // rpf.cpp:425
+            ps.wrf[i] = ratio(drf, drf + dpf);                                   // rpf.cpp:465
+            ps.dcf[i] = ((0.0 + ps.mi[52 + i]) + ps.mi[68 + i]) + ps.mi[84 + i]; // P1: sum over colours of MI(c_i, f_j)
+        } else if (tid >= 32 && tid < 32 + NC) {
+            const int i = tid - 32, t = 48 + 16 * i;
+            const double drc = (0.0 + ps.mi[t]) + ps.mi[t + 1];                  // rpf.cpp:432
+            const double dpc = (0.0 + ps.mi[t + 2]) + ps.mi[t + 3];              // rpf.cpp:436
+            double dfc = 0.0;
+            for (int j = 0; j < NF; ++j) dfc += ps.mi[t + 4 + j];                // rpf.cpp:440
+            ps.dsum[i] = dfc;
+            ps.dsum[3 + i] = drc;
+            ps.dsum[6 + i] = dpc;
+            const double w = ratio(drc, drc + dpc);                              // rpf.cpp:470
+            ps.wrck[i] = w;
+            ps.alpha[i] = 1.0 - w;                                               // rpf.cpp:475
         }
-        ps.wrc = wrc / NC;
-        for (int i = 0; i < NF; ++i) {
-            const double num = p1 ? D_c_f[i] : (i < NC ? D_f_c[i] : __longlong_as_double(0x7ff8000000000000ll));
-            const double wcf = ratio(num, Dfc + Drc + Dpc);
-            const double wrf = ratio(D_r_f[i], D_r_f[i] + D_p_f[i]);
-            ps.beta[i] = (1.0 - wrf) * wcf;
+        __syncthreads();
+        if (tid < NF) {
+            const int i = tid;
+            const double Dfc = ((0.0 + ps.dsum[0]) + ps.dsum[1]) + ps.dsum[2];   // rpf.cpp:449-456
+            const double Drc = ((0.0 + ps.dsum[3]) + ps.dsum[4]) + ps.dsum[5];
+            const double Dpc = ((0.0 + ps.dsum[6]) + ps.dsum[7]) + ps.dsum[8];
+            const double num = (p.flags & FLAG_P1) ? ps.dcf[i]
+                                                   : (i < NC ? ps.dsum[i] : __longlong_as_double(0x7ff8000000000000ll));
+            ps.beta[i] = (1.0 - ps.wrf[i]) * ratio(num, Dfc + Drc + Dpc);        // rpf.cpp:464,479
+        } else if (tid == 32) {
+            ps.wrc = (((0.0 + ps.wrck[0]) + ps.wrck[1]) + ps.wrck[2]) / NC;      // rpf.cpp:483-487
+            atomicAdd(&p.counters[0], static_cast<unsigned long long>(N));
+            atomicMin(&p.counters[2], static_cast<unsigned long long>(N));
+            atomicMax(&p.counters[3], static_cast<unsigned long long>(N));
         }
+        __syncthreads();
         if (p.dbg_n) {
-            p.dbg_n[pix] = N;
-            for (int i = 0; i < NC; ++i) p.dbg_alpha[pix * NC + i] = ps.alpha[i];
-            for (int i = 0; i < NF; ++i) p.dbg_beta[pix * NF + i] = ps.beta[i];
-            p.dbg_wrc[pix] = ps.wrc;
+            if (tid == 0) { p.dbg_n[pix] = N; p.dbg_wrc[pix] = ps.wrc; }
+            if (tid < NC) p.dbg_alpha[pix * NC + tid] = ps.alpha[tid];
+            if (tid < NF) p.dbg_beta[pix * NF + tid] = ps.beta[tid];
         }
-        atomicAdd(&p.counters[0], static_cast<unsigned long long>(N));
-        atomicMin(&p.counters[2], static_cast<unsigned long long>(N));
-        atomicMax(&p.counters[3], static_cast<unsigned long long>(N));
     }
-    __syncthreads();
 
     // ---- phase 7: cross-bilateral weights and blend (rpf.cpp:627-717) -------------------------------------
     // w_ij = exp(-sum_p d^2/(2 sp2)) * exp(-sum_c alpha d^2/(2 s2)) * exp(-sum_f beta d^2/(2 s2)) on NORMALISED
-    // values; here the three exponents are summed and each normalised channel is pre-scaled by
-    // sqrt(coefficient)/sigma, so a pair costs 17 subtract + 17 FMA + one exp. Differences to the
-    // three-exp product are O(1e-16) relative (and in which denormal weights flush to 0).
+    // values; here the three exponents are summed and each channel is pre-scaled by sqrt(coefficient)/sigma, so a
+    // pair costs 17 subtract + 17 FMA + one exp. Differences to the three-exp product are O(1e-16) relative (and in
+    // which denormal weights flush to 0). Each thread keeps its neighbour sample j in registers (read straight from
+    // global memory); only the P own samples are shared, sample-major for 128-bit broadcast loads.
     {
-        const int ncap = p.sm.ncap;
-        double *zs = reinterpret_cast<double *>(big);          // [17][ncap]  scaled normalised channels
-        double *rcol = zs + static_cast<size_t>(NWZ) * ncap;   // [3][ncap]   raw colours (blend uses un-normalised colours)
-        double *zi = rcol + static_cast<size_t>(NC) * ncap;    // [P][18]     own samples, sample-major for 128-bit broadcasts
-        double *scl = reinterpret_cast<double *>(ps.red);      // 17 scale factors (reuses scratch, consumed before the reduction)
+        double *zi = reinterpret_cast<double *>(big);  // [P][18]
         if (tid < NWZ) {
             const int k = tid;
             const int c = k < 5 ? k : k + 2;
@@ -348,40 +404,41 @@ __global__ void __launch_bounds__(THREADS) rpf_pixel_kernel(const FilterParams p
             else if (k < 5) coef = ps.alpha[k - 2] / (2.0 * s2);
             else coef = ps.beta[k - 5] / (2.0 * s2);
             const double sd = ps.SD[c];
-            scl[k] = sd == 0.0 ? 0.0 : sqrt(coef) / sd;
+            ps.scl[k] = sd == 0.0 ? 0.0 : sqrt(coef) / sd;
+            ps.mz[k] = ps.M[c];
         }
         __syncthreads();
-        for (int n = tid; n < N; n += THREADS) {
-            const uint32_t g = idx[n];
+        auto load_z = [&](uint32_t g, double *z, double *col) {
 #pragma unroll
             for (int k = 0; k < NWZ; ++k) {
-                const int c = k < 5 ? k : k + 2;
                 double x;
                 if (k >= 2 && k < 5) {
                     x = p.col_in[static_cast<size_t>(k - 2) * S + g];
-                    rcol[(k - 2) * ncap + n] = x;
+                    col[k - 2] = x;
                 } else {
-                    x = static_cast<double>(__ldg(p.f.planes + static_cast<size_t>(c) * S + g));
+                    x = static_cast<double>(__ldg(p.f.planes + static_cast<size_t>(k < 2 ? k : k + 2) * S + g));
                 }
-                const double z = (x - ps.M[c]) * scl[k];
-                zs[k * ncap + n] = z;
-                if (n < P) zi[n * 18 + k] = z;
+                z[k] = (x - ps.mz[k]) * ps.scl[k];
             }
-            if (n < P) zi[n * 18 + 17] = 0.0;
+        };
+        for (int n = tid; n < P; n += THREADS) {
+            double z[NWZ], col[NC];
+            load_z(idx[n], z, col);
+#pragma unroll
+            for (int k = 0; k < NWZ; ++k) zi[n * 18 + k] = z[k];
+            zi[n * 18 + 17] = 0.0;
         }
         __syncthreads();
 
-        constexpr int IC = 8;  // own samples per pass
+        constexpr int IC = 4;  // own samples per pass
         for (int i0 = 0; i0 < P; i0 += IC) {
             double sw[IC], swc[IC][NC];
 #pragma unroll
             for (int ii = 0; ii < IC; ++ii) { sw[ii] = 0.0; swc[ii][0] = swc[ii][1] = swc[ii][2] = 0.0; }
             for (int j = tid; j < N; j += THREADS) {
-                double zj[NWZ + 1];
-#pragma unroll
-                for (int k = 0; k < NWZ; ++k) zj[k] = zs[k * ncap + j];
+                double zj[NWZ + 1], cj[NC];
+                load_z(idx[j], zj, cj);
                 zj[NWZ] = 0.0;
-                const double c0 = rcol[j], c1 = rcol[ncap + j], c2 = rcol[2 * ncap + j];
 #pragma unroll
                 for (int ii = 0; ii < IC; ++ii) {
                     if (i0 + ii < P) {
@@ -397,13 +454,13 @@ __global__ void __launch_bounds__(THREADS) rpf_pixel_kernel(const FilterParams p
                         // exp(-arg) underflows to exactly 0 beyond ~745.2; NaN falls through to exp
                         const double w = arg > 745.2 ? 0.0 : exp(-arg);
                         sw[ii] += w;
-                        swc[ii][0] = fma(w, c0, swc[ii][0]);
-                        swc[ii][1] = fma(w, c1, swc[ii][1]);
-                        swc[ii][2] = fma(w, c2, swc[ii][2]);
+                        swc[ii][0] = fma(w, cj[0], swc[ii][0]);
+                        swc[ii][1] = fma(w, cj[1], swc[ii][1]);
+                        swc[ii][2] = fma(w, cj[2], swc[ii][2]);
                     }
                 }
             }
-            // reduce the 32 partial sums over the CTA
+            // reduce the 16 partial sums over the CTA
             __syncthreads();  // previous pass finished with ps.red
 #pragma unroll
             for (int ii = 0; ii < IC; ++ii) {
