@@ -31,7 +31,7 @@ typedef enum rpf_status {
     RPF_ERR_INVALID = -1,     /* bad argument */
     RPF_ERR_CUDA = -2,        /* CUDA runtime error (message has the CUDA string) */
     RPF_ERR_NO_DEVICE = -3,   /* no CUDA device / not an sm_100 part */
-    RPF_ERR_UNSUPPORTED = -4, /* neighbourhood too large for this build (see message) */
+    RPF_ERR_UNSUPPORTED = -4, /* box*box*spp above rpf_max_neighbourhood() (see message) */
     RPF_ERR_STATE = -5        /* call order (e.g. filter before upload) */
 } rpf_status;
 
@@ -42,6 +42,9 @@ typedef enum rpf_status {
 #define RPF_FLAG_P3_CLAMP_VAR 4   /* neighbourhood sigma = sqrt(max(0,var)) (ops.h:141) */
 #define RPF_FLAGS_DEFINED 7
 #define RPF_FLAGS_VERBATIM 0x100    /* none of P1-P3: beta[3..11] is NaN (the reference value is undefined there) */
+/* Testing / tuning switch, may be OR-ed into flags: route every box size through the general three-kernel path
+ * (membership mask in HBM, shared-atomic histograms) even where the fused shared-memory kernel would serve it. */
+#define RPF_FLAG_FORCE_GENERAL 0x200
 
 typedef struct rpf_ctx rpf_ctx;
 
@@ -107,7 +110,7 @@ int rpf_reconstruct_box(rpf_ctx *ctx, float *rgb);
 int rpf_get_stats(rpf_ctx *ctx, rpf_stats_t *out);
 int rpf_reset_stats(rpf_ctx *ctx);
 
-/* Largest neighbourhood (box*box*spp samples) this build can filter, for error messages and tests. */
+/* Largest neighbourhood (box*box*spp candidate samples) this build can filter, for error messages and tests. */
 int rpf_max_neighbourhood(void);
 
 /* Deterministic synthetic feature buffer, host side, float32 values.

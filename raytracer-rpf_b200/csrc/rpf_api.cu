@@ -5,11 +5,13 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
 
 #include "rpf_pixel_kernel.cuh"
+#include "rpf_general.cuh"
 
 using namespace rpf;
 
@@ -22,8 +24,18 @@ struct rpf_ctx {
     int cur = 0;
     double *d_pstat = nullptr;      // [npix][24]
     int pstat_y0 = 0, pstat_y1 = 0; // rows with valid per-pixel statistics
-    double *d_gtab = nullptr, *d_gpre = nullptr;
+    double *d_gtab = nullptr, *d_gpre = nullptr, *d_hln = nullptr;
+    unsigned long long *d_gq = nullptr, *d_hq = nullptr;
     int gtab_n = 0;
+    // general path (rpf_general.cuh): per-chunk scratch in HBM
+    uint32_t *d_mask = nullptr;
+    double *d_rec = nullptr;
+    uint8_t *d_bins = nullptr;
+    unsigned int *d_work = nullptr;
+    size_t mask_bytes = 0, rec_bytes = 0, bins_bytes = 0;
+    int kb_static_smem = 0, num_sms = 0;
+    bool force_general = false;
+    size_t scratch_budget = 2048ull << 20;
     unsigned long long *d_counters = nullptr;  // 4
     int *d_dbg_n = nullptr;
     double *d_dbg_alpha = nullptr, *d_dbg_beta = nullptr, *d_dbg_wrc = nullptr;
@@ -96,13 +108,7 @@ static bool plan_smem(long long ncap, int spp, int limit, SmemLayout &L) {
 
 static const int kSmemLimit = 227 * 1024 - 6 * 1024;  // minus static PixelSmall and the per-CTA reserve
 
-extern "C" int rpf_max_neighbourhood(void) {
-    int best = 0;
-    SmemLayout L;
-    for (int n = 1; n <= 1279; n += 1)
-        if (plan_smem(n, 8, kSmemLimit, L)) best = n; else break;
-    return best;
-}
+extern "C" int rpf_max_neighbourhood(void) { return 65535; }
 
 extern "C" const char *rpf_last_error(const rpf_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
 
@@ -115,6 +121,13 @@ extern "C" void rpf_destroy(rpf_ctx *ctx) {
     cudaFree(ctx->d_pstat);
     cudaFree(ctx->d_gtab);
     cudaFree(ctx->d_gpre);
+    cudaFree(ctx->d_hln);
+    cudaFree(ctx->d_gq);
+    cudaFree(ctx->d_hq);
+    cudaFree(ctx->d_mask);
+    cudaFree(ctx->d_rec);
+    cudaFree(ctx->d_bins);
+    cudaFree(ctx->d_work);
     cudaFree(ctx->d_counters);
     cudaFree(ctx->d_dbg_n);
     cudaFree(ctx->d_dbg_alpha);
@@ -138,24 +151,46 @@ static int reset_counters(rpf_ctx *ctx) {
 static int ensure_gtab(rpf_ctx *ctx, int n) {
     if (n + 2 <= ctx->gtab_n) return RPF_OK;
     const int m = n + 2;
-    std::vector<double> g(m), pre(m + 1);
+    std::vector<double> g(m), pre(m + 1), hln(m + 1);
+    const int mq = m > KB_GSM ? m : KB_GSM;
+    std::vector<unsigned long long> gq(mq, 0ull), hq(mq + 1, 0ull);  // fixed point, unit 2^-43 (rpf_general.cuh)
     for (int k = 0; k < m; ++k) {
         const long double a = k + 1, b = k;
         g[k] = static_cast<double>(a * logl(a) - (k ? b * logl(b) : 0.0L));
+        hln[k] = k ? static_cast<double>(b * logl(b)) : 0.0;
     }
+    for (int k = 0; k < mq; ++k) {
+        const long double a = k + 1, b = k;
+        gq[k] = static_cast<unsigned long long>(llroundl((a * logl(a) - (k ? b * logl(b) : 0.0L)) * 8796093022208.0L));
+        hq[k + 1] = hq[k] + gq[k];
+    }
+    hln[m] = static_cast<double>(static_cast<long double>(m) * logl(static_cast<long double>(m)));
     double acc = 0.0;
     pre[0] = 0.0;
     for (int k = 0; k < m; ++k) {
         acc += g[k];
         pre[k + 1] = acc;
     }
+    CU(ctx, cudaStreamSynchronize(ctx->stream));  // kernels in flight may still read the old tables
     cudaFree(ctx->d_gtab);
     cudaFree(ctx->d_gpre);
-    ctx->d_gtab = ctx->d_gpre = nullptr;
-    CU(ctx, cudaMalloc(&ctx->d_gtab, m * sizeof(double)));
+    cudaFree(ctx->d_hln);
+    cudaFree(ctx->d_gq);
+    cudaFree(ctx->d_hq);
+    ctx->d_gtab = ctx->d_gpre = ctx->d_hln = nullptr;
+    ctx->d_gq = ctx->d_hq = nullptr;
+    ctx->gtab_n = 0;
+    CU(ctx, cudaMalloc(&ctx->d_gtab, (m > KB_GSM ? m : KB_GSM) * sizeof(double)));
     CU(ctx, cudaMalloc(&ctx->d_gpre, (m + 1) * sizeof(double)));
+    CU(ctx, cudaMalloc(&ctx->d_hln, (m + 1) * sizeof(double)));
+    CU(ctx, cudaMemset(ctx->d_gtab, 0, (m > KB_GSM ? m : KB_GSM) * sizeof(double)));
     CU(ctx, cudaMemcpy(ctx->d_gtab, g.data(), m * sizeof(double), cudaMemcpyHostToDevice));
     CU(ctx, cudaMemcpy(ctx->d_gpre, pre.data(), (m + 1) * sizeof(double), cudaMemcpyHostToDevice));
+    CU(ctx, cudaMemcpy(ctx->d_hln, hln.data(), (m + 1) * sizeof(double), cudaMemcpyHostToDevice));
+    CU(ctx, cudaMalloc(&ctx->d_gq, mq * sizeof(unsigned long long)));
+    CU(ctx, cudaMalloc(&ctx->d_hq, (mq + 1) * sizeof(unsigned long long)));
+    CU(ctx, cudaMemcpy(ctx->d_gq, gq.data(), mq * sizeof(unsigned long long), cudaMemcpyHostToDevice));
+    CU(ctx, cudaMemcpy(ctx->d_hq, hq.data(), (mq + 1) * sizeof(unsigned long long), cudaMemcpyHostToDevice));
     ctx->gtab_n = m;
     return RPF_OK;
 }
@@ -177,6 +212,7 @@ extern "C" int rpf_create(rpf_ctx **out, const rpf_config *cfg) {
                     cfg->device);
     rpf_ctx *ctx = new rpf_ctx;
     ctx->cfg = *cfg;
+    ctx->cfg.flags &= ~RPF_FLAG_FORCE_GENERAL;
     if (ctx->cfg.flags == 0) ctx->cfg.flags = RPF_FLAGS_DEFINED;
     ctx->S = 1ull * cfg->width * cfg->height * cfg->spp;
     ctx->npix = cfg->width * cfg->height;
@@ -207,6 +243,17 @@ extern "C" int rpf_create(rpf_ctx **out, const rpf_config *cfg) {
         CUC(cudaMemset(ctx->d_dbg_n, 0, ctx->npix * sizeof(int)));
     }
     CUC(cudaFuncSetAttribute(rpf_pixel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
+    {
+        cudaFuncAttributes fa;
+        CUC(cudaFuncGetAttributes(&fa, dependency_kernel));
+        ctx->kb_static_smem = static_cast<int>(fa.sharedSizeBytes);
+        CUC(cudaFuncSetAttribute(dependency_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 227 * 1024 - ctx->kb_static_smem - 1024));
+        ctx->num_sms = prop.multiProcessorCount;
+        CUC(cudaMalloc(&ctx->d_work, sizeof(unsigned int)));
+        ctx->force_general = (cfg->flags & RPF_FLAG_FORCE_GENERAL) || (getenv("RPF_FORCE_GENERAL") && atoi(getenv("RPF_FORCE_GENERAL")));
+        if (const char *mb = getenv("RPF_SCRATCH_MB")) if (atoll(mb) > 0) ctx->scratch_budget = static_cast<size_t>(atoll(mb)) << 20;
+    }
 #undef CUC
     int rc = reset_counters(ctx);
     if (rc != RPF_OK) {
@@ -259,28 +306,146 @@ extern "C" int rpf_upload_colors_f64(rpf_ctx *ctx, const double *rgb) {
     return RPF_OK;
 }
 
+
+// ---- general path (rpf_general.cuh) ----------------------------------------------------------------------
+static const int kGeneralMaxCandidates = 65535;  // u16 candidate numbers and histogram cells, u8 bins (nb <= 255)
+
+// Shared-memory plan of the dependency kernel for ncap = box*box*spp candidates.
+static bool plan_general(long long ncap, int spp, int dyn_limit, GeneralPlan &L) {
+    if (ncap > kGeneralMaxCandidates) return false;
+    L.ncap = static_cast<int>(ncap);
+    L.mw = ((L.ncap + 127) / 128) * 4;
+    L.nq = (L.ncap + 3) / 4;
+    const int nb = bins_for(L.ncap);
+    L.nbs = (nb + 3) & ~3;
+    L.hw = (((nb * nb + 1) / 2) + 3) & ~3;
+    L.off_gsm = 0;
+    L.off_marg = KB_GSM * 8;
+    L.off_region = align16(L.off_marg + NCH * L.nbs * 4);
+    const int idx_bytes = align16(2 * L.ncap);
+    const int bins_bytes = NCH * L.nq * 4;
+    auto region = [&](int G) { const int h = G * L.hw * 4; return h > idx_bytes ? h : idx_bytes; };
+    L.kc_smem = spp * 18 * 8;
+    // bins stay in shared memory only when four histograms fit beside them; otherwise they go to an L2-resident
+    // per-CTA scratch and the histogram region takes what is there
+    if (L.off_region + region(4) + bins_bytes <= dyn_limit) {
+        L.G = 4;
+        L.bins_in_smem = 1;
+        L.off_bins = L.off_region + region(4);
+        L.kb_smem = L.off_bins + bins_bytes;
+        return true;
+    }
+    for (int G = 4; G >= 1; G >>= 1) {
+        if (L.off_region + region(G) <= dyn_limit) {
+            L.G = G;
+            L.bins_in_smem = 0;
+            L.off_bins = 0;
+            L.kb_smem = L.off_region + region(G);
+            return true;
+        }
+    }
+    return false;
+}
+
+template <class T>
+static int ensure_buffer(rpf_ctx *ctx, T **ptr, size_t *have, size_t need) {
+    if (need <= *have) return RPF_OK;
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    cudaFree(*ptr);
+    *ptr = nullptr;
+    *have = 0;
+    CU(ctx, cudaMalloc(ptr, need));
+    *have = need;
+    return RPF_OK;
+}
+
+static int ensure_pstat(rpf_ctx *ctx, const FrameView &f, int y0, int y1) {
+    if (ctx->pstat_y0 <= y0 && y1 <= ctx->pstat_y1) return RPF_OK;
+    // features never change between iterations (rpf.cpp:715 writes colours only): computed once per upload
+    const long long n = 1ll * (y1 - y0) * ctx->cfg.width * NF;
+    pixel_stats_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, ctx->stream>>>(f, y0, y1, ctx->d_pstat);
+    ctx->launches++;
+    CU(ctx, cudaGetLastError());
+    if (ctx->pstat_y1 <= ctx->pstat_y0) { ctx->pstat_y0 = y0; ctx->pstat_y1 = y1; }
+    else { ctx->pstat_y0 = y0 < ctx->pstat_y0 ? y0 : ctx->pstat_y0; ctx->pstat_y1 = y1 > ctx->pstat_y1 ? y1 : ctx->pstat_y1; }
+    return RPF_OK;
+}
+
+static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
+    GeneralParams p{};
+    const int dyn_limit = 227 * 1024 - ctx->kb_static_smem - 1024;
+    if (!plan_general(1ll * box * box * ctx->cfg.spp, ctx->cfg.spp, dyn_limit, p.pl))
+        return fail(ctx, RPF_ERR_UNSUPPORTED,
+                    "neighbourhood of box %d x %d spp = %lld candidates exceeds this build (max %d: 16-bit histogram cells)", box,
+                    ctx->cfg.spp, 1ll * box * box * ctx->cfg.spp, kGeneralMaxCandidates);
+    if (p.pl.kc_smem > 40 * 1024) return fail(ctx, RPF_ERR_UNSUPPORTED, "spp %d too large for the blend kernel", ctx->cfg.spp);
+    int rc = ensure_gtab(ctx, p.pl.ncap);
+    if (rc != RPF_OK) return rc;
+    p.f = FrameView{ctx->d_planes, ctx->S, ctx->cfg.width, ctx->cfg.height, ctx->cfg.spp};
+    rc = ensure_pstat(ctx, p.f, y0, y1);
+    if (rc != RPF_OK) return rc;
+    const int W = ctx->cfg.width;
+    const size_t per_pixel = static_cast<size_t>(p.pl.mw) * 4 + REC_DOUBLES * 8;
+    long long rows = static_cast<long long>(ctx->scratch_budget / (per_pixel * W));
+    if (rows < 1) rows = 1;
+    if (rows > y1 - y0) rows = y1 - y0;
+    int occ = 0;
+    CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dependency_kernel, KB_THREADS, p.pl.kb_smem));
+    if (occ < 1) return fail(ctx, RPF_ERR_CUDA, "dependency kernel does not fit on an SM with %d bytes of shared memory", p.pl.kb_smem);
+    const long long chunk_px = rows * W;
+    p.pl.kb_grid = static_cast<int>(chunk_px < 1ll * occ * ctx->num_sms ? chunk_px : 1ll * occ * ctx->num_sms);
+    if ((rc = ensure_buffer(ctx, &ctx->d_mask, &ctx->mask_bytes, static_cast<size_t>(chunk_px) * p.pl.mw * 4)) != RPF_OK) return rc;
+    if ((rc = ensure_buffer(ctx, &ctx->d_rec, &ctx->rec_bytes, static_cast<size_t>(chunk_px) * REC_DOUBLES * 8)) != RPF_OK) return rc;
+    if (!p.pl.bins_in_smem &&
+        (rc = ensure_buffer(ctx, &ctx->d_bins, &ctx->bins_bytes, static_cast<size_t>(p.pl.kb_grid) * NCH * p.pl.nq * 4)) != RPF_OK)
+        return rc;
+    p.col_in = ctx->d_col[ctx->cur];
+    p.col_out = ctx->d_col[ctx->cur ^ 1];
+    p.pstat = ctx->d_pstat;
+    p.gq = ctx->d_gq;
+    p.hq = ctx->d_hq;
+    p.box = box;
+    p.flags = ctx->cfg.flags;
+    p.seed = seed;
+    p.mask = ctx->d_mask;
+    p.rec = ctx->d_rec;
+    p.bins_scratch = ctx->d_bins;
+    p.work_counter = ctx->d_work;
+    p.dbg_n = ctx->d_dbg_n;
+    p.dbg_alpha = ctx->d_dbg_alpha;
+    p.dbg_beta = ctx->d_dbg_beta;
+    p.dbg_wrc = ctx->d_dbg_wrc;
+    p.counters = ctx->d_counters;
+    for (int r0 = y0; r0 < y1; r0 += static_cast<int>(rows)) {
+        p.row0 = r0;
+        p.nrows = r0 + rows <= y1 ? static_cast<int>(rows) : y1 - r0;
+        const unsigned npx = static_cast<unsigned>(p.nrows * W);
+        CU(ctx, cudaMemsetAsync(ctx->d_work, 0, sizeof(unsigned int), ctx->stream));
+        nbh_stats_kernel<<<npx, KA_THREADS, 0, ctx->stream>>>(p);
+        const unsigned gridb = npx < static_cast<unsigned>(p.pl.kb_grid) ? npx : static_cast<unsigned>(p.pl.kb_grid);
+        dependency_kernel<<<gridb, KB_THREADS, p.pl.kb_smem, ctx->stream>>>(p);
+        blend_kernel<<<npx, KC_THREADS, p.pl.kc_smem, ctx->stream>>>(p);
+        ctx->launches += 3;
+        CU(ctx, cudaGetLastError());
+    }
+    ctx->pixels_filtered += 1ll * (y1 - y0) * W;
+    return RPF_OK;
+}
+
 static int launch_rows(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
     if (!ctx->uploaded) return fail(ctx, RPF_ERR_STATE, "rpf_filter: no samples uploaded");
     if (box < 1 || (box & 1) == 0) return fail(ctx, RPF_ERR_INVALID, "box size %d must be odd and positive (rpf.cpp:561)", box);
     if (y0 < 0 || y1 > ctx->cfg.height || y0 >= y1) return fail(ctx, RPF_ERR_INVALID, "bad row range [%d,%d)", y0, y1);
     if (!(seed > 0.0)) return fail(ctx, RPF_ERR_INVALID, "sigma_fc_seed must be positive");
     FilterParams p{};
-    if (!plan_smem(1ll * box * box * ctx->cfg.spp, ctx->cfg.spp, ctx->max_dyn_smem, p.sm))
-        return fail(ctx, RPF_ERR_UNSUPPORTED,
-                    "neighbourhood of box %d x %d spp = %lld samples exceeds the shared-memory resident kernel (max %d)", box,
-                    ctx->cfg.spp, 1ll * box * box * ctx->cfg.spp, rpf_max_neighbourhood());
+    // the fused shared-memory-resident kernel serves small neighbourhoods; everything else takes the general path
+    if (ctx->force_general || !plan_smem(1ll * box * box * ctx->cfg.spp, ctx->cfg.spp, ctx->max_dyn_smem, p.sm))
+        return launch_general(ctx, box, seed, y0, y1);
     int rc = ensure_gtab(ctx, p.sm.ncap);
     if (rc != RPF_OK) return rc;
     p.f = FrameView{ctx->d_planes, ctx->S, ctx->cfg.width, ctx->cfg.height, ctx->cfg.spp};
-    if (!(ctx->pstat_y0 <= y0 && y1 <= ctx->pstat_y1)) {
-        // features never change between iterations (rpf.cpp:715 writes colours only): computed once per upload
-        const long long n = 1ll * (y1 - y0) * ctx->cfg.width * NF;
-        pixel_stats_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, ctx->stream>>>(p.f, y0, y1, ctx->d_pstat);
-        ctx->launches++;
-        CU(ctx, cudaGetLastError());
-        if (ctx->pstat_y1 <= ctx->pstat_y0) { ctx->pstat_y0 = y0; ctx->pstat_y1 = y1; }
-        else { ctx->pstat_y0 = y0 < ctx->pstat_y0 ? y0 : ctx->pstat_y0; ctx->pstat_y1 = y1 > ctx->pstat_y1 ? y1 : ctx->pstat_y1; }
-    }
+    rc = ensure_pstat(ctx, p.f, y0, y1);
+    if (rc != RPF_OK) return rc;
     p.col_in = ctx->d_col[ctx->cur];
     p.col_out = ctx->d_col[ctx->cur ^ 1];
     p.pstat = ctx->d_pstat;

@@ -1,0 +1,752 @@
+// rpf_general.cuh -- the general (any neighbourhood size) RPF path: three kernels per ApplyRPFFilter pass.
+//
+//   KA  nbh_stats_kernel   3-sigma membership over the box -> per-pixel acceptance bit mask, N, and the
+//                          neighbourhood mean / sigma / min / max of all 19 channels           [rpf.cpp:556-601]
+//   KB  dependency_kernel  normalise + bin every accepted sample, 96 joint histograms in shared memory
+//                          (shared atomics), mutual information, alpha / beta / W_r_c        [rpf.cpp:603-618,356-488; mi.cpp]
+//   KC  blend_kernel       cross-bilateral weights of the P own samples against the N accepted samples, blend
+//                                                                                              [rpf.cpp:627-717]
+//
+// The fused one-CTA-per-pixel kernel (rpf_pixel_kernel.cuh) keeps the whole neighbourhood in shared memory and
+// lane-private histograms, which stops at N = 1279. Here nothing per-sample is resident: KA leaves one bit per
+// candidate in HBM (candidate order = reference enumeration order xn, yn, sample: rpf.cpp:562-573), KB and KC
+// regenerate the sample list from it. What must follow the reference's order -- the sequential FP64 sums behind
+// mean and sigma (ops.h:111-144), whose rounding decides bin boundaries -- is done in KA by one lane per channel
+// walking the accepted samples in that order; everything else is order independent (integer counts) or differs
+// from the CPU at the 1e-15 level (sums of logs, sums of weights).
+#pragma once
+#include "rpf_kernels.cuh"
+
+namespace rpf {
+
+constexpr int REC_M = 0, REC_SD = 19, REC_RLO = 38, REC_RHI = 57, REC_N = 76, REC_ALPHA = 77, REC_BETA = 80, REC_WRC = 92;
+constexpr int REC_DOUBLES = 96;  // per-pixel record in HBM scratch
+constexpr int KA_THREADS = 128, KA_STRIDE = 129;
+constexpr int KB_THREADS = 512, KB_GSM = 1024;
+constexpr int KC_THREADS = 128, KC_SEG_WORDS = 128, KC_IC = 8;
+
+struct GeneralPlan {
+    int ncap;        // box*box*spp candidates
+    int mw;          // mask words per pixel (multiple of 4)
+    int nq;          // ceil(ncap/4): words per channel of packed u8 bins
+    int G;           // joint histograms accumulated concurrently (4, 2 or 1)
+    int hw;          // words per joint histogram (two u16 cells per word), multiple of 4
+    int nbs;         // words per marginal histogram
+    int bins_in_smem;
+    int off_gsm, off_marg, off_region, off_bins, kb_smem;  // KB dynamic shared memory layout (bytes)
+    int kb_grid;
+    int kc_smem;
+};
+
+struct GeneralParams {
+    FrameView f;
+    const double *col_in;
+    double *col_out;
+    const double *pstat;
+    // Fixed-point entropy tables (unit 2^-43): gq[k] = round(((k+1)ln(k+1) - k ln k) * 2^43), hq[n] = gq[0]+...+gq[n-1]
+    // (~ n ln n). Integer sums are exact and order independent, so the atomics-ordered accumulation is deterministic.
+    const unsigned long long *gq;
+    const unsigned long long *hq;
+    int box, flags;
+    double seed;
+    int row0, nrows;      // pixel rows of this chunk
+    uint32_t *mask;       // [chunk pixels][mw]
+    double *rec;          // [chunk pixels][REC_DOUBLES]
+    uint8_t *bins_scratch;  // [kb_grid][19][nq*4] when bins do not fit in shared memory
+    unsigned int *work_counter;
+    GeneralPlan pl;
+    int *dbg_n;
+    double *dbg_alpha, *dbg_beta, *dbg_wrc;
+    unsigned long long *counters;
+};
+
+__device__ __forceinline__ float warp_min_f(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ unsigned long long warp_sum_u64(unsigned long long v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max_f(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// candidate t -> global sample index, or false when the neighbour pixel is out of bounds (rpf.cpp:569)
+__device__ __forceinline__ bool candidate_sample(int t, int px, int py, int B, int P, int W, int H, uint32_t &g, bool &centre) {
+    const int BP = B * P, bd = (B - 1) / 2;
+    const int bx = t / BP, r = t - bx * BP, by = r / P, s = r - by * P;
+    const int xn = px - bd + bx, yn = py - bd + by;
+    centre = (xn == px) && (yn == py);
+    if (xn < 0 || xn >= W || yn < 0 || yn >= H) return false;
+    g = static_cast<uint32_t>((static_cast<size_t>(yn) * W + xn) * P + s);
+    return true;
+}
+
+// =====================================================================================================
+// KA: membership mask + ordered statistics. One CTA of 128 threads per pixel.
+struct KASmem {
+    float sf[2][16][KA_STRIDE];   // staged non-colour channels (slot order of slot_channel), double buffered
+    double sc[2][NC][KA_STRIDE];  // staged colours
+    double mu[NF], sd3[NF];
+    int wcnt[2][4];
+    int cnt[2];
+    float redf[4][32];
+    double redd[4][6];
+};
+
+__global__ void __launch_bounds__(KA_THREADS) nbh_stats_kernel(const GeneralParams p) {
+    __shared__ KASmem sm;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int W = p.f.W, H = p.f.H, P = p.f.P;
+    const size_t S = p.f.S;
+    const int pl = blockIdx.x;
+    const int py = p.row0 + pl / W, px = pl - (pl / W) * W;
+    const size_t pix = static_cast<size_t>(py) * W + px;
+    const uint32_t base = static_cast<uint32_t>(pix * P);
+    uint32_t *mask = p.mask + static_cast<size_t>(pl) * p.pl.mw;
+
+    if (tid < 2 * NF) {
+        const double v = p.pstat[pix * 24 + tid];
+        if (tid < NF) sm.mu[tid] = v; else sm.sd3[tid - NF] = v;
+    }
+    float mn[16], mx[16];
+    double cmn[NC], cmx[NC];
+#pragma unroll
+    for (int s = 0; s < 16; ++s) { mn[s] = __int_as_float(0x7f800000); mx[s] = __int_as_float(0xff800000); }
+#pragma unroll
+    for (int k = 0; k < NC; ++k) { cmn[k] = __longlong_as_double(0x7ff0000000000000ll); cmx[k] = __longlong_as_double(0xfff0000000000000ll); }
+    double acc = 0.0, sq = 0.0;  // warp 0, lane c < 19: sequential sum and sum of squares of channel c (ops.h:111-144)
+
+    auto stage = [&](int buf, int slot, uint32_t g, const float *feat) {
+        // loads what the membership test has not loaded yet, tracks min / max, writes the staging slot
+#pragma unroll
+        for (int s = 0; s < 16; ++s) {
+            const float v = (feat && s >= 4) ? feat[s - 4] : __ldg(p.f.planes + static_cast<size_t>(slot_channel(s)) * S + g);
+            mn[s] = v < mn[s] ? v : mn[s];
+            mx[s] = mx[s] < v ? v : mx[s];
+            sm.sf[buf][s][slot] = v;
+        }
+#pragma unroll
+        for (int k = 0; k < NC; ++k) {
+            const double v = p.col_in[static_cast<size_t>(k) * S + g];
+            cmn[k] = v < cmn[k] ? v : cmn[k];
+            cmx[k] = cmx[k] < v ? v : cmx[k];
+            sm.sc[buf][k][slot] = v;
+        }
+    };
+    auto chain = [&](int buf) {
+        if (warp == 0 && lane < NCH) {
+            const int n = sm.cnt[buf];
+            const int c = lane;
+            const bool isc = c >= CH_COL && c < CH_COL + NC;
+            const double *pd = sm.sc[buf][isc ? c - CH_COL : 0];
+            const float *pf = sm.sf[buf][isc ? 0 : channel_slot(c)];
+            for (int k = 0; k < n; ++k) {  // one loop for all lanes: colour lanes read doubles, the rest floats
+                const double v = isc ? pd[k] : static_cast<double>(pf[k]);
+                acc = __dadd_rn(acc, v);
+                sq = __dadd_rn(sq, __dmul_rn(v, v));
+            }
+        }
+    };
+
+    // own samples first, unconditionally and in order (rpf.cpp:558). Every round: barrier, stage this round's accepted
+    // samples into buffer round&1, then warp 0 sums the buffer staged one round earlier (made visible by that barrier).
+    int round = 0, nacc = 0;
+    for (int s0 = 0; s0 < P; s0 += KA_THREADS, ++round) {
+        const int buf = round & 1;
+        const int n = min(KA_THREADS, P - s0);
+        __syncthreads();
+        if (tid < n) stage(buf, tid, base + s0 + tid, nullptr);
+        if (tid == 0) sm.cnt[buf] = n;
+        nacc += n;
+        if (round > 0) chain(buf ^ 1);
+    }
+    const int B = p.box, ncand = B * B * P;
+    for (int c0 = 0; c0 < ncand; c0 += KA_THREADS, ++round) {
+        const int buf = round & 1;
+        const int t = c0 + tid;
+        bool accept = false, centre = false, inb = false;
+        uint32_t g = 0;
+        float fv[NF];
+        if (t < ncand) {
+            inb = candidate_sample(t, px, py, B, P, W, H, g, centre);
+            if (inb && !centre) {
+#pragma unroll
+                for (int k = 0; k < NF; ++k) fv[k] = __ldg(p.f.planes + static_cast<size_t>(CH_FEAT + k) * S + g);
+                accept = true;
+#pragma unroll
+                for (int k = 0; k < NF; ++k) {
+                    // allLessThan(|f - mu|, 3 sigma): reject on >= ; a NaN sigma accepts (ops.h:100-107)
+                    const double d = fabs(__dsub_rn(static_cast<double>(fv[k]), sm.mu[k]));
+                    if (d >= sm.sd3[k]) accept = false;
+                }
+            }
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, accept);
+        const unsigned mc = __ballot_sync(0xffffffffu, inb && centre);
+        if (lane == 0) {
+            sm.wcnt[buf][warp] = __popc(m);
+            if ((c0 >> 5) + warp < p.pl.mw) mask[(c0 >> 5) + warp] = m | mc;  // own samples count as members for KB / KC
+        }
+        __syncthreads();
+        int off = 0, tot = 0;
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+            const int c = sm.wcnt[buf][w];
+            if (w < warp) off += c;
+            tot += c;
+        }
+        if (accept) stage(buf, off + __popc(m & ((1u << lane) - 1u)), g, fv);
+        if (tid == 0) sm.cnt[buf] = tot;
+        nacc += tot;
+        chain(buf ^ 1);  // the round staged before this one (visible since the barrier above)
+    }
+    // zero the mask tail (mw is rounded up)
+    for (int w = ((ncand + KA_THREADS - 1) / KA_THREADS) * 4 + tid; w < p.pl.mw; w += KA_THREADS) mask[w] = 0u;
+    __syncthreads();
+    chain((round - 1) & 1);
+
+    // min / max over the CTA
+#pragma unroll
+    for (int s = 0; s < 16; ++s) {
+        const float a = warp_min_f(mn[s]), b = warp_max_f(mx[s]);
+        if (lane == 0) { sm.redf[warp][s] = a; sm.redf[warp][16 + s] = b; }
+    }
+#pragma unroll
+    for (int k = 0; k < NC; ++k) {
+        const double a = warp_min(cmn[k]), b = warp_max(cmx[k]);
+        if (lane == 0) { sm.redd[warp][k] = a; sm.redd[warp][NC + k] = b; }
+    }
+    __syncthreads();
+    const int N = nacc;
+    double *rec = p.rec + static_cast<size_t>(pl) * REC_DOUBLES;
+    if (tid < NCH) {
+        const int c = tid;
+        const double n = static_cast<double>(N);
+        const double m = __ddiv_rn(acc, n);
+        double var = __dsub_rn(__ddiv_rn(sq, n), __dmul_rn(m, m));
+        if ((p.flags & FLAG_P3) && !(var > 0.0) && var == var) var = 0.0;  // P3: sqrt(max(0,var)), NaN kept
+        double lo, hi;
+        if (c >= CH_COL && c < CH_COL + NC) {
+            const int k = c - CH_COL;
+            lo = fmin(fmin(sm.redd[0][k], sm.redd[1][k]), fmin(sm.redd[2][k], sm.redd[3][k]));
+            hi = fmax(fmax(sm.redd[0][NC + k], sm.redd[1][NC + k]), fmax(sm.redd[2][NC + k], sm.redd[3][NC + k]));
+        } else {
+            const int s = channel_slot(c);
+            lo = fminf(fminf(sm.redf[0][s], sm.redf[1][s]), fminf(sm.redf[2][s], sm.redf[3][s]));
+            hi = fmaxf(fmaxf(sm.redf[0][16 + s], sm.redf[1][16 + s]), fmaxf(sm.redf[2][16 + s], sm.redf[3][16 + s]));
+        }
+        rec[REC_M + c] = m;
+        rec[REC_SD + c] = __dsqrt_rn(var);
+        rec[REC_RLO + c] = lo;
+        rec[REC_RHI + c] = hi;
+    }
+    if (tid == 32) {
+        rec[REC_N] = static_cast<double>(N);
+        atomicAdd(&p.counters[0], static_cast<unsigned long long>(N));
+        atomicMin(&p.counters[2], static_cast<unsigned long long>(N));
+        atomicMax(&p.counters[3], static_cast<unsigned long long>(N));
+    }
+}
+
+// =====================================================================================================
+// shared helpers for KB / KC
+
+// Exclusive prefix of one int per thread over a CTA of NT threads; returns the prefix, total in *total.
+template <int NT>
+__device__ __forceinline__ int block_exclusive_scan(int v, int *wsum /* [NT/32 + 1] shared */, int *total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int u = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += u;
+    }
+    if (lane == 31) wsum[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        int w = lane < NT / 32 ? wsum[lane] : 0, winc = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int u = __shfl_up_sync(0xffffffffu, winc, o);
+            if (lane >= o) winc += u;
+        }
+        if (lane < NT / 32) wsum[lane] = winc - w;
+        if (lane == 31) wsum[NT / 32] = winc;
+    }
+    __syncthreads();
+    *total = wsum[NT / 32];
+    const int r = wsum[warp] + inc - v;
+    __syncthreads();  // wsum may be reused right away
+    return r;
+}
+
+struct KBSmall {
+    double M[NCH], SD[NCH], lo[NCH], hi[NCH], rlo[NCH], rhi[NCH], rsd[NCH], rr[NCH];
+    int flat[NCH], ordered[NCH];
+    unsigned long long Sm[NCH];  // sum n ln n of each marginal (fixed point)
+    unsigned long long red[KB_THREADS / 32][4];
+    double redd[KB_THREADS / 32];
+    double mi[N_JOINT];
+    double alpha[NC], beta[NF], wrc;
+    double wrf[NF], dcf[NF], dsum[9], wrck[NC];
+    int wsum[KB_THREADS / 32 + 1];
+    int N, nb, Q, redo[4];
+    unsigned int pixel;
+};
+
+// mi.cpp:14-16 on top of sd.h:224-235: bin of raw value x of channel c. A reciprocal-multiply estimate decides
+// unless it lands within 1e-9 of an integer; then the reference's exact divisions run (see rpf_pixel_kernel.cuh).
+__device__ __forceinline__ int bin_value(double x, int c, const KBSmall &ks, int nb, double dnb) {
+    if (ks.flat[c]) return 0;
+    const bool ordered = ks.ordered[c];
+    if (ordered && x == ks.rlo[c]) return 0;
+    if (ordered && x == ks.rhi[c]) return nb - 1;
+    const double te = ((x - ks.M[c]) * ks.rsd[c] - ks.lo[c]) * ks.rr[c];
+    const double r = rint(te);
+    int b;
+    if (ordered && fabs(te - r) > 1e-9 * (fabs(te) + 1.0)) {
+        b = static_cast<int>(te);
+    } else {
+        const double z = normalise(x, ks.M[c], ks.SD[c]);
+        b = __double2int_rz(__dmul_rn(__ddiv_rn(__dsub_rn(z, ks.lo[c]), __dsub_rn(ks.hi[c], ks.lo[c])), dnb));
+    }
+    return max(min(b, nb - 1), 0);
+}
+
+// rpf.cpp:416-487 from the 96 mutual informations (same code path as phase 6 of the fused kernel)
+__device__ __forceinline__ void cf_weights_from_mi(KBSmall &ks, int flags, int tid) {
+    const bool p2 = flags & FLAG_P2;
+    auto ratio = [&](double num, double den) { return (p2 && den == 0.0) ? 0.0 : num / den; };
+    if (tid < NF) {
+        const int i = tid;
+        const double drf = (0.0 + ks.mi[4 * i]) + ks.mi[4 * i + 1];          // rpf.cpp:421
+        const double dpf = (0.0 + ks.mi[4 * i + 2]) + ks.mi[4 * i + 3];      // rpf.cpp:425
+        ks.wrf[i] = ratio(drf, drf + dpf);                                   // rpf.cpp:465
+        ks.dcf[i] = ((0.0 + ks.mi[52 + i]) + ks.mi[68 + i]) + ks.mi[84 + i]; // P1: sum over colours of MI(c_i, f_j)
+    } else if (tid >= 32 && tid < 32 + NC) {
+        const int i = tid - 32, t = 48 + 16 * i;
+        const double drc = (0.0 + ks.mi[t]) + ks.mi[t + 1];                  // rpf.cpp:432
+        const double dpc = (0.0 + ks.mi[t + 2]) + ks.mi[t + 3];              // rpf.cpp:436
+        double dfc = 0.0;
+        for (int j = 0; j < NF; ++j) dfc += ks.mi[t + 4 + j];                // rpf.cpp:440
+        ks.dsum[i] = dfc;
+        ks.dsum[3 + i] = drc;
+        ks.dsum[6 + i] = dpc;
+        const double w = ratio(drc, drc + dpc);                              // rpf.cpp:470
+        ks.wrck[i] = w;
+        ks.alpha[i] = 1.0 - w;                                               // rpf.cpp:475
+    }
+    __syncthreads();
+    if (tid < NF) {
+        const int i = tid;
+        const double Dfc = ((0.0 + ks.dsum[0]) + ks.dsum[1]) + ks.dsum[2];   // rpf.cpp:449-456
+        const double Drc = ((0.0 + ks.dsum[3]) + ks.dsum[4]) + ks.dsum[5];
+        const double Dpc = ((0.0 + ks.dsum[6]) + ks.dsum[7]) + ks.dsum[8];
+        const double num = (flags & FLAG_P1) ? ks.dcf[i] : (i < NC ? ks.dsum[i] : __longlong_as_double(0x7ff8000000000000ll));
+        ks.beta[i] = (1.0 - ks.wrf[i]) * ratio(num, Dfc + Drc + Dpc);        // rpf.cpp:464,479
+    } else if (tid == 32) {
+        ks.wrc = (((0.0 + ks.wrck[0]) + ks.wrck[1]) + ks.wrck[2]) / NC;      // rpf.cpp:483-487
+    }
+    __syncthreads();
+}
+
+// The 24 pair groups: one row channel a against four column channels. Group g < 12: feature g against
+// {r0, r1, p0, p1}; g >= 12: colour (g-12)/4 against quarter (g-12)%4 of {r0, r1, p0, p1, f0..f11}.
+// Task index (rpf_common.cuh task_channels) of member j: t0 + j.
+__device__ __forceinline__ void group_channels(int g, int &a, int &t0) {
+    if (g < 12) { a = CH_FEAT + g; t0 = 4 * g; }
+    else { const int u = g - 12; a = CH_COL + (u >> 2); t0 = 48 + 16 * (u >> 2) + 4 * (u & 3); }
+}
+
+// =====================================================================================================
+// KB: bins + joint histograms + MI + alpha/beta. Persistent CTAs of 512 threads.
+__global__ void __launch_bounds__(KB_THREADS, 1) dependency_kernel(const GeneralParams p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ KBSmall ks;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int W = p.f.W, H = p.f.H, P = p.f.P, B = p.box;
+    const size_t S = p.f.S;
+    const GeneralPlan &L = p.pl;
+    unsigned long long *gsm = reinterpret_cast<unsigned long long *>(smem + L.off_gsm);
+    unsigned *marg = reinterpret_cast<unsigned *>(smem + L.off_marg);  // [19][nbs]
+    unsigned *region = reinterpret_cast<unsigned *>(smem + L.off_region);
+    unsigned short *idx16 = reinterpret_cast<unsigned short *>(region);
+    uint32_t *bins = L.bins_in_smem ? reinterpret_cast<uint32_t *>(smem + L.off_bins)
+                                    : reinterpret_cast<uint32_t *>(p.bins_scratch + static_cast<size_t>(blockIdx.x) * NCH * L.nq * 4);
+    const int nq = L.nq, G = L.G, hw = L.hw;
+    const int npix = p.nrows * W;
+
+    for (int k = tid; k < KB_GSM; k += KB_THREADS) gsm[k] = p.gq[k];
+
+    for (;;) {
+        __syncthreads();
+        if (tid == 0) ks.pixel = atomicAdd(p.work_counter, 1u);
+        __syncthreads();
+        const int pl = static_cast<int>(ks.pixel);
+        if (pl >= npix) break;
+        const int py = p.row0 + pl / W, px = pl - (pl / W) * W;
+        const size_t pix = static_cast<size_t>(py) * W + px;
+        const uint32_t *mask = p.mask + static_cast<size_t>(pl) * L.mw;
+        double *rec = p.rec + static_cast<size_t>(pl) * REC_DOUBLES;
+
+        // ---- per-channel constants --------------------------------------------------------------------
+        if (tid == 0) {
+            const int N = static_cast<int>(rec[REC_N]);
+            int nb = static_cast<int>(__dsqrt_rn(static_cast<double>(N)));  // mi.cpp:53-58
+            if (nb < 1) nb = 1;
+            ks.N = N;
+            ks.nb = nb;
+            // slot -> sample permutation step: adjacent slots hold samples far apart in enumeration order, so the lanes
+            // of a warp rarely hit one histogram cell together even for smooth channels
+            int q = static_cast<int>(0.6180339887 * N) | 1;
+            if (q >= N) q = 1;
+            for (;; q += 2) {
+                int a = q, b = N;
+                while (b) { const int r = a % b; a = b; b = r; }
+                if (a == 1) break;
+            }
+            ks.Q = N > 1 ? q % N : 0;
+            if (N > 1 && ks.Q == 0) ks.Q = 1;
+        }
+        __syncthreads();
+        const int N = ks.N, nb = ks.nb;
+        const double dnb = static_cast<double>(nb), dn = static_cast<double>(N);
+        if (tid < NCH) {
+            const int c = tid;
+            const double m = rec[REC_M + c], sd = rec[REC_SD + c], rlo = rec[REC_RLO + c], rhi = rec[REC_RHI + c];
+            // (x-M)/SD is monotone in x, so the extremes of the normalised channel are the normalised extremes
+            const double lo = normalise(rlo, m, sd), hi = normalise(rhi, m, sd);
+            ks.M[c] = m; ks.SD[c] = sd; ks.rlo[c] = rlo; ks.rhi[c] = rhi; ks.lo[c] = lo; ks.hi[c] = hi;
+            ks.flat[c] = hi == lo;
+            ks.ordered[c] = hi > lo;  // false when sigma is NaN: everything takes the exact path
+            ks.rsd[c] = 1.0 / sd;
+            ks.rr[c] = dnb / (hi - lo);
+        }
+        for (int k = tid; k < NCH * L.nbs; k += KB_THREADS) marg[k] = 0u;
+
+        // ---- accepted candidates -> idx16 (candidate numbers, any order) ---------------------------------
+        {
+            const int wpt = (L.mw + KB_THREADS - 1) / KB_THREADS;
+            const int w0 = tid * wpt;
+            int cnt = 0;
+            for (int w = w0; w < min(w0 + wpt, L.mw); ++w) cnt += __popc(mask[w]);
+            int total;
+            int off = block_exclusive_scan<KB_THREADS>(cnt, ks.wsum, &total);
+            for (int w = w0; w < min(w0 + wpt, L.mw); ++w) {
+                unsigned bits = mask[w];
+                while (bits) {
+                    const int b = __ffs(bits) - 1;
+                    bits &= bits - 1;
+                    idx16[off++] = static_cast<unsigned short>(w * 32 + b);
+                }
+            }
+        }
+        __syncthreads();
+
+        // ---- normalise + bin: four slots per thread, packed u8 bins, marginal counts ----------------------
+        {
+            const unsigned Q = static_cast<unsigned>(ks.Q), uN = static_cast<unsigned>(N);
+            const int nqn = (N + 3) >> 2;
+            for (int q = tid; q < nqn; q += KB_THREADS) {
+                uint32_t pack[NCH];
+#pragma unroll
+                for (int c = 0; c < NCH; ++c) pack[c] = 0u;
+#pragma unroll 1
+                for (int k = 0; k < 4; ++k) {
+                    const unsigned m = 4u * q + k;
+                    if (m < uN) {
+                        const int t = idx16[(m * Q) % uN];
+                        uint32_t g;
+                        bool centre;
+                        candidate_sample(t, px, py, B, P, W, H, g, centre);
+#pragma unroll
+                        for (int c = 0; c < NCH; ++c) {
+                            const bool isc = c >= CH_COL && c < CH_COL + NC;
+                            const double x = isc ? p.col_in[static_cast<size_t>(c - CH_COL) * S + g]
+                                                 : static_cast<double>(__ldg(p.f.planes + static_cast<size_t>(c) * S + g));
+                            const int b = bin_value(x, c, ks, nb, dnb);
+                            pack[c] |= static_cast<uint32_t>(b) << (8 * k);
+                            atomicAdd(&marg[c * L.nbs + b], 1u);
+                        }
+                    }
+                }
+#pragma unroll
+                for (int c = 0; c < NCH; ++c) bins[c * nq + q] = pack[c];
+            }
+        }
+        __syncthreads();
+
+        // ---- marginals: S_c = sum_i n_i ln n_i; clear the histogram region (idx16 is dead now) ---------------
+        for (int c = warp; c < NCH; c += KB_THREADS / 32) {
+            unsigned long long s = 0ull;
+            for (int i = lane; i < nb; i += 32) s += p.hq[marg[c * L.nbs + i]];
+            s = warp_sum_u64(s);
+            if (lane == 0) ks.Sm[c] = s;
+        }
+        {
+            uint4 *r4 = reinterpret_cast<uint4 *>(region);
+            for (int k = tid; k < (G * hw) >> 2; k += KB_THREADS) r4[k] = make_uint4(0u, 0u, 0u, 0u);
+        }
+        __syncthreads();
+
+        // ---- 96 joint histograms, G at a time; sum n ln n accumulated incrementally ---------------------------
+        // Raising a cell from k to k+1 adds g[k] = (k+1)ln(k+1) - k ln k; the returning shared atomic supplies k.
+        // MI(a,b) = (S_ab - S_a - S_b + N ln N)/N  (equals mi.cpp:79-87 up to rounding), in exact integer arithmetic.
+        const unsigned long long Stot = p.hq[N];
+        const int nqn = (N + 3) >> 2;
+        for (int grp = 0; grp < 24; ++grp) {
+            int a, t0;
+            group_channels(grp, a, t0);
+            if (ks.flat[a]) {  // a constant channel has MI exactly 0 with everything (mi.cpp: every ratio is 1)
+                if (tid < 4) ks.mi[t0 + tid] = 0.0;
+                continue;
+            }
+            for (int sub = 0; sub < 4; sub += G) {
+                int bch[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) { int aa, bb; task_channels(t0 + sub + (j < G ? j : 0), aa, bb); bch[j] = bb; }
+                unsigned long long acc[4] = {0ull, 0ull, 0ull, 0ull};
+                const uint32_t *ba = bins + a * nq;
+                for (int q = tid; q < nqn; q += KB_THREADS) {
+                    const uint32_t wa = ba[q];
+                    uint32_t wb[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) if (j < G) wb[j] = bins[bch[j] * nq + q];
+                    const int valid = min(4, N - 4 * q);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        if (k < valid) {
+                            const unsigned ca = ((wa >> (8 * k)) & 255u) * nb;
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                if (j < G) {
+                                    const unsigned cell = ca + ((wb[j] >> (8 * k)) & 255u);
+                                    const unsigned old = atomicAdd(&region[j * hw + (cell >> 1)], (cell & 1u) ? 0x10000u : 1u);
+                                    const unsigned cnt = (cell & 1u) ? (old >> 16) : (old & 0xffffu);
+                                    acc[j] += cnt < KB_GSM ? gsm[cnt] : p.gq[cnt];
+                                }
+                            }
+                        }
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    if (j < G) {
+                        const unsigned long long s = warp_sum_u64(acc[j]);
+                        if (lane == 0) ks.red[warp][j] = s;
+                    }
+                }
+                __syncthreads();
+                if (tid < G) {
+                    unsigned long long s = 0ull;
+                    for (int w = 0; w < KB_THREADS / 32; ++w) s += ks.red[w][tid];
+                    int aa, b;
+                    task_channels(t0 + sub + tid, aa, b);
+                    double mi = 0.0;
+                    int redo = 0;
+                    if (!ks.flat[b]) {
+                        const long long num = static_cast<long long>((s + Stot) - (ks.Sm[a] + ks.Sm[b]));
+                        mi = static_cast<double>(num) * (1.0 / 8796093022208.0) / dn;  // 2^-43
+                        // Exactly independent tables give exactly 0 in mi.cpp (every ratio is 1.0) but rounding noise here;
+                        // the P2 guards branch on such zeros, so suspiciously small values are recomputed cell by cell.
+                        redo = mi != 0.0 && fabs(mi) < 1e-4 / (dn * dn);
+                    }
+                    ks.mi[t0 + sub + tid] = mi;
+                    ks.redo[tid] = redo;
+                }
+                __syncthreads();
+                for (int j = 0; j < G; ++j) {
+                    if (!ks.redo[j]) continue;  // block-uniform
+                    const int b = bch[j];
+                    double s = 0.0;
+                    for (int cell = tid; cell < nb * nb; cell += KB_THREADS) {
+                        const unsigned wv = region[j * hw + (cell >> 1)];
+                        const unsigned n = (cell & 1) ? (wv >> 16) : (wv & 0xffffu);
+                        if (n == 0) continue;
+                        const int i = cell / nb, jj = cell - i * nb;
+                        const double pxv = __ddiv_rn(static_cast<double>(marg[a * L.nbs + i]), dn);
+                        const double pyv = __ddiv_rn(static_cast<double>(marg[b * L.nbs + jj]), dn);
+                        const double pxy = __ddiv_rn(static_cast<double>(n), dn);
+                        const double pp = __dmul_rn(pxv, pyv);
+                        if (pp != 0.0) s = __dadd_rn(s, __dmul_rn(pxy, log(__ddiv_rn(pxy, pp))));
+                    }
+                    s = warp_sum(s);
+                    __syncthreads();
+                    if (lane == 0) ks.redd[warp] = s;
+                    __syncthreads();
+                    if (tid == 0) {
+                        double r = 0.0;
+                        for (int w = 0; w < KB_THREADS / 32; ++w) r += ks.redd[w];
+                        ks.mi[t0 + sub + j] = r;
+                    }
+                }
+                {
+                    uint4 *r4 = reinterpret_cast<uint4 *>(region);
+                    for (int k = tid; k < (G * hw) >> 2; k += KB_THREADS) r4[k] = make_uint4(0u, 0u, 0u, 0u);
+                }
+                __syncthreads();
+            }
+        }
+        __syncthreads();
+
+        // ---- dependencies -> alpha, beta, W_r_c (rpf.cpp:416-487) ------------------------------------------
+        cf_weights_from_mi(ks, p.flags, tid);
+        if (tid < NC) rec[REC_ALPHA + tid] = ks.alpha[tid];
+        if (tid < NF) rec[REC_BETA + tid] = ks.beta[tid];
+        if (tid == 0) rec[REC_WRC] = ks.wrc;
+        if (p.dbg_n) {
+            if (tid == 0) { p.dbg_n[pix] = N; p.dbg_wrc[pix] = ks.wrc; }
+            if (tid < NC) p.dbg_alpha[pix * NC + tid] = ks.alpha[tid];
+            if (tid < NF) p.dbg_beta[pix * NF + tid] = ks.beta[tid];
+        }
+    }
+}
+
+// =====================================================================================================
+// KC: cross-bilateral weights and blend (rpf.cpp:627-717). One CTA of 128 threads per pixel.
+// w_ij = exp(-sum_p d^2/(2 sp2)) * exp(-sum_c alpha d^2/(2 s2)) * exp(-sum_f beta d^2/(2 s2)) on NORMALISED values;
+// the three exponents are summed and each channel is pre-scaled by sqrt(coefficient)/sigma. Every term is >= 0, so
+// once the running exponent passes 745.2 the weight is exactly 0 (exp underflows) and the rest is skipped.
+struct KCSmall {
+    double scl[NWZ], mz[NWZ];
+    double red[4][KC_IC * 4];
+    int wsum[KC_THREADS / 32 + 1];
+};
+
+__global__ void __launch_bounds__(KC_THREADS, 4) blend_kernel(const GeneralParams p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ KCSmall ks;
+    __shared__ unsigned short segidx[KC_SEG_WORDS * 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int W = p.f.W, H = p.f.H, P = p.f.P, B = p.box;
+    const size_t S = p.f.S;
+    const int pl = blockIdx.x;
+    const int py = p.row0 + pl / W, px = pl - (pl / W) * W;
+    const size_t pix = static_cast<size_t>(py) * W + px;
+    const uint32_t base = static_cast<uint32_t>(pix * P);
+    const uint32_t *mask = p.mask + static_cast<size_t>(pl) * p.pl.mw;
+    const double *rec = p.rec + static_cast<size_t>(pl) * REC_DOUBLES;
+    double *zi = reinterpret_cast<double *>(smem);  // [P][18]: order colour(3), features(12), position(2), pad
+
+    // channel order inside z: k = 0..2 colour, 3..14 features, 15..16 position (most selective first)
+    if (tid < NWZ) {
+        const int k = tid;
+        const int c = k < 3 ? CH_COL + k : (k < 15 ? CH_FEAT + (k - 3) : CH_POS + (k - 15));
+        const double wrc = rec[REC_WRC];
+        const double sigma_p = static_cast<double>(B / 4);                       // rpf.cpp:531 integer division
+        const double s2 = p.seed * p.seed / (1.0 - wrc) / (1.0 - wrc);           // rpf.cpp:662
+        double coef;
+        if (k < 3) coef = rec[REC_ALPHA + k] / (2.0 * s2);
+        else if (k < 15) coef = rec[REC_BETA + (k - 3)] / (2.0 * s2);
+        else coef = 1.0 / (2.0 * (sigma_p * sigma_p));
+        const double sd = rec[REC_SD + c];
+        ks.scl[k] = sd == 0.0 ? 0.0 : sqrt(coef) / sd;
+        ks.mz[k] = rec[REC_M + c];
+    }
+    __syncthreads();
+    auto load_z = [&](uint32_t g, double *z, double *col) {
+#pragma unroll
+        for (int k = 0; k < NWZ; ++k) {
+            double x;
+            if (k < 3) {
+                x = p.col_in[static_cast<size_t>(k) * S + g];
+                col[k] = x;
+            } else {
+                const int c = k < 15 ? CH_FEAT + (k - 3) : CH_POS + (k - 15);
+                x = static_cast<double>(__ldg(p.f.planes + static_cast<size_t>(c) * S + g));
+            }
+            z[k] = (x - ks.mz[k]) * ks.scl[k];
+        }
+    };
+    for (int n = tid; n < P; n += KC_THREADS) {
+        double z[NWZ], col[NC];
+        load_z(base + n, z, col);
+#pragma unroll
+        for (int k = 0; k < NWZ; ++k) zi[n * 18 + k] = z[k];
+        zi[n * 18 + 17] = 0.0;
+    }
+    __syncthreads();
+
+    const int nseg = (p.pl.mw + KC_SEG_WORDS - 1) / KC_SEG_WORDS;
+    for (int i0 = 0; i0 < P; i0 += KC_IC) {
+        double sw[KC_IC], swc[KC_IC][NC];
+#pragma unroll
+        for (int ii = 0; ii < KC_IC; ++ii) { sw[ii] = 0.0; swc[ii][0] = swc[ii][1] = swc[ii][2] = 0.0; }
+        for (int seg = 0; seg < nseg; ++seg) {
+            const int w = seg * KC_SEG_WORDS + tid;
+            unsigned bits = w < p.pl.mw ? mask[w] : 0u;
+            int total;
+            int off = block_exclusive_scan<KC_THREADS>(__popc(bits), ks.wsum, &total);
+            while (bits) {
+                const int b = __ffs(bits) - 1;
+                bits &= bits - 1;
+                segidx[off++] = static_cast<unsigned short>(tid * 32 + b);
+            }
+            __syncthreads();
+            for (int n = tid; n < total; n += KC_THREADS) {
+                const int t = seg * (KC_SEG_WORDS * 32) + segidx[n];
+                uint32_t g;
+                bool centre;
+                candidate_sample(t, px, py, B, P, W, H, g, centre);
+                double zj[NWZ], cj[NC];
+                load_z(g, zj, cj);
+#pragma unroll
+                for (int ii = 0; ii < KC_IC; ++ii) {
+                    if (i0 + ii < P) {
+                        const double *zr = zi + (i0 + ii) * 18;
+                        double arg = 0.0;
+#pragma unroll
+                        for (int k = 0; k < 3; ++k) {
+                            const double d = zr[k] - zj[k];
+                            arg = fma(d, d, arg);
+                        }
+                        if (!(arg > 745.2)) {  // NaN falls through to exp
+#pragma unroll
+                            for (int k = 3; k < NWZ; ++k) {
+                                const double d = zr[k] - zj[k];
+                                arg = fma(d, d, arg);
+                            }
+                            const double wgt = arg > 745.2 ? 0.0 : exp(-arg);
+                            sw[ii] += wgt;
+                            swc[ii][0] = fma(wgt, cj[0], swc[ii][0]);
+                            swc[ii][1] = fma(wgt, cj[1], swc[ii][1]);
+                            swc[ii][2] = fma(wgt, cj[2], swc[ii][2]);
+                        }
+                    }
+                }
+            }
+            __syncthreads();
+        }
+#pragma unroll
+        for (int ii = 0; ii < KC_IC; ++ii) {
+            const double a = warp_sum(sw[ii]), b0 = warp_sum(swc[ii][0]), b1 = warp_sum(swc[ii][1]), b2 = warp_sum(swc[ii][2]);
+            if (lane == 0) {
+                ks.red[warp][ii * 4 + 0] = a;
+                ks.red[warp][ii * 4 + 1] = b0;
+                ks.red[warp][ii * 4 + 2] = b1;
+                ks.red[warp][ii * 4 + 3] = b2;
+            }
+        }
+        __syncthreads();
+        if (tid < KC_IC * NC) {
+            const int ii = tid / NC, k = tid - ii * NC;
+            if (i0 + ii < P) {
+                const double a = ((ks.red[0][ii * 4] + ks.red[1][ii * 4]) + ks.red[2][ii * 4]) + ks.red[3][ii * 4];
+                const double b = ((ks.red[0][ii * 4 + 1 + k] + ks.red[1][ii * 4 + 1 + k]) + ks.red[2][ii * 4 + 1 + k]) +
+                                 ks.red[3][ii * 4 + 1 + k];
+                const double c = b / a;  // rpf.cpp:700
+                if (c != c) atomicAdd(&p.counters[1], 1ull);  // P4: count, never exit (rpf.cpp:702-705)
+                p.col_out[static_cast<size_t>(k) * S + base + i0 + ii] = c;
+            }
+        }
+        __syncthreads();
+    }
+}
+
+}  // namespace rpf

@@ -15,9 +15,9 @@ TOL_RELMSE = 1e-5   # north_star
 TOL_TIGHT = 1e-9    # what the FP64 kernels actually deliver
 
 
-def _gpu(planes, W, H, P, boxes, seed, flags=7, colors=None):
+def _gpu(planes, W, H, P, boxes, seed, flags=7, colors=None, general=False):
     import rpf_b200
-    f = rpf_b200.RPFFilter(W, H, P, flags=flags, debug=True)
+    f = rpf_b200.RPFFilter(W, H, P, flags=flags, debug=True, force_general=general)
     f.upload(planes)
     if colors is not None:
         f.upload_colors_f64(colors)
@@ -49,27 +49,75 @@ def _compare(g, o, W, H, P):
     assert g["stats"]["nan_channels"] == o["nan_count"]
 
 
+PATHS = pytest.mark.parametrize("general", [False, True], ids=["fused", "general"])
+
+
+@PATHS
 @pytest.mark.parametrize("seed", [0.002, 0.2, 2.0])
 @pytest.mark.parametrize("kind", [0, 1])
-def test_box7_matches_oracle(seed, kind):
+def test_box7_matches_oracle(seed, kind, general):
     import rpf_b200
     W, H, P = 40, 28, 8
     planes = rpf_b200.synth_planes(W, H, P, seed=1234, kind=kind)
     o = ob.oracle_filter(planes, W, H, P, [7], seed=seed, debug=True)
-    g = _gpu(planes, W, H, P, [7], seed)
+    g = _gpu(planes, W, H, P, [7], seed, general=general)
     _compare(g, o, W, H, P)
     if kind == 0 and seed > 0.1:
         assert np.abs(g["colors"] - planes[2:5]).max() > 1e-2  # the filter is not the identity here
 
 
+@PATHS
 @pytest.mark.parametrize("boxes,P", [([3], 8), ([5], 4), ([9, 7, 5], 8), ([7], 16), ([7, 7], 3), ([11], 1)])
-def test_box_and_spp_variants(boxes, P):
+def test_box_and_spp_variants(boxes, P, general):
     import rpf_b200
     W, H = 24, 20
     planes = rpf_b200.synth_planes(W, H, P, seed=7, kind=0)
     o = ob.oracle_filter(planes, W, H, P, boxes, seed=0.5, debug=True)
-    g = _gpu(planes, W, H, P, boxes, 0.5)
+    g = _gpu(planes, W, H, P, boxes, 0.5, general=general)
     _compare(g, o, W, H, P)
+
+
+# Large neighbourhoods (general path). What each case exercises in the dependency kernel's plan (rpf_api.cu plan_general):
+#   box 17 x 8 spp   N <= 2312   bins in shared memory, 4 histograms at a time
+#   box 35 x 8 spp   ncap 9800   bins in the L2-resident scratch, 4 histograms
+#   box 57 x 8 spp   ncap 25992  2 histograms at a time
+#   box 41 x 32 spp  ncap 53792  1 histogram at a time
+#   box 13 x 64 spp  ncap 10816  64 own samples per pixel (8 blend passes)
+@pytest.mark.parametrize("W,H,P,boxes,seed,kind", [
+    (40, 36, 8, [17], 0.5, 0),
+    (36, 30, 8, [17, 7], 0.02, 1),
+    (24, 20, 8, [35], 1.0, 0),
+    (24, 20, 8, [57, 35], 0.5, 0),
+    (20, 16, 32, [41], 0.5, 0),
+    (14, 12, 64, [13], 0.2, 0),
+    (30, 26, 16, [21, 9], 2.0, 0),
+])
+def test_large_neighbourhoods(W, H, P, boxes, seed, kind):
+    import rpf_b200
+    planes = rpf_b200.synth_planes(W, H, P, seed=31, kind=kind)
+    o = ob.oracle_filter(planes, W, H, P, boxes, seed=seed, debug=True)
+    g = _gpu(planes, W, H, P, boxes, seed)
+    _compare(g, o, W, H, P)
+
+
+def test_box55_full_neighbourhood():
+    """north_star's largest box at 8 spp on a frame big enough that interior pixels see all 24,200 candidates."""
+    import rpf_b200
+    W, H, P = 60, 58, 8
+    planes = rpf_b200.synth_planes(W, H, P, seed=55, kind=0)
+    o = ob.oracle_filter(planes, W, H, P, [55], seed=0.5, debug=True)
+    g = _gpu(planes, W, H, P, [55], 0.5)
+    assert g["N"].max() > 5000
+    _compare(g, o, W, H, P)
+
+
+def test_unsupported_neighbourhood_is_an_error():
+    import rpf_b200
+    f = rpf_b200.RPFFilter(8, 8, 64)
+    f.upload(rpf_b200.synth_planes(8, 8, 64, seed=1, kind=0))
+    with pytest.raises(rpf_b200.RPFError, match="exceeds this build"):
+        f.apply([35], 0.5)   # 35*35*64 = 78,400 candidates > 65,535
+    f.close()
 
 
 def test_verbatim_flags_match_reference_semantics():
@@ -85,21 +133,23 @@ def test_verbatim_flags_match_reference_semantics():
     assert np.isnan(g["beta"][:, 3:]).all()
 
 
-def test_tiny_and_ragged_frames():
+@PATHS
+def test_tiny_and_ragged_frames(general):
     import rpf_b200
-    for (W, H, P) in [(1, 1, 8), (2, 9, 8), (7, 3, 5)]:
+    for (W, H, P) in [(1, 1, 8), (2, 9, 8), (7, 3, 5), (1, 1, 1), (3, 2, 200)]:
         planes = rpf_b200.synth_planes(W, H, P, seed=11, kind=0)
         o = ob.oracle_filter(planes, W, H, P, [7], seed=1.0, debug=True)
-        g = _gpu(planes, W, H, P, [7], 1.0)
+        g = _gpu(planes, W, H, P, [7], 1.0, general=general)
         _compare(g, o, W, H, P)
 
 
-def test_row_band_equals_full_frame():
+@PATHS
+def test_row_band_equals_full_frame(general):
     """filter_rows over two bands (what two ranks would do) equals one full-frame pass."""
     import rpf_b200
     W, H, P = 32, 24, 8
     planes = rpf_b200.synth_planes(W, H, P, seed=5, kind=0)
-    f = rpf_b200.RPFFilter(W, H, P)
+    f = rpf_b200.RPFFilter(W, H, P, force_general=general)
     f.upload(planes)
     f.apply([7], 0.5)
     full = f.download_colors_f64()
