@@ -4,9 +4,11 @@
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
   N>1: python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
-A step is one rpf_filter pass schedule (all configured box sizes) over one synthetic frame. Row bands are sharded
-across ranks with halo exchange of the filtered colours between passes (NCCL point-to-point); total work is fixed
-as N grows ("strong" scaling of one frame). Prints ONE JSON line on rank 0.
+A step is one rpf_filter pass schedule (all configured box sizes) over one synthetic frame. The default workload is
+BASELINE.json configs[1]: 1280x720, 8 spp, four RPF iterations with the box sizes 55/35/17/7 of north_star (the
+reference ships {7} and keeps {55,35,17,7} in a comment, rpf.cpp:767; `--boxes 7` times the shipped schedule).
+Row bands are sharded across ranks with halo exchange of the filtered colours between passes (NCCL point-to-point);
+total work is fixed as N grows ("strong" scaling of one frame). Prints ONE JSON line on rank 0.
 """
 import argparse
 import json
@@ -35,7 +37,7 @@ def parse():
     ap.add_argument("--width", type=int, default=1280)
     ap.add_argument("--height", type=int, default=720)
     ap.add_argument("--spp", type=int, default=8)
-    ap.add_argument("--boxes", default=os.environ.get("RPF_BENCH_BOXES", "7"))
+    ap.add_argument("--boxes", default=os.environ.get("RPF_BENCH_BOXES", "55,35,17,7"))
     ap.add_argument("--seed", type=float, default=0.002, help="sigma_fc_seed, reference literal rpf.cpp:533")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -78,10 +80,11 @@ class ClockSampler(threading.Thread):
                 "reasons": reasons, "samples": len(sm)}
 
 
-def crop_for_cpu(boxes, cores, W, H, target_s=15.0):
-    cost_px = 1.2e-3 * sum(b * b for b in boxes) / 49.0  # core-seconds per pixel (SURVEY.md section 6 probe)
-    side = int((target_s * cores / cost_px) ** 0.5) // 16 * 16
-    side = max(48, min(256, side))
+def crop_for_cpu(boxes, cores, W, H):
+    """Bounded CPU sample: a centre crop filtered as a frame of its own (about 10-30 s on 8-16 cores, measured:
+    80x80 with boxes 55/35/17/7 = 27 s on 8 cores, 256x256 with box 7 = 2.7 s on 16). Pixels near the crop's edge see
+    truncated boxes, as the border pixels of the full frame do, so the CPU figure is mildly optimistic."""
+    side = 80 if max(boxes) >= 17 else 256
     return min(side, W), min(side, H)
 
 
@@ -170,9 +173,7 @@ def main():
         def __init__(self, ptr):
             self.__cuda_array_interface__ = {"shape": (3, S_loc), "typestr": "<f8", "data": (ptr, False), "version": 2}
 
-    kernel_ms = []
-
-    def step(record=False):
+    def step():
         for i, b in enumerate(boxes):
             ctx.filter_rows(b, o0, o1, args.seed)
             if world > 1 and i + 1 < len(boxes):
@@ -180,10 +181,6 @@ def main():
                 nxt = torch.as_tensor(DevView(ctx.color_ptr(1)), device=f"cuda:{local_rank}")
                 bands.exchange_halos(dist, band, boxes[i + 1], nxt, row)
                 torch.cuda.synchronize()
-            elif record:
-                ctx.synchronize()
-            if record:
-                kernel_ms.append(ctx.stats()["last_filter_ms"])
             ctx.swap_colors()
 
     def barrier():
@@ -196,26 +193,29 @@ def main():
         step()
     barrier()
     ctx.reset_stats()
+    ctx.set_profiling(True)  # a CUDA event pair around every kernel launch, on the stream the kernels run on
     sampler = ClockSampler(local_rank)
     sampler.start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     stream = torch.cuda.ExternalStream(ctx.stream(), device=local_rank)
+    barrier()
     t0 = time.perf_counter()
     ev0.record(stream)
     for _ in range(args.steps):
-        step(record=True)
+        step()
     ev1.record(stream)
     barrier()
     wall = time.perf_counter() - t0
     sampler.stop_flag = True
     dev_s = ev0.elapsed_time(ev1) / 1e3
     st = ctx.stats()
+    ktimes = ctx.kernel_times()
+    ctx.set_profiling(False)
     t = torch.tensor([dev_s, wall], dtype=torch.float64, device=f"cuda:{local_rank}")
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     dev_s, wall = t.tolist()
     total_samples = W * H * P
-    # with per-launch stats reads the device-event bracket includes host gaps; both are reported, value uses the bracket
     value = total_samples * args.steps / dev_s / 1e6
 
     # e2e: host planes -> device, all passes, colours back to the host, every step (through the public C ABI)
@@ -239,24 +239,35 @@ def main():
                "h2d_bytes_per_step": 19 * S_loc * 4 * world, "d2h_bytes_per_step": 3 * S_loc * 4 * world}
 
     peak, peak_src = peaks()
-    k_ms = float(np.mean(kernel_ms)) if kernel_ms else None
     own_samples = W * (band.own1 - band.own0) * P
+    # dominant kernel = largest share of the timed region. Its algorithmic bytes: 88 B per sample per pass
+    # (19 fp32 channels read + 3 fp32 colours written) for every pass it takes part in; one launch covers a chunk of rows.
+    kern = {k: {"ms_total": ms, "launches": n, "share_of_step": ms / (dev_s * 1e3)} for k, (ms, n) in ktimes.items() if n}
+    dom = max(kern, key=lambda k: kern[k]["ms_total"]) if kern else None
     roof = None
-    if k_ms:
-        achieved = ALG_BYTES_PER_SAMPLE_ITER * own_samples / (k_ms * 1e-3) / 1e9
-        roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "peak_source": peak_src, "kernel": "rpf_pixel_kernel",
-                "kernel_ms_per_launch": k_ms, "launches_timed": len(kernel_ms),
-                "note": "path is bound by shared-memory read-modify-write and FP64 issue, not HBM (DESIGN.md)"}
+    if dom:
+        general = dom != "rpf_pixel_kernel"
+        passes = [b for b in boxes if (b * b * P > 1279) == general] if dom != "pixel_stats_kernel" else boxes[:1]
+        alg_bytes = ALG_BYTES_PER_SAMPLE_ITER * own_samples * len(passes) * args.steps
+        k_ms, k_n = kern[dom]["ms_total"], kern[dom]["launches"]
+        achieved = alg_bytes / (k_ms * 1e-3) / 1e9
+        upd = 96 * st["nbh_sum"]  # joint-histogram updates in the timed region: 96 MI pairs x N per pixel-pass
+        roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "peak_source": peak_src, "kernel": dom, "kernel_ms_per_launch": k_ms / k_n, "launches_timed": k_n,
+                "algorithmic_bytes_per_launch": alg_bytes / k_n,
+                "note": "the path is bound by shared-memory atomic / FP64 issue, not HBM (DESIGN.md section 4)",
+                "on_chip": {"bound": "shared_atomics", "achieved": upd / (dev_s) / 1e9, "peak": 2180.0,
+                            "unit": "G histogram updates/s", "frac": upd / dev_s / 1e9 / 2180.0,
+                            "peak_source": "profiles/micro/smem_micro.cu: random-address ATOMS, 1024 threads/SM, this pool's B200"}}
     res = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dev_s / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
         "config": {"workload": workload, "sharding": f"{world} row band(s), halo {band.own0 - band.buf0}/{band.buf1 - band.own1} rows",
-                   "l2": "inputs (0.9 GB per 1280x720x8 frame) exceed the 126 MB L2", "mean_neighbourhood":
+                   "l2": f"inputs ({19 * 4 * W * H * P / 1e9:.2f} GB of planes per frame) exceed the 126 MB L2", "mean_neighbourhood":
                        st["nbh_sum"] / max(1, st["pixels_filtered"])},
         "wall_ms_per_step": wall / args.steps * 1e3, "gpu_launches": st["kernel_launches"], "nan_channels": st["nan_channels"],
-        "clocks": sampler.summary(), "roofline": roof, "e2e": e2e,
+        "clocks": sampler.summary(), "roofline": roof, "kernels": kern, "e2e": e2e,
     }
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         res["cpu_baseline"], _ = cpu_reference_run(args, boxes, 1, 0)

@@ -110,6 +110,18 @@ int rpf_reconstruct_box(rpf_ctx *ctx, float *rgb);
 int rpf_get_stats(rpf_ctx *ctx, rpf_stats_t *out);
 int rpf_reset_stats(rpf_ctx *ctx);
 
+/* Per-kernel device time (the reference bills the whole filter to one pbrt profiler category).
+ * With profiling on, every kernel launch is bracketed by CUDA events on the context's stream; totals accumulate
+ * until rpf_reset_stats. Kernels: per-pixel feature statistics (rpf.cpp:302-353), the fused small-neighbourhood
+ * kernel, and the three kernels of the general path (membership + statistics, dependency estimation, blend). */
+enum { RPF_K_PIXEL_STATS = 0, RPF_K_FUSED = 1, RPF_K_NBH_STATS = 2, RPF_K_DEPENDENCY = 3, RPF_K_BLEND = 4, RPF_NUM_KERNELS = 5 };
+typedef struct rpf_kernel_times_t {
+    double ms[RPF_NUM_KERNELS];
+    long long launches[RPF_NUM_KERNELS];
+} rpf_kernel_times_t;
+int rpf_set_profiling(rpf_ctx *ctx, int on);
+int rpf_get_kernel_times(rpf_ctx *ctx, rpf_kernel_times_t *out);
+
 /* Largest neighbourhood (box*box*spp candidate samples) this build can filter, for error messages and tests. */
 int rpf_max_neighbourhood(void);
 

@@ -35,6 +35,13 @@ struct rpf_ctx {
     size_t mask_bytes = 0, rec_bytes = 0, bins_bytes = 0;
     int kb_static_smem = 0, num_sms = 0;
     bool force_general = false;
+    // optional per-kernel timing: an event pair around every launch, resolved at the next synchronising call
+    bool profiling = false;
+    struct Span { cudaEvent_t a, b; int k; };
+    std::vector<Span> spans;
+    std::vector<cudaEvent_t> free_events;
+    double k_ms[RPF_NUM_KERNELS] = {};
+    long long k_launches[RPF_NUM_KERNELS] = {};
     size_t scratch_budget = 2048ull << 20;
     unsigned long long *d_counters = nullptr;  // 4
     int *d_dbg_n = nullptr;
@@ -133,10 +140,38 @@ extern "C" void rpf_destroy(rpf_ctx *ctx) {
     cudaFree(ctx->d_dbg_alpha);
     cudaFree(ctx->d_dbg_beta);
     cudaFree(ctx->d_dbg_wrc);
+    for (auto &sp : ctx->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
+    for (auto e : ctx->free_events) cudaEventDestroy(e);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
+}
+
+static void prof_begin(rpf_ctx *ctx, int k) {
+    if (!ctx->profiling) return;
+    rpf_ctx::Span sp{nullptr, nullptr, k};
+    for (cudaEvent_t *e : {&sp.a, &sp.b}) {
+        if (!ctx->free_events.empty()) { *e = ctx->free_events.back(); ctx->free_events.pop_back(); }
+        else cudaEventCreate(e);
+    }
+    cudaEventRecord(sp.a, ctx->stream);
+    ctx->spans.push_back(sp);
+}
+static void prof_end(rpf_ctx *ctx) {
+    if (ctx->profiling) cudaEventRecord(ctx->spans.back().b, ctx->stream);
+}
+static void prof_collect(rpf_ctx *ctx) {  // the stream must be idle
+    for (auto &sp : ctx->spans) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, sp.a, sp.b) == cudaSuccess) {
+            ctx->k_ms[sp.k] += ms;
+            ctx->k_launches[sp.k]++;
+        }
+        ctx->free_events.push_back(sp.a);
+        ctx->free_events.push_back(sp.b);
+    }
+    ctx->spans.clear();
 }
 
 static int reset_counters(rpf_ctx *ctx) {
@@ -363,7 +398,9 @@ static int ensure_pstat(rpf_ctx *ctx, const FrameView &f, int y0, int y1) {
     if (ctx->pstat_y0 <= y0 && y1 <= ctx->pstat_y1) return RPF_OK;
     // features never change between iterations (rpf.cpp:715 writes colours only): computed once per upload
     const long long n = 1ll * (y1 - y0) * ctx->cfg.width * NF;
+    prof_begin(ctx, RPF_K_PIXEL_STATS);
     pixel_stats_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, ctx->stream>>>(f, y0, y1, ctx->d_pstat);
+    prof_end(ctx);
     ctx->launches++;
     CU(ctx, cudaGetLastError());
     if (ctx->pstat_y1 <= ctx->pstat_y0) { ctx->pstat_y0 = y0; ctx->pstat_y1 = y1; }
@@ -421,10 +458,16 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
         p.nrows = r0 + rows <= y1 ? static_cast<int>(rows) : y1 - r0;
         const unsigned npx = static_cast<unsigned>(p.nrows * W);
         CU(ctx, cudaMemsetAsync(ctx->d_work, 0, sizeof(unsigned int), ctx->stream));
+        prof_begin(ctx, RPF_K_NBH_STATS);
         nbh_stats_kernel<<<npx, KA_THREADS, 0, ctx->stream>>>(p);
+        prof_end(ctx);
         const unsigned gridb = npx < static_cast<unsigned>(p.pl.kb_grid) ? npx : static_cast<unsigned>(p.pl.kb_grid);
+        prof_begin(ctx, RPF_K_DEPENDENCY);
         dependency_kernel<<<gridb, KB_THREADS, p.pl.kb_smem, ctx->stream>>>(p);
+        prof_end(ctx);
+        prof_begin(ctx, RPF_K_BLEND);
         blend_kernel<<<npx, KC_THREADS, p.pl.kc_smem, ctx->stream>>>(p);
+        prof_end(ctx);
         ctx->launches += 3;
         CU(ctx, cudaGetLastError());
     }
@@ -462,7 +505,9 @@ static int launch_rows(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
     p.dbg_wrc = ctx->d_dbg_wrc;
     p.counters = ctx->d_counters;
     const unsigned grid = static_cast<unsigned>((y1 - y0) * ctx->cfg.width);
+    prof_begin(ctx, RPF_K_FUSED);
     rpf_pixel_kernel<<<grid, THREADS, p.sm.total, ctx->stream>>>(p);
+    prof_end(ctx);
     ctx->launches++;
     CU(ctx, cudaGetLastError());
     ctx->pixels_filtered += grid;
@@ -531,7 +576,23 @@ extern "C" int rpf_synchronize(rpf_ctx *ctx) {
     if (!ctx) return RPF_ERR_INVALID;
     CU(ctx, cudaSetDevice(ctx->cfg.device));
     CU(ctx, cudaStreamSynchronize(ctx->stream));
+    prof_collect(ctx);
     return finish_timing(ctx);
+}
+
+extern "C" int rpf_set_profiling(rpf_ctx *ctx, int on) {
+    if (!ctx) return RPF_ERR_INVALID;
+    int rc = rpf_synchronize(ctx);
+    ctx->profiling = on != 0;
+    return rc;
+}
+
+extern "C" int rpf_get_kernel_times(rpf_ctx *ctx, rpf_kernel_times_t *out) {
+    if (!ctx || !out) return RPF_ERR_INVALID;
+    int rc = rpf_synchronize(ctx);
+    if (rc != RPF_OK) return rc;
+    for (int k = 0; k < RPF_NUM_KERNELS; ++k) { out->ms[k] = ctx->k_ms[k]; out->launches[k] = ctx->k_launches[k]; }
+    return RPF_OK;
 }
 
 extern "C" int rpf_download_colors_f64(rpf_ctx *ctx, double *rgb) {
@@ -600,6 +661,9 @@ extern "C" int rpf_get_stats(rpf_ctx *ctx, rpf_stats_t *out) {
 extern "C" int rpf_reset_stats(rpf_ctx *ctx) {
     if (!ctx) return RPF_ERR_INVALID;
     CU(ctx, cudaSetDevice(ctx->cfg.device));
+    int rc = rpf_synchronize(ctx);
+    if (rc != RPF_OK) return rc;
     ctx->launches = 0;
+    for (int k = 0; k < RPF_NUM_KERNELS; ++k) { ctx->k_ms[k] = 0.0; ctx->k_launches[k] = 0; }
     return reset_counters(ctx);
 }

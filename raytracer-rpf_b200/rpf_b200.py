@@ -22,7 +22,8 @@ ABI_SYMBOLS = [
     "rpf_create", "rpf_destroy", "rpf_last_error", "rpf_upload", "rpf_upload_device", "rpf_upload_colors_f64",
     "rpf_filter", "rpf_filter_rows", "rpf_swap_colors", "rpf_color_device_ptr", "rpf_stream", "rpf_synchronize",
     "rpf_download_colors", "rpf_download_colors_f64", "rpf_download_debug", "rpf_reconstruct_box",
-    "rpf_get_stats", "rpf_reset_stats", "rpf_max_neighbourhood", "rpf_synth_planes",
+    "rpf_get_stats", "rpf_reset_stats", "rpf_set_profiling", "rpf_get_kernel_times", "rpf_max_neighbourhood",
+    "rpf_synth_planes",
 ]
 
 
@@ -39,6 +40,13 @@ class Stats(C.Structure):
     _fields_ = [("pixels_filtered", C.c_longlong), ("nbh_sum", C.c_longlong), ("nbh_min", C.c_int),
                 ("nbh_max", C.c_int), ("nan_channels", C.c_longlong), ("kernel_launches", C.c_longlong),
                 ("last_filter_ms", C.c_double)]
+
+
+KERNEL_NAMES = ["pixel_stats_kernel", "rpf_pixel_kernel", "nbh_stats_kernel", "dependency_kernel", "blend_kernel"]
+
+
+class KernelTimes(C.Structure):
+    _fields_ = [("ms", C.c_double * 5), ("launches", C.c_longlong * 5)]
 
 
 _lib = None
@@ -72,6 +80,8 @@ def lib():
         L.rpf_reconstruct_box.argtypes = [vp, vp]
         L.rpf_get_stats.argtypes = [vp, C.POINTER(Stats)]
         L.rpf_reset_stats.argtypes = [vp]
+        L.rpf_set_profiling.argtypes = [vp, i]
+        L.rpf_get_kernel_times.argtypes = [vp, C.POINTER(KernelTimes)]
         L.rpf_max_neighbourhood.argtypes = []
         L.rpf_synth_planes.argtypes = [i, i, i, C.c_ulonglong, i, i, i, vp]
         _lib = L
@@ -187,6 +197,15 @@ class RPFFilter:
         s = Stats()
         self._check(lib().rpf_get_stats(self._h, C.byref(s)))
         return {k: getattr(s, k) for k, _ in Stats._fields_}
+
+    def set_profiling(self, on=True):
+        self._check(lib().rpf_set_profiling(self._h, 1 if on else 0))
+
+    def kernel_times(self):
+        """{kernel name: (total ms, launches)} since the last reset_stats; needs set_profiling(True)."""
+        kt = KernelTimes()
+        self._check(lib().rpf_get_kernel_times(self._h, C.byref(kt)))
+        return {KERNEL_NAMES[k]: (kt.ms[k], kt.launches[k]) for k in range(5)}
 
     def reset_stats(self):
         self._check(lib().rpf_reset_stats(self._h))
