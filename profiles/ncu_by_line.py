@@ -15,12 +15,19 @@ from collections import defaultdict
 def main():
     rep, cubin, kern = sys.argv[1:4]
     top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
-    txt = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+    txt = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "-k", f"regex:{kern}"], capture_output=True,
+                         text=True).stdout
     rows = list(csv.reader(io.StringIO(txt)))
     hi = next(i for i, r in enumerate(rows) if "Source" in r and "Address" in r)
     hdr = rows[hi]
     ci, cs, csrc = hdr.index("Instructions Executed"), hdr.index("Warp Stall Sampling (All Samples)"), hdr.index("Source")
-    sass = [(r[csrc].strip(), int(r[ci]), int(r[cs])) for r in rows[hi + 1:] if len(r) > cs and r[ci].isdigit()]
+    sass = []
+    for r in rows[hi + 1:]:  # first matching launch only (a report may hold several kernels / launches)
+        if len(r) <= max(ci, cs) or not r[ci].isdigit():
+            if sass:
+                break
+            continue
+        sass.append((r[csrc].strip(), int(r[ci]), int(r[cs])))
     dis = subprocess.run(["nvdisasm", "-g", "-c", cubin], capture_output=True, text=True).stdout.splitlines()
     lines, cur, inside = [], None, False
     for ln in dis:
