@@ -4,7 +4,7 @@
  *   void RPFIntegrator::ApplyRPFFilter(SamplingFilm&, const int tileSize, int box_size)
  *       reference: src/custom/rpf.h:91-95, src/custom/rpf.cpp:497-733, called per box size from
  *       RPFIntegrator::Render at src/custom/rpf.cpp:767-775.
- * The replacement host integrator (raytracer-rpf_b200/host/rpf_integrator.cpp) packs the SamplingFilm
+ * The replacement host integrator (raytracer-rpf_b200/host/rpf_b200_host.cpp) packs the SamplingFilm
  * into structure-of-arrays planes and calls the entry points below instead of ApplyRPFFilter.
  *
  * Conventions: plain pointers and sizes only; every call returns RPF_OK (0) or a negative rpf_status and

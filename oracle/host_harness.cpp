@@ -1,0 +1,44 @@
+// oracle/host_harness.cpp -- TEST INFRASTRUCTURE. Drives the product's host-side C++ (raytracer-rpf_b200/host/
+// rpf_b200_host.cpp) exactly as the reference's Render would: through a real SamplingFilm built from the reference's own
+// sample_film.cpp / sd.h (compiled from /root/reference behind oracle/ref_stubs). Built into oracle/_ref/ by the Makefile.
+#include "pbrt.h"
+
+#include "rpf_b200_host.h"
+
+using namespace pbrt;
+
+extern "C" int host_apply_rpf_b200(int W, int H, int P, const float *planes, double *colors, const int *boxes, int n_boxes,
+                                   double seed, int flags, double *mean_nbh, long long *nan_channels, char *err, int err_len) {
+    Bounds2i bounds(Point2i(0, 0), Point2i(W, H));
+    SamplingFilm sf(bounds);
+    const size_t S = static_cast<size_t>(W) * H * P;
+    for (int y = 0; y < H; ++y)
+        for (int x = 0; x < W; ++x)
+            for (int s = 0; s < P; ++s) {
+                const size_t i = (static_cast<size_t>(y) * W + x) * P + s;
+                SampleData sd;
+                for (int c = 0; c < 19; ++c) sd.data[c] = planes[c * S + i];
+                for (int k = 0; k < 3; ++k) sd.data[2 + k] = colors[k * S + i];
+                sd.rayWeight = 1;
+                sf.AddSample(Point2i(x, y), sd);
+            }
+    RPFB200Options opt;
+    opt.boxSizes.assign(boxes, boxes + n_boxes);
+    opt.sigmaSeed = seed;
+    opt.flags = flags;
+    RPFB200Report rep;
+    std::string error;
+    if (!ApplyRPFFilterB200(sf, opt, &rep, &error)) {
+        if (err && err_len > 0) { std::snprintf(err, err_len, "%s", error.c_str()); }
+        return -1;
+    }
+    for (int y = 0; y < H; ++y)
+        for (int x = 0; x < W; ++x)
+            for (int s = 0; s < P; ++s) {
+                const size_t i = (static_cast<size_t>(y) * W + x) * P + s;
+                for (int k = 0; k < 3; ++k) colors[k * S + i] = sf.samples[x][y][s].data[2 + k];
+            }
+    if (mean_nbh) *mean_nbh = rep.meanNeighbourhood;
+    if (nan_channels) *nan_channels = rep.nanChannels;
+    return 0;
+}

@@ -1,0 +1,90 @@
+// rpf_b200_host.cpp -- see rpf_b200_host.h. Host C++ only; all device work happens behind include/rpf_b200.h.
+#include "rpf_b200_host.h"
+
+#include <memory>
+
+#include "rpf_b200.h"
+
+namespace pbrt {
+
+namespace {
+struct CtxDeleter {
+    void operator()(rpf_ctx *c) const { rpf_destroy(c); }
+};
+bool failed(std::string *error, const std::string &what, const rpf_ctx *ctx) {
+    if (error) *error = what + ": " + rpf_last_error(ctx);
+    return false;
+}
+}  // namespace
+
+bool ApplyRPFFilterB200(SamplingFilm &film, const RPFB200Options &opt, RPFB200Report *report, std::string *error) {
+    const int W = film.getWidth(), H = film.getHeight();
+    if (W <= 0 || H <= 0 || film.samples.empty() || film.samples[0].empty()) {
+        if (error) *error = "empty SamplingFilm";
+        return false;
+    }
+    // every sampler of the reference yields a constant count per pixel; the device layout needs it
+    const size_t spp = film.samples[0][0].size();
+    for (int x = 0; x < W; ++x)
+        for (int y = 0; y < H; ++y)
+            if (film.samples[x][y].size() != spp || spp == 0) {
+                if (error) *error = "SamplingFilm has a ragged or zero sample count at pixel (" + std::to_string(x) + "," +
+                                    std::to_string(y) + ")";
+                return false;
+            }
+    const size_t S = static_cast<size_t>(W) * H * spp;
+
+    // pack: plane[c][(y*W + x)*spp + s]; SampleData::data order (sd.h:62-94). The producer writes pbrt Floats into the
+    // doubles (sd.h:62-94), so narrowing to float is exact for a fresh film.
+    std::vector<float> planes(static_cast<size_t>(RPF_NUM_CHANNELS) * S);
+    std::vector<double> colours(3 * S);
+    for (int x = 0; x < W; ++x)
+        for (int y = 0; y < H; ++y) {
+            const SampleDataSet &px = film.samples[x][y];
+            const size_t base = (static_cast<size_t>(y) * W + x) * spp;
+            for (size_t s = 0; s < spp; ++s) {
+                for (int c = 0; c < RPF_NUM_CHANNELS; ++c) planes[c * S + base + s] = static_cast<float>(px[s].data[c]);
+                for (int k = 0; k < 3; ++k) colours[k * S + base + s] = px[s].data[2 + k];
+            }
+        }
+
+    rpf_config cfg{};
+    cfg.width = W;
+    cfg.height = H;
+    cfg.spp = static_cast<int>(spp);
+    cfg.device = opt.device;
+    cfg.flags = opt.flags;
+    rpf_ctx *raw = nullptr;
+    if (rpf_create(&raw, &cfg) != RPF_OK) return failed(error, "rpf_create", nullptr);
+    std::unique_ptr<rpf_ctx, CtxDeleter> ctx(raw);
+
+    const float *ptrs[RPF_NUM_CHANNELS];
+    for (int c = 0; c < RPF_NUM_CHANNELS; ++c) ptrs[c] = planes.data() + c * S;
+    if (rpf_upload(ctx.get(), ptrs) != RPF_OK) return failed(error, "rpf_upload", ctx.get());
+    // colours re-entering the filter after an earlier pass are doubles (sd.h:205-207): keep every bit
+    if (rpf_upload_colors_f64(ctx.get(), colours.data()) != RPF_OK) return failed(error, "rpf_upload_colors_f64", ctx.get());
+    if (rpf_filter(ctx.get(), opt.boxSizes.data(), static_cast<int>(opt.boxSizes.size()), opt.sigmaSeed) != RPF_OK)
+        return failed(error, "rpf_filter", ctx.get());
+    if (rpf_download_colors_f64(ctx.get(), colours.data()) != RPF_OK) return failed(error, "rpf_download_colors_f64", ctx.get());
+    rpf_stats_t st{};
+    if (rpf_get_stats(ctx.get(), &st) != RPF_OK) return failed(error, "rpf_get_stats", ctx.get());
+
+    // rpf.cpp:715,732: only the three colour slots change
+    for (int x = 0; x < W; ++x)
+        for (int y = 0; y < H; ++y) {
+            SampleDataSet &px = film.samples[x][y];
+            const size_t base = (static_cast<size_t>(y) * W + x) * spp;
+            for (size_t s = 0; s < spp; ++s)
+                for (int k = 0; k < 3; ++k) px[s].data[2 + k] = colours[k * S + base + s];
+        }
+    if (report) {
+        report->nanChannels = st.nan_channels;
+        report->meanNeighbourhood = st.pixels_filtered ? static_cast<double>(st.nbh_sum) / st.pixels_filtered : 0.0;
+        report->minNeighbourhood = st.nbh_min;
+        report->maxNeighbourhood = st.nbh_max;
+        report->filterMs = st.last_filter_ms;
+    }
+    return true;
+}
+
+}  // namespace pbrt

@@ -76,3 +76,23 @@ def test_band_planning():
             assert g(lo, s[1]) == g(hi, t[2]) and g(hi, t[1]) == g(lo, s[2])
             assert s[1][1] - s[1][0] == bands.b_delta(nb)
     assert bands.halo_plan(bands.make_band(0, 1, H, boxes), 7) == []
+
+
+def test_host_cpp_reports_missing_device():
+    """The C++ host shim (built against the reference's SamplingFilm) surfaces the C ABI's error instead of falling back."""
+    import torch
+    path = os.path.join(ROOT, "oracle", "_ref", "libhost_harness.so")
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref/libhost_harness.so not built")
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    _lib_or_skip()
+    lib = C.CDLL(path)
+    W, H, P = 4, 3, 2
+    planes = np.zeros((19, W * H * P), np.float32)
+    col = np.zeros((3, W * H * P), np.float64)
+    bx = np.asarray([3], np.int32)
+    err = C.create_string_buffer(512)
+    rc = lib.host_apply_rpf_b200(W, H, P, planes.ctypes.data_as(C.c_void_p), col.ctypes.data_as(C.c_void_p),
+                                 bx.ctypes.data_as(C.c_void_p), 1, C.c_double(0.5), 0, None, None, err, 512)
+    assert rc == -1 and b"rpf_create" in err.value

@@ -160,3 +160,25 @@ def test_row_band_equals_full_frame(general):
     bands = f.download_colors_f64()
     f.close()
     assert np.array_equal(full, bands)
+
+
+def test_host_cpp_through_reference_samplingfilm():
+    """The product's host C++ (raytracer-rpf_b200/host/rpf_b200_host.cpp) packing a real reference SamplingFilm, as Render would."""
+    import ctypes as C
+    import os
+    import rpf_b200
+    path = os.path.join(ob.ORACLE_DIR, "_ref", "libhost_harness.so")
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref/libhost_harness.so was not built (needs /root/reference at build time)")
+    lib = C.CDLL(path)
+    W, H, P, boxes, seed = 28, 22, 8, [9, 7], 0.5
+    planes = rpf_b200.synth_planes(W, H, P, seed=21, kind=0)
+    col = planes[2:5].astype(np.float64).copy()
+    bx = np.asarray(boxes, np.int32)
+    mean, nans, err = C.c_double(), C.c_longlong(), C.create_string_buffer(512)
+    rc = lib.host_apply_rpf_b200(W, H, P, planes.ctypes.data_as(C.c_void_p), col.ctypes.data_as(C.c_void_p),
+                                 bx.ctypes.data_as(C.c_void_p), len(bx), C.c_double(seed), 0, C.byref(mean), C.byref(nans), err, 512)
+    assert rc == 0, err.value
+    o = ob.oracle_filter(planes, W, H, P, boxes, seed=seed)
+    assert np.abs(col - o["colors"]).max() <= TOL_TIGHT
+    assert nans.value == o["nan_count"] and mean.value > P
