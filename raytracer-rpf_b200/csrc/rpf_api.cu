@@ -368,6 +368,7 @@ static bool plan_general(long long ncap, int spp, int dyn_limit, GeneralPlan &L)
         L.bins_in_smem = 1;
         L.off_bins = L.off_region + region(4);
         L.kb_smem = L.off_bins + bins_bytes;
+        L.region_words = region(4) / 4;
         return true;
     }
     for (int G = 4; G >= 1; G >>= 1) {
@@ -376,6 +377,7 @@ static bool plan_general(long long ncap, int spp, int dyn_limit, GeneralPlan &L)
             L.bins_in_smem = 0;
             L.off_bins = 0;
             L.kb_smem = L.off_region + region(G);
+            L.region_words = region(G) / 4;
             return true;
         }
     }

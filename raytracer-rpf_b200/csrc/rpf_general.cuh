@@ -34,6 +34,7 @@ struct GeneralPlan {
     int nbs;         // words per marginal histogram
     int bins_in_smem;
     int off_gsm, off_marg, off_region, off_bins, kb_smem;  // KB dynamic shared memory layout (bytes)
+    int region_words;  // capacity of the histogram region in 32-bit words
     int kb_grid;
     int kc_smem;
 };
@@ -290,13 +291,13 @@ struct KBSmall {
     double M[NCH], SD[NCH], lo[NCH], hi[NCH], rlo[NCH], rhi[NCH], rsd[NCH], rr[NCH];
     int flat[NCH], ordered[NCH];
     unsigned long long Sm[NCH];  // sum n ln n of each marginal (fixed point)
-    unsigned long long red[KB_THREADS / 32][4];
+    unsigned long long Sj[KB_THREADS / 32][4];  // per team: sum n ln n of the joint tables being built
     double redd[KB_THREADS / 32];
     double mi[N_JOINT];
     double alpha[NC], beta[NF], wrc;
     double wrf[NF], dcf[NF], dsum[9], wrck[NC];
     int wsum[KB_THREADS / 32 + 1];
-    int N, nb, Q, redo[4];
+    int N, nb, Q, redo[KB_THREADS / 32][4];
     unsigned int pixel;
 };
 
@@ -364,6 +365,127 @@ __device__ __forceinline__ void group_channels(int g, int &a, int &t0) {
     else { const int u = g - 12; a = CH_COL + (u >> 2); t0 = 48 + 16 * (u >> 2) + 4 * (u & 3); }
 }
 
+
+__device__ __forceinline__ void team_sync(int team, int nthreads) {
+    if (nthreads == 32) __syncwarp();
+    else asm volatile("bar.sync %0, %1;" ::"r"(team + 1), "r"(nthreads) : "memory");
+}
+
+// Joint histograms of one pixel. Raising a cell from k to k+1 adds g[k] = (k+1)ln(k+1) - k ln k to the table's
+// sum of n ln n; the returning shared atomic supplies k. MI(a,b) = (S_ab - S_a - S_b + N ln N)/N (equals
+// mi.cpp:79-87 up to rounding), evaluated in exact integer arithmetic (unit 2^-43).
+template <int G>
+__device__ __forceinline__ void joint_phase(const GeneralParams &p, KBSmall &ks, const uint32_t *bins, unsigned *region,
+                                            const unsigned *marg, const unsigned long long *gsm, int N, int nb, int hwn,
+                                            int teams) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tw = (KB_THREADS / 32) / teams, team = warp / tw;
+    const int tn = tw * 32, tt = tid - team * tn;
+    unsigned *th = region + team * G * hwn;
+    const int nq = p.pl.nq, nbs = p.pl.nbs;
+    const int nfull = N >> 2, ntail = N & 3;
+    const double dn = static_cast<double>(N);
+    const unsigned long long Stot = p.hq[N];
+    constexpr int SUBS = 4 / G;
+    auto update = [&](unsigned ca, unsigned cb, int j, unsigned long long &acc) {
+        const unsigned cell = ca + cb, sh = (cell & 1u) << 4;
+        const unsigned old = atomicAdd(&th[j * hwn + (cell >> 1)], 1u << sh);
+        const unsigned cnt = (old >> sh) & 0xffffu;
+        acc += cnt < KB_GSM ? gsm[cnt] : p.gq[cnt];
+    };
+    for (int u = team; u < 24 * SUBS; u += teams) {
+        const int grp = u / SUBS, sub = (u - grp * SUBS) * G;
+        int a, t0;
+        group_channels(grp, a, t0);
+        if (ks.flat[a]) {  // a constant channel has MI exactly 0 with everything (mi.cpp: every ratio is 1)
+            if (tt < G) ks.mi[t0 + sub + tt] = 0.0;
+            continue;
+        }
+        const uint32_t *ba = bins + a * nq;
+        const uint32_t *bb[G];
+#pragma unroll
+        for (int j = 0; j < G; ++j) { int aa, b; task_channels(t0 + sub + j, aa, b); bb[j] = bins + b * nq; }
+        unsigned long long acc[G];
+#pragma unroll
+        for (int j = 0; j < G; ++j) acc[j] = 0ull;
+        for (int q = tt; q < nfull; q += tn) {
+            const uint32_t wa = ba[q];
+            uint32_t wb[G];
+#pragma unroll
+            for (int j = 0; j < G; ++j) wb[j] = bb[j][q];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const unsigned ca = ((wa >> (8 * k)) & 255u) * nb;
+#pragma unroll
+                for (int j = 0; j < G; ++j) update(ca, (wb[j] >> (8 * k)) & 255u, j, acc[j]);
+            }
+        }
+        if (ntail && tt == 0) {
+            const uint32_t wa = ba[nfull];
+            for (int k = 0; k < ntail; ++k) {
+                const unsigned ca = ((wa >> (8 * k)) & 255u) * nb;
+#pragma unroll
+                for (int j = 0; j < G; ++j) update(ca, (bb[j][nfull] >> (8 * k)) & 255u, j, acc[j]);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < G; ++j) {
+            const unsigned long long sj = warp_sum_u64(acc[j]);
+            if (lane == 0) atomicAdd(&ks.Sj[team][j], sj);
+        }
+        team_sync(team, tn);
+        if (tt < G) {
+            const unsigned long long sab = ks.Sj[team][tt];
+            ks.Sj[team][tt] = 0ull;
+            int aa, b;
+            task_channels(t0 + sub + tt, aa, b);
+            double mi = 0.0;
+            int redo = 0;
+            if (!ks.flat[b]) {
+                const long long num = static_cast<long long>((sab + Stot) - (ks.Sm[a] + ks.Sm[b]));
+                mi = static_cast<double>(num) * (1.0 / 8796093022208.0) / dn;  // 2^-43
+                // Exactly independent tables give exactly 0 in mi.cpp (every ratio is 1.0) but rounding noise here;
+                // the P2 guards branch on such zeros, so suspiciously small values are recomputed cell by cell.
+                redo = mi != 0.0 && fabs(mi) < 1e-4 / (dn * dn);
+            }
+            ks.mi[t0 + sub + tt] = mi;
+            ks.redo[team][tt] = redo;
+        }
+        team_sync(team, tn);
+        for (int j = 0; j < G; ++j) {
+            if (!ks.redo[team][j]) continue;  // team-uniform
+            int aa, b;
+            task_channels(t0 + sub + j, aa, b);
+            double sr = 0.0;
+            for (int cell = tt; cell < nb * nb; cell += tn) {
+                const unsigned wv = th[j * hwn + (cell >> 1)];
+                const unsigned n = (cell & 1) ? (wv >> 16) : (wv & 0xffffu);
+                if (n == 0) continue;
+                const int i = cell / nb, jj = cell - i * nb;
+                const double pxv = __ddiv_rn(static_cast<double>(marg[a * nbs + i]), dn);
+                const double pyv = __ddiv_rn(static_cast<double>(marg[b * nbs + jj]), dn);
+                const double pxy = __ddiv_rn(static_cast<double>(n), dn);
+                const double pp = __dmul_rn(pxv, pyv);
+                if (pp != 0.0) sr = __dadd_rn(sr, __dmul_rn(pxy, log(__ddiv_rn(pxy, pp))));
+            }
+            sr = warp_sum(sr);
+            if (lane == 0) ks.redd[warp] = sr;
+            team_sync(team, tn);
+            if (tt == 0) {
+                double r = 0.0;
+                for (int w = 0; w < tw; ++w) r += ks.redd[team * tw + w];
+                ks.mi[t0 + sub + j] = r;
+            }
+            team_sync(team, tn);
+        }
+        {
+            uint4 *r4 = reinterpret_cast<uint4 *>(th);
+            for (int k = tt; k < (G * hwn) >> 2; k += tn) r4[k] = make_uint4(0u, 0u, 0u, 0u);
+        }
+        team_sync(team, tn);
+    }
+}
+
 // =====================================================================================================
 // KB: bins + joint histograms + MI + alpha/beta. Persistent CTAs of 512 threads.
 __global__ void __launch_bounds__(KB_THREADS, 1) dependency_kernel(const GeneralParams p) {
@@ -379,7 +501,7 @@ __global__ void __launch_bounds__(KB_THREADS, 1) dependency_kernel(const General
     unsigned short *idx16 = reinterpret_cast<unsigned short *>(region);
     uint32_t *bins = L.bins_in_smem ? reinterpret_cast<uint32_t *>(smem + L.off_bins)
                                     : reinterpret_cast<uint32_t *>(p.bins_scratch + static_cast<size_t>(blockIdx.x) * NCH * L.nq * 4);
-    const int nq = L.nq, G = L.G, hw = L.hw;
+    const int nq = L.nq;
     const int npix = p.nrows * W;
 
     for (int k = tid; k < KB_GSM; k += KB_THREADS) gsm[k] = p.gq[k];
@@ -489,109 +611,24 @@ __global__ void __launch_bounds__(KB_THREADS, 1) dependency_kernel(const General
             s = warp_sum_u64(s);
             if (lane == 0) ks.Sm[c] = s;
         }
+        // ---- 96 joint histograms ----------------------------------------------------------------------------------
+        // The histogram region is cut into slots of the ACTUAL table size (nb*nb u16 cells); the 16 warps split into
+        // teams, each team owns G slots and works through its share of the 96 pairs without CTA-wide barriers.
         {
-            uint4 *r4 = reinterpret_cast<uint4 *>(region);
-            for (int k = tid; k < (G * hw) >> 2; k += KB_THREADS) r4[k] = make_uint4(0u, 0u, 0u, 0u);
-        }
-        __syncthreads();
-
-        // ---- 96 joint histograms, G at a time; sum n ln n accumulated incrementally ---------------------------
-        // Raising a cell from k to k+1 adds g[k] = (k+1)ln(k+1) - k ln k; the returning shared atomic supplies k.
-        // MI(a,b) = (S_ab - S_a - S_b + N ln N)/N  (equals mi.cpp:79-87 up to rounding), in exact integer arithmetic.
-        const unsigned long long Stot = p.hq[N];
-        const int nqn = (N + 3) >> 2;
-        for (int grp = 0; grp < 24; ++grp) {
-            int a, t0;
-            group_channels(grp, a, t0);
-            if (ks.flat[a]) {  // a constant channel has MI exactly 0 with everything (mi.cpp: every ratio is 1)
-                if (tid < 4) ks.mi[t0 + tid] = 0.0;
-                continue;
+            const int hwn = (((nb * nb + 1) >> 1) + 3) & ~3;
+            const int slots = L.region_words / hwn;
+            const int Gp = slots >= 4 ? 4 : (slots >= 2 ? 2 : 1);
+            int teams = 1;
+            while (teams * 2 <= KB_THREADS / 32 && teams * 2 * Gp <= slots) teams *= 2;
+            {
+                uint4 *r4 = reinterpret_cast<uint4 *>(region);
+                for (int k = tid; k < (teams * Gp * hwn) >> 2; k += KB_THREADS) r4[k] = make_uint4(0u, 0u, 0u, 0u);
+                if (tid < 64) (&ks.Sj[0][0])[tid] = 0ull;
             }
-            for (int sub = 0; sub < 4; sub += G) {
-                int bch[4];
-#pragma unroll
-                for (int j = 0; j < 4; ++j) { int aa, bb; task_channels(t0 + sub + (j < G ? j : 0), aa, bb); bch[j] = bb; }
-                unsigned long long acc[4] = {0ull, 0ull, 0ull, 0ull};
-                const uint32_t *ba = bins + a * nq;
-                for (int q = tid; q < nqn; q += KB_THREADS) {
-                    const uint32_t wa = ba[q];
-                    uint32_t wb[4];
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) if (j < G) wb[j] = bins[bch[j] * nq + q];
-                    const int valid = min(4, N - 4 * q);
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        if (k < valid) {
-                            const unsigned ca = ((wa >> (8 * k)) & 255u) * nb;
-#pragma unroll
-                            for (int j = 0; j < 4; ++j) {
-                                if (j < G) {
-                                    const unsigned cell = ca + ((wb[j] >> (8 * k)) & 255u);
-                                    const unsigned old = atomicAdd(&region[j * hw + (cell >> 1)], (cell & 1u) ? 0x10000u : 1u);
-                                    const unsigned cnt = (cell & 1u) ? (old >> 16) : (old & 0xffffu);
-                                    acc[j] += cnt < KB_GSM ? gsm[cnt] : p.gq[cnt];
-                                }
-                            }
-                        }
-                    }
-                }
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    if (j < G) {
-                        const unsigned long long s = warp_sum_u64(acc[j]);
-                        if (lane == 0) ks.red[warp][j] = s;
-                    }
-                }
-                __syncthreads();
-                if (tid < G) {
-                    unsigned long long s = 0ull;
-                    for (int w = 0; w < KB_THREADS / 32; ++w) s += ks.red[w][tid];
-                    int aa, b;
-                    task_channels(t0 + sub + tid, aa, b);
-                    double mi = 0.0;
-                    int redo = 0;
-                    if (!ks.flat[b]) {
-                        const long long num = static_cast<long long>((s + Stot) - (ks.Sm[a] + ks.Sm[b]));
-                        mi = static_cast<double>(num) * (1.0 / 8796093022208.0) / dn;  // 2^-43
-                        // Exactly independent tables give exactly 0 in mi.cpp (every ratio is 1.0) but rounding noise here;
-                        // the P2 guards branch on such zeros, so suspiciously small values are recomputed cell by cell.
-                        redo = mi != 0.0 && fabs(mi) < 1e-4 / (dn * dn);
-                    }
-                    ks.mi[t0 + sub + tid] = mi;
-                    ks.redo[tid] = redo;
-                }
-                __syncthreads();
-                for (int j = 0; j < G; ++j) {
-                    if (!ks.redo[j]) continue;  // block-uniform
-                    const int b = bch[j];
-                    double s = 0.0;
-                    for (int cell = tid; cell < nb * nb; cell += KB_THREADS) {
-                        const unsigned wv = region[j * hw + (cell >> 1)];
-                        const unsigned n = (cell & 1) ? (wv >> 16) : (wv & 0xffffu);
-                        if (n == 0) continue;
-                        const int i = cell / nb, jj = cell - i * nb;
-                        const double pxv = __ddiv_rn(static_cast<double>(marg[a * L.nbs + i]), dn);
-                        const double pyv = __ddiv_rn(static_cast<double>(marg[b * L.nbs + jj]), dn);
-                        const double pxy = __ddiv_rn(static_cast<double>(n), dn);
-                        const double pp = __dmul_rn(pxv, pyv);
-                        if (pp != 0.0) s = __dadd_rn(s, __dmul_rn(pxy, log(__ddiv_rn(pxy, pp))));
-                    }
-                    s = warp_sum(s);
-                    __syncthreads();
-                    if (lane == 0) ks.redd[warp] = s;
-                    __syncthreads();
-                    if (tid == 0) {
-                        double r = 0.0;
-                        for (int w = 0; w < KB_THREADS / 32; ++w) r += ks.redd[w];
-                        ks.mi[t0 + sub + j] = r;
-                    }
-                }
-                {
-                    uint4 *r4 = reinterpret_cast<uint4 *>(region);
-                    for (int k = tid; k < (G * hw) >> 2; k += KB_THREADS) r4[k] = make_uint4(0u, 0u, 0u, 0u);
-                }
-                __syncthreads();
-            }
+            __syncthreads();
+            if (Gp == 4) joint_phase<4>(p, ks, bins, region, marg, gsm, N, nb, hwn, teams);
+            else if (Gp == 2) joint_phase<2>(p, ks, bins, region, marg, gsm, N, nb, hwn, teams);
+            else joint_phase<1>(p, ks, bins, region, marg, gsm, N, nb, hwn, teams);
         }
         __syncthreads();
 
