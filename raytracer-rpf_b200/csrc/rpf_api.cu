@@ -280,10 +280,12 @@ extern "C" int rpf_create(rpf_ctx **out, const rpf_config *cfg) {
     CUC(cudaFuncSetAttribute(rpf_pixel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
     {
         cudaFuncAttributes fa;
-        CUC(cudaFuncGetAttributes(&fa, dependency_kernel));
+        CUC(cudaFuncGetAttributes(&fa, dependency_kernel<512>));
         ctx->kb_static_smem = static_cast<int>(fa.sharedSizeBytes);
-        CUC(cudaFuncSetAttribute(dependency_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        CUC(cudaFuncSetAttribute(dependency_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  227 * 1024 - ctx->kb_static_smem - 1024));
+        CUC(cudaFuncSetAttribute(dependency_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (228 * 1024) / 2 - ctx->kb_static_smem - 1024));
         ctx->num_sms = prop.multiProcessorCount;
         CUC(cudaMalloc(&ctx->d_work, sizeof(unsigned int)));
         ctx->force_general = (cfg->flags & RPF_FLAG_FORCE_GENERAL) || (getenv("RPF_FORCE_GENERAL") && atoi(getenv("RPF_FORCE_GENERAL")));
@@ -345,8 +347,11 @@ extern "C" int rpf_upload_colors_f64(rpf_ctx *ctx, const double *rgb) {
 // ---- general path (rpf_general.cuh) ----------------------------------------------------------------------
 static const int kGeneralMaxCandidates = 65535;  // u16 candidate numbers and histogram cells, u8 bins (nb <= 255)
 
-// Shared-memory plan of the dependency kernel for ncap = box*box*spp candidates.
-static bool plan_general(long long ncap, int spp, int dyn_limit, GeneralPlan &L) {
+// Shared-memory plan of the dependency kernel for ncap = box*box*spp candidates. Two CTAs of 256 threads per SM when
+// at least two full-size histograms fit in half an SM's shared memory, else one CTA of 512 threads. Whatever is left
+// after the fixed tables goes to the histogram region (more slots = more warp teams); the bin bytes stay in shared
+// memory only if eight full-size histograms still fit beside them, otherwise they go to an L2-resident per-CTA scratch.
+static bool plan_general(long long ncap, int spp, int static_smem, GeneralPlan &L) {
     if (ncap > kGeneralMaxCandidates) return false;
     L.ncap = static_cast<int>(ncap);
     L.mw = ((L.ncap + 127) / 128) * 4;
@@ -357,29 +362,23 @@ static bool plan_general(long long ncap, int spp, int dyn_limit, GeneralPlan &L)
     L.off_gsm = 0;
     L.off_marg = KB_GSM * 8;
     L.off_region = align16(L.off_marg + NCH * L.nbs * 4);
+    L.kc_smem = spp * 18 * 8;
     const int idx_bytes = align16(2 * L.ncap);
     const int bins_bytes = NCH * L.nq * 4;
-    auto region = [&](int G) { const int h = G * L.hw * 4; return h > idx_bytes ? h : idx_bytes; };
-    L.kc_smem = spp * 18 * 8;
-    // bins stay in shared memory only when four histograms fit beside them; otherwise they go to an L2-resident
-    // per-CTA scratch and the histogram region takes what is there
-    if (L.off_region + region(4) + bins_bytes <= dyn_limit) {
-        L.G = 4;
-        L.bins_in_smem = 1;
-        L.off_bins = L.off_region + region(4);
-        L.kb_smem = L.off_bins + bins_bytes;
-        L.region_words = region(4) / 4;
+    const int hist_bytes = L.hw * 4;
+    auto atleast = [&](int n) { const int h = n * hist_bytes; return h > idx_bytes ? h : idx_bytes; };
+    const int limit[2] = {(228 * 1024) / 2 - static_smem - 1024, 227 * 1024 - static_smem - 1024};
+    for (int v = 0; v < 2; ++v) {
+        const int avail = (limit[v] - L.off_region) & ~15;
+        if (avail < atleast(v == 0 ? 2 : 1)) continue;
+        L.nt = v == 0 ? 256 : 512;
+        L.bins_in_smem = bins_bytes + atleast(8) <= avail;
+        const int region = L.bins_in_smem ? avail - bins_bytes : avail;
+        L.off_bins = L.bins_in_smem ? L.off_region + region : 0;
+        L.region_words = region / 4;
+        L.kb_smem = L.off_region + avail;
+        L.G = 0;
         return true;
-    }
-    for (int G = 4; G >= 1; G >>= 1) {
-        if (L.off_region + region(G) <= dyn_limit) {
-            L.G = G;
-            L.bins_in_smem = 0;
-            L.off_bins = 0;
-            L.kb_smem = L.off_region + region(G);
-            L.region_words = region(G) / 4;
-            return true;
-        }
     }
     return false;
 }
@@ -412,8 +411,7 @@ static int ensure_pstat(rpf_ctx *ctx, const FrameView &f, int y0, int y1) {
 
 static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
     GeneralParams p{};
-    const int dyn_limit = 227 * 1024 - ctx->kb_static_smem - 1024;
-    if (!plan_general(1ll * box * box * ctx->cfg.spp, ctx->cfg.spp, dyn_limit, p.pl))
+    if (!plan_general(1ll * box * box * ctx->cfg.spp, ctx->cfg.spp, ctx->kb_static_smem, p.pl))
         return fail(ctx, RPF_ERR_UNSUPPORTED,
                     "neighbourhood of box %d x %d spp = %lld candidates exceeds this build (max %d: 16-bit histogram cells)", box,
                     ctx->cfg.spp, 1ll * box * box * ctx->cfg.spp, kGeneralMaxCandidates);
@@ -429,7 +427,8 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
     if (rows < 1) rows = 1;
     if (rows > y1 - y0) rows = y1 - y0;
     int occ = 0;
-    CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dependency_kernel, KB_THREADS, p.pl.kb_smem));
+    if (p.pl.nt == 256) CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dependency_kernel<256>, 256, p.pl.kb_smem));
+    else CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dependency_kernel<512>, 512, p.pl.kb_smem));
     if (occ < 1) return fail(ctx, RPF_ERR_CUDA, "dependency kernel does not fit on an SM with %d bytes of shared memory", p.pl.kb_smem);
     const long long chunk_px = rows * W;
     p.pl.kb_grid = static_cast<int>(chunk_px < 1ll * occ * ctx->num_sms ? chunk_px : 1ll * occ * ctx->num_sms);
@@ -465,7 +464,8 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
         prof_end(ctx);
         const unsigned gridb = npx < static_cast<unsigned>(p.pl.kb_grid) ? npx : static_cast<unsigned>(p.pl.kb_grid);
         prof_begin(ctx, RPF_K_DEPENDENCY);
-        dependency_kernel<<<gridb, KB_THREADS, p.pl.kb_smem, ctx->stream>>>(p);
+        if (p.pl.nt == 256) dependency_kernel<256><<<gridb, 256, p.pl.kb_smem, ctx->stream>>>(p);
+        else dependency_kernel<512><<<gridb, 512, p.pl.kb_smem, ctx->stream>>>(p);
         prof_end(ctx);
         prof_begin(ctx, RPF_K_BLEND);
         blend_kernel<<<npx, KC_THREADS, p.pl.kc_smem, ctx->stream>>>(p);

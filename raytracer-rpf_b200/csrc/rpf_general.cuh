@@ -22,14 +22,15 @@ namespace rpf {
 constexpr int REC_M = 0, REC_SD = 19, REC_RLO = 38, REC_RHI = 57, REC_N = 76, REC_ALPHA = 77, REC_BETA = 80, REC_WRC = 92;
 constexpr int REC_DOUBLES = 96;  // per-pixel record in HBM scratch
 constexpr int KA_THREADS = 128, KA_STRIDE = 129;
-constexpr int KB_THREADS = 512, KB_GSM = 1024;
+constexpr int KB_MAX_WARPS = 16, KB_GSM = 512;
 constexpr int KC_THREADS = 128, KC_SEG_WORDS = 128, KC_IC = 8;
 
 struct GeneralPlan {
     int ncap;        // box*box*spp candidates
     int mw;          // mask words per pixel (multiple of 4)
     int nq;          // ceil(ncap/4): words per channel of packed u8 bins
-    int G;           // joint histograms accumulated concurrently (4, 2 or 1)
+    int G;           // unused (the kernel picks 4, 2 or 1 tables at a time per pixel from the actual table size)
+    int nt;          // threads per CTA of the dependency kernel: 256 (two CTAs per SM) or 512
     int hw;          // words per joint histogram (two u16 cells per word), multiple of 4
     int nbs;         // words per marginal histogram
     int bins_in_smem;
@@ -288,32 +289,33 @@ __device__ __forceinline__ int block_exclusive_scan(int v, int *wsum /* [NT/32 +
 }
 
 struct KBSmall {
-    double M[NCH], SD[NCH], lo[NCH], hi[NCH], rlo[NCH], rhi[NCH], rsd[NCH], rr[NCH];
-    int flat[NCH], ordered[NCH];
-    unsigned long long Sm[NCH];  // sum n ln n of each marginal (fixed point)
-    unsigned long long Sj[KB_THREADS / 32][4];  // per team: sum n ln n of the joint tables being built
-    double redd[KB_THREADS / 32];
+    double M[NCH], SD[NCH], lo[NCH], hi[NCH];
+    double A[NCH], Bc[NCH], tol[NCH];  // bin estimate te = x*A + Bc, trusted unless within tol*(|te|+1) of an integer
+    int flat[NCH];
+    unsigned long long Sm[NCH];        // sum n ln n of each marginal (fixed point)
+    unsigned long long Sab[N_JOINT];   // sum n ln n of each joint table (fixed point)
+    double redd[KB_MAX_WARPS];
     double mi[N_JOINT];
+    int susp[N_JOINT];                 // pairs whose MI must be recomputed with the reference's own expression
     double alpha[NC], beta[NF], wrc;
     double wrf[NF], dcf[NF], dsum[9], wrck[NC];
-    int wsum[KB_THREADS / 32 + 1];
-    int N, nb, Q, redo[KB_THREADS / 32][4];
+    int wsum[KB_MAX_WARPS + 1];
+    int N, nb, Q, any_susp;
     unsigned int pixel;
 };
 
-// mi.cpp:14-16 on top of sd.h:224-235: bin of raw value x of channel c. A reciprocal-multiply estimate decides
-// unless it lands within 1e-9 of an integer; then the reference's exact divisions run (see rpf_pixel_kernel.cuh).
+// mi.cpp:14-16 on top of sd.h:224-235: bin of raw value x of channel c. The reference value is
+// trunc((((x-M)/SD) - lo)/(hi-lo) * nb) with every operation rounded; one FMA estimates it, and only when the estimate is
+// too close to an integer for its error bound (or is NaN) do the reference's exact divisions run. A flat channel has
+// A = 0, Bc = 0.5 (always bin 0); a NaN sigma makes A NaN (always the exact path).
 __device__ __forceinline__ int bin_value(double x, int c, const KBSmall &ks, int nb, double dnb) {
-    if (ks.flat[c]) return 0;
-    const bool ordered = ks.ordered[c];
-    if (ordered && x == ks.rlo[c]) return 0;
-    if (ordered && x == ks.rhi[c]) return nb - 1;
-    const double te = ((x - ks.M[c]) * ks.rsd[c] - ks.lo[c]) * ks.rr[c];
+    const double te = fma(x, ks.A[c], ks.Bc[c]);
     const double r = rint(te);
     int b;
-    if (ordered && fabs(te - r) > 1e-9 * (fabs(te) + 1.0)) {
-        b = static_cast<int>(te);
+    if (fabs(te - r) > ks.tol[c] * (fabs(te) + 1.0)) {
+        b = __double2int_rz(te);
     } else {
+        if (ks.flat[c]) return 0;
         const double z = normalise(x, ks.M[c], ks.SD[c]);
         b = __double2int_rz(__dmul_rn(__ddiv_rn(__dsub_rn(z, ks.lo[c]), __dsub_rn(ks.hi[c], ks.lo[c])), dnb));
     }
@@ -371,43 +373,33 @@ __device__ __forceinline__ void team_sync(int team, int nthreads) {
     else asm volatile("bar.sync %0, %1;" ::"r"(team + 1), "r"(nthreads) : "memory");
 }
 
-// Joint histograms of one pixel. Raising a cell from k to k+1 adds g[k] = (k+1)ln(k+1) - k ln k to the table's
-// sum of n ln n; the returning shared atomic supplies k. MI(a,b) = (S_ab - S_a - S_b + N ln N)/N (equals
-// mi.cpp:79-87 up to rounding), evaluated in exact integer arithmetic (unit 2^-43).
-template <int G>
+// Joint histograms of one pixel: fire-and-forget shared atomics build the tables (u16 cells, two per word), then the
+// team sweeps each table once, adding n ln n per non-empty cell from a fixed-point table (unit 2^-43, exact integer
+// sums, so the result does not depend on the order of the atomics) and zeroing it for its next use.
+// MI(a,b) = (S_ab - S_a - S_b + N ln N)/N equals mi.cpp:79-87 up to rounding.
+// The NT/32 warps form `teams` teams; a team owns `sets` x G histogram slots and takes every teams-th unit of work
+// (one row channel against G column channels). With two slot sets a unit costs one team barrier: unit i+1 fills the
+// other set while slower threads may still be sweeping the set of unit i.
+template <int G, int NT>
 __device__ __forceinline__ void joint_phase(const GeneralParams &p, KBSmall &ks, const uint32_t *bins, unsigned *region,
-                                            const unsigned *marg, const unsigned long long *gsm, int N, int nb, int hwn,
-                                            int teams) {
+                                            const unsigned long long *hsm, int N, int nb, int hwn, int teams, int sets) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tw = (KB_THREADS / 32) / teams, team = warp / tw;
+    const int tw = (NT / 32) / teams, team = warp / tw;
     const int tn = tw * 32, tt = tid - team * tn;
-    unsigned *th = region + team * G * hwn;
-    const int nq = p.pl.nq, nbs = p.pl.nbs;
+    const int nq = p.pl.nq;
     const int nfull = N >> 2, ntail = N & 3;
-    const double dn = static_cast<double>(N);
-    const unsigned long long Stot = p.hq[N];
     constexpr int SUBS = 4 / G;
-    auto update = [&](unsigned ca, unsigned cb, int j, unsigned long long &acc) {
-        const unsigned cell = ca + cb, sh = (cell & 1u) << 4;
-        const unsigned old = atomicAdd(&th[j * hwn + (cell >> 1)], 1u << sh);
-        const unsigned cnt = (old >> sh) & 0xffffu;
-        acc += cnt < KB_GSM ? gsm[cnt] : p.gq[cnt];
-    };
+    int set = 0;
     for (int u = team; u < 24 * SUBS; u += teams) {
         const int grp = u / SUBS, sub = (u - grp * SUBS) * G;
         int a, t0;
         group_channels(grp, a, t0);
-        if (ks.flat[a]) {  // a constant channel has MI exactly 0 with everything (mi.cpp: every ratio is 1)
-            if (tt < G) ks.mi[t0 + sub + tt] = 0.0;
-            continue;
-        }
+        if (ks.flat[a]) continue;  // a constant channel has MI exactly 0 with everything; Sab stays unused
+        unsigned *th = region + (team * sets + set) * G * hwn;
         const uint32_t *ba = bins + a * nq;
         const uint32_t *bb[G];
 #pragma unroll
         for (int j = 0; j < G; ++j) { int aa, b; task_channels(t0 + sub + j, aa, b); bb[j] = bins + b * nq; }
-        unsigned long long acc[G];
-#pragma unroll
-        for (int j = 0; j < G; ++j) acc[j] = 0ull;
         for (int q = tt; q < nfull; q += tn) {
             const uint32_t wa = ba[q];
             uint32_t wb[G];
@@ -417,7 +409,10 @@ __device__ __forceinline__ void joint_phase(const GeneralParams &p, KBSmall &ks,
             for (int k = 0; k < 4; ++k) {
                 const unsigned ca = ((wa >> (8 * k)) & 255u) * nb;
 #pragma unroll
-                for (int j = 0; j < G; ++j) update(ca, (wb[j] >> (8 * k)) & 255u, j, acc[j]);
+                for (int j = 0; j < G; ++j) {
+                    const unsigned cell = ca + ((wb[j] >> (8 * k)) & 255u);
+                    atomicAdd(&th[j * hwn + (cell >> 1)], 1u << ((cell & 1u) << 4));
+                }
             }
         }
         if (ntail && tt == 0) {
@@ -425,70 +420,84 @@ __device__ __forceinline__ void joint_phase(const GeneralParams &p, KBSmall &ks,
             for (int k = 0; k < ntail; ++k) {
                 const unsigned ca = ((wa >> (8 * k)) & 255u) * nb;
 #pragma unroll
-                for (int j = 0; j < G; ++j) update(ca, (bb[j][nfull] >> (8 * k)) & 255u, j, acc[j]);
+                for (int j = 0; j < G; ++j) {
+                    const unsigned cell = ca + ((bb[j][nfull] >> (8 * k)) & 255u);
+                    atomicAdd(&th[j * hwn + (cell >> 1)], 1u << ((cell & 1u) << 4));
+                }
             }
         }
+        team_sync(team, tn);
+        // sweep: sum n ln n over the cells, zero them
 #pragma unroll
         for (int j = 0; j < G; ++j) {
-            const unsigned long long sj = warp_sum_u64(acc[j]);
-            if (lane == 0) atomicAdd(&ks.Sj[team][j], sj);
-        }
-        team_sync(team, tn);
-        if (tt < G) {
-            const unsigned long long sab = ks.Sj[team][tt];
-            ks.Sj[team][tt] = 0ull;
-            int aa, b;
-            task_channels(t0 + sub + tt, aa, b);
-            double mi = 0.0;
-            int redo = 0;
-            if (!ks.flat[b]) {
-                const long long num = static_cast<long long>((sab + Stot) - (ks.Sm[a] + ks.Sm[b]));
-                mi = static_cast<double>(num) * (1.0 / 8796093022208.0) / dn;  // 2^-43
-                // Exactly independent tables give exactly 0 in mi.cpp (every ratio is 1.0) but rounding noise here;
-                // the P2 guards branch on such zeros, so suspiciously small values are recomputed cell by cell.
-                redo = mi != 0.0 && fabs(mi) < 1e-4 / (dn * dn);
+            uint4 *r4 = reinterpret_cast<uint4 *>(th + j * hwn);
+            unsigned long long acc = 0ull;
+            for (int k = tt; k < hwn >> 2; k += tn) {
+                const uint4 v = r4[k];
+                if ((v.x | v.y | v.z | v.w) == 0u) continue;
+                r4[k] = make_uint4(0u, 0u, 0u, 0u);
+                const unsigned wv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const unsigned c0 = wv[e] & 0xffffu, c1 = wv[e] >> 16;
+                    acc += hsm[min(c0, static_cast<unsigned>(KB_GSM - 1))];
+                    acc += hsm[min(c1, static_cast<unsigned>(KB_GSM - 1))];
+                    if (c0 >= KB_GSM) acc += p.hq[c0] - hsm[KB_GSM - 1];
+                    if (c1 >= KB_GSM) acc += p.hq[c1] - hsm[KB_GSM - 1];
+                }
             }
-            ks.mi[t0 + sub + tt] = mi;
-            ks.redo[team][tt] = redo;
+            acc = warp_sum_u64(acc);
+            if (lane == 0 && acc) atomicAdd(&ks.Sab[t0 + sub + j], acc);
         }
-        team_sync(team, tn);
-        for (int j = 0; j < G; ++j) {
-            if (!ks.redo[team][j]) continue;  // team-uniform
-            int aa, b;
-            task_channels(t0 + sub + j, aa, b);
-            double sr = 0.0;
-            for (int cell = tt; cell < nb * nb; cell += tn) {
-                const unsigned wv = th[j * hwn + (cell >> 1)];
-                const unsigned n = (cell & 1) ? (wv >> 16) : (wv & 0xffffu);
-                if (n == 0) continue;
-                const int i = cell / nb, jj = cell - i * nb;
-                const double pxv = __ddiv_rn(static_cast<double>(marg[a * nbs + i]), dn);
-                const double pyv = __ddiv_rn(static_cast<double>(marg[b * nbs + jj]), dn);
-                const double pxy = __ddiv_rn(static_cast<double>(n), dn);
-                const double pp = __dmul_rn(pxv, pyv);
-                if (pp != 0.0) sr = __dadd_rn(sr, __dmul_rn(pxy, log(__ddiv_rn(pxy, pp))));
-            }
-            sr = warp_sum(sr);
-            if (lane == 0) ks.redd[warp] = sr;
-            team_sync(team, tn);
-            if (tt == 0) {
-                double r = 0.0;
-                for (int w = 0; w < tw; ++w) r += ks.redd[team * tw + w];
-                ks.mi[t0 + sub + j] = r;
-            }
-            team_sync(team, tn);
-        }
-        {
-            uint4 *r4 = reinterpret_cast<uint4 *>(th);
-            for (int k = tt; k < (G * hwn) >> 2; k += tn) r4[k] = make_uint4(0u, 0u, 0u, 0u);
-        }
-        team_sync(team, tn);
+        if (sets == 1) team_sync(team, tn);
+        else set ^= 1;
     }
 }
 
+// Rare: recompute one pair cell by cell with the reference's expression and rounding (mi.cpp:66-87). Whole CTA.
+template <int NT>
+__device__ void exact_pair(const GeneralParams &p, KBSmall &ks, const uint32_t *bins, unsigned *region, const unsigned *marg,
+                           int t, int N, int nb) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int nq = p.pl.nq, nbs = p.pl.nbs;
+    int a, b;
+    task_channels(t, a, b);
+    const double dn = static_cast<double>(N);
+    for (int k = tid; k < (nb * nb + 1) / 2; k += NT) region[k] = 0u;
+    __syncthreads();
+    const uint8_t *ba = reinterpret_cast<const uint8_t *>(bins + a * nq), *bb = reinterpret_cast<const uint8_t *>(bins + b * nq);
+    for (int n = tid; n < N; n += NT) {
+        const unsigned cell = ba[n] * nb + bb[n];
+        atomicAdd(&region[cell >> 1], (cell & 1u) ? 0x10000u : 1u);
+    }
+    __syncthreads();
+    double sr = 0.0;
+    for (int cell = tid; cell < nb * nb; cell += NT) {
+        const unsigned wv = region[cell >> 1];
+        const unsigned n = (cell & 1) ? (wv >> 16) : (wv & 0xffffu);
+        if (n == 0) continue;
+        const int i = cell / nb, jj = cell - i * nb;
+        const double pxv = __ddiv_rn(static_cast<double>(marg[a * nbs + i]), dn);
+        const double pyv = __ddiv_rn(static_cast<double>(marg[b * nbs + jj]), dn);
+        const double pxy = __ddiv_rn(static_cast<double>(n), dn);
+        const double pp = __dmul_rn(pxv, pyv);
+        if (pp != 0.0) sr = __dadd_rn(sr, __dmul_rn(pxy, log(__ddiv_rn(pxy, pp))));
+    }
+    sr = warp_sum(sr);
+    if (lane == 0) ks.redd[warp] = sr;
+    __syncthreads();
+    if (tid == 0) {
+        double r = 0.0;
+        for (int w = 0; w < NT / 32; ++w) r += ks.redd[w];
+        ks.mi[t] = r;
+    }
+    __syncthreads();
+}
+
 // =====================================================================================================
-// KB: bins + joint histograms + MI + alpha/beta. Persistent CTAs of 512 threads.
-__global__ void __launch_bounds__(KB_THREADS, 1) dependency_kernel(const GeneralParams p) {
+// KB: bins + joint histograms + MI + alpha/beta. Persistent CTAs of NT threads (256: two per SM, 512: one per SM).
+template <int NT>
+__global__ void __launch_bounds__(NT, NT == 512 ? 1 : 2) dependency_kernel(const GeneralParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ KBSmall ks;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -504,7 +513,7 @@ __global__ void __launch_bounds__(KB_THREADS, 1) dependency_kernel(const General
     const int nq = L.nq;
     const int npix = p.nrows * W;
 
-    for (int k = tid; k < KB_GSM; k += KB_THREADS) gsm[k] = p.gq[k];
+    for (int k = tid; k < KB_GSM; k += NT) gsm[k] = p.hq[k];  // n ln n for small counts
 
     for (;;) {
         __syncthreads();
@@ -518,12 +527,11 @@ __global__ void __launch_bounds__(KB_THREADS, 1) dependency_kernel(const General
         double *rec = p.rec + static_cast<size_t>(pl) * REC_DOUBLES;
 
         // ---- per-channel constants --------------------------------------------------------------------
-        if (tid == 0) {
-            const int N = static_cast<int>(rec[REC_N]);
-            int nb = static_cast<int>(__dsqrt_rn(static_cast<double>(N)));  // mi.cpp:53-58
-            if (nb < 1) nb = 1;
-            ks.N = N;
-            ks.nb = nb;
+        const int N = static_cast<int>(rec[REC_N]);
+        int nb = static_cast<int>(__dsqrt_rn(static_cast<double>(N)));  // mi.cpp:53-58
+        if (nb < 1) nb = 1;
+        const double dnb = static_cast<double>(nb);
+        if (tid == 32) {
             // slot -> sample permutation step: adjacent slots hold samples far apart in enumeration order, so the lanes
             // of a warp rarely hit one histogram cell together even for smooth channels
             int q = static_cast<int>(0.6180339887 * N) | 1;
@@ -535,31 +543,35 @@ __global__ void __launch_bounds__(KB_THREADS, 1) dependency_kernel(const General
             }
             ks.Q = N > 1 ? q % N : 0;
             if (N > 1 && ks.Q == 0) ks.Q = 1;
+            ks.any_susp = 0;
         }
-        __syncthreads();
-        const int N = ks.N, nb = ks.nb;
-        const double dnb = static_cast<double>(nb), dn = static_cast<double>(N);
         if (tid < NCH) {
             const int c = tid;
             const double m = rec[REC_M + c], sd = rec[REC_SD + c], rlo = rec[REC_RLO + c], rhi = rec[REC_RHI + c];
             // (x-M)/SD is monotone in x, so the extremes of the normalised channel are the normalised extremes
             const double lo = normalise(rlo, m, sd), hi = normalise(rhi, m, sd);
-            ks.M[c] = m; ks.SD[c] = sd; ks.rlo[c] = rlo; ks.rhi[c] = rhi; ks.lo[c] = lo; ks.hi[c] = hi;
-            ks.flat[c] = hi == lo;
-            ks.ordered[c] = hi > lo;  // false when sigma is NaN: everything takes the exact path
-            ks.rsd[c] = 1.0 / sd;
-            ks.rr[c] = dnb / (hi - lo);
+            ks.M[c] = m; ks.SD[c] = sd; ks.lo[c] = lo; ks.hi[c] = hi;
+            const bool flat = hi == lo;
+            ks.flat[c] = flat;
+            const double rr = dnb / (hi - lo), rsd = 1.0 / sd;
+            double A = rsd * rr, Bc = (-m * rsd - lo) * rr;
+            if (flat) { A = 0.0; Bc = 0.5; }
+            if (!flat && !(hi > lo)) A = __longlong_as_double(0x7ff8000000000000ll);  // sigma is NaN: always the exact path
+            ks.A[c] = A;
+            ks.Bc[c] = Bc;
+            ks.tol[c] = 1e-9 + 1e-14 * (fabs(m * A) + fabs(Bc) + fabs(rhi * A) + fabs(rlo * A));
         }
-        for (int k = tid; k < NCH * L.nbs; k += KB_THREADS) marg[k] = 0u;
+        for (int k = tid; k < N_JOINT; k += NT) { ks.susp[k] = 0; ks.Sab[k] = 0ull; }
+        for (int k = tid; k < NCH * L.nbs; k += NT) marg[k] = 0u;
 
         // ---- accepted candidates -> idx16 (candidate numbers, any order) ---------------------------------
         {
-            const int wpt = (L.mw + KB_THREADS - 1) / KB_THREADS;
+            const int wpt = (L.mw + NT - 1) / NT;
             const int w0 = tid * wpt;
             int cnt = 0;
             for (int w = w0; w < min(w0 + wpt, L.mw); ++w) cnt += __popc(mask[w]);
             int total;
-            int off = block_exclusive_scan<KB_THREADS>(cnt, ks.wsum, &total);
+            int off = block_exclusive_scan<NT>(cnt, ks.wsum, &total);
             for (int w = w0; w < min(w0 + wpt, L.mw); ++w) {
                 unsigned bits = mask[w];
                 while (bits) {
@@ -575,7 +587,7 @@ __global__ void __launch_bounds__(KB_THREADS, 1) dependency_kernel(const General
         {
             const unsigned Q = static_cast<unsigned>(ks.Q), uN = static_cast<unsigned>(N);
             const int nqn = (N + 3) >> 2;
-            for (int q = tid; q < nqn; q += KB_THREADS) {
+            for (int q = tid; q < nqn; q += NT) {
                 uint32_t pack[NCH];
 #pragma unroll
                 for (int c = 0; c < NCH; ++c) pack[c] = 0u;
@@ -587,12 +599,16 @@ __global__ void __launch_bounds__(KB_THREADS, 1) dependency_kernel(const General
                         uint32_t g;
                         bool centre;
                         candidate_sample(t, px, py, B, P, W, H, g, centre);
+                        double x[NCH];
 #pragma unroll
                         for (int c = 0; c < NCH; ++c) {
                             const bool isc = c >= CH_COL && c < CH_COL + NC;
-                            const double x = isc ? p.col_in[static_cast<size_t>(c - CH_COL) * S + g]
-                                                 : static_cast<double>(__ldg(p.f.planes + static_cast<size_t>(c) * S + g));
-                            const int b = bin_value(x, c, ks, nb, dnb);
+                            x[c] = isc ? p.col_in[static_cast<size_t>(c - CH_COL) * S + g]
+                                       : static_cast<double>(__ldg(p.f.planes + static_cast<size_t>(c) * S + g));
+                        }
+#pragma unroll
+                        for (int c = 0; c < NCH; ++c) {
+                            const int b = bin_value(x[c], c, ks, nb, dnb);
                             pack[c] |= static_cast<uint32_t>(b) << (8 * k);
                             atomicAdd(&marg[c * L.nbs + b], 1u);
                         }
@@ -604,33 +620,53 @@ __global__ void __launch_bounds__(KB_THREADS, 1) dependency_kernel(const General
         }
         __syncthreads();
 
-        // ---- marginals: S_c = sum_i n_i ln n_i; clear the histogram region (idx16 is dead now) ---------------
-        for (int c = warp; c < NCH; c += KB_THREADS / 32) {
+        // ---- marginals: S_c = sum_i n_i ln n_i ---------------------------------------------------------------------
+        for (int c = warp; c < NCH; c += NT / 32) {
             unsigned long long s = 0ull;
             for (int i = lane; i < nb; i += 32) s += p.hq[marg[c * L.nbs + i]];
             s = warp_sum_u64(s);
             if (lane == 0) ks.Sm[c] = s;
         }
         // ---- 96 joint histograms ----------------------------------------------------------------------------------
-        // The histogram region is cut into slots of the ACTUAL table size (nb*nb u16 cells); the 16 warps split into
-        // teams, each team owns G slots and works through its share of the 96 pairs without CTA-wide barriers.
+        // The histogram region (idx16 is dead now) is cut into slots of the ACTUAL table size (nb*nb u16 cells).
         {
             const int hwn = (((nb * nb + 1) >> 1) + 3) & ~3;
             const int slots = L.region_words / hwn;
-            const int Gp = slots >= 4 ? 4 : (slots >= 2 ? 2 : 1);
-            int teams = 1;
-            while (teams * 2 <= KB_THREADS / 32 && teams * 2 * Gp <= slots) teams *= 2;
+            int Gp, sets = 1, teams = 1;
+            if (slots >= 8) {
+                Gp = 4;
+                sets = 2;
+                while (teams * 2 <= NT / 32 && teams * 2 * 8 <= slots) teams *= 2;
+            } else Gp = slots >= 4 ? 4 : (slots >= 2 ? 2 : 1);
             {
                 uint4 *r4 = reinterpret_cast<uint4 *>(region);
-                for (int k = tid; k < (teams * Gp * hwn) >> 2; k += KB_THREADS) r4[k] = make_uint4(0u, 0u, 0u, 0u);
-                if (tid < 64) (&ks.Sj[0][0])[tid] = 0ull;
+                for (int k = tid; k < (teams * sets * Gp * hwn) >> 2; k += NT) r4[k] = make_uint4(0u, 0u, 0u, 0u);
             }
             __syncthreads();
-            if (Gp == 4) joint_phase<4>(p, ks, bins, region, marg, gsm, N, nb, hwn, teams);
-            else if (Gp == 2) joint_phase<2>(p, ks, bins, region, marg, gsm, N, nb, hwn, teams);
-            else joint_phase<1>(p, ks, bins, region, marg, gsm, N, nb, hwn, teams);
+            if (Gp == 4) joint_phase<4, NT>(p, ks, bins, region, gsm, N, nb, hwn, teams, sets);
+            else if (Gp == 2) joint_phase<2, NT>(p, ks, bins, region, gsm, N, nb, hwn, teams, sets);
+            else joint_phase<1, NT>(p, ks, bins, region, gsm, N, nb, hwn, teams, sets);
         }
         __syncthreads();
+        if (tid < N_JOINT) {
+            int a, b;
+            task_channels(tid, a, b);
+            double mi = 0.0;
+            if (!ks.flat[a] && !ks.flat[b]) {  // a constant channel has MI exactly 0 with everything (mi.cpp: every ratio is 1)
+                const double dn = static_cast<double>(N);
+                const long long num = static_cast<long long>((ks.Sab[tid] + p.hq[N]) - (ks.Sm[a] + ks.Sm[b]));
+                mi = static_cast<double>(num) * (1.0 / 8796093022208.0) / dn;  // 2^-43
+                // Exactly independent tables give exactly 0 in mi.cpp (every ratio is 1.0) but rounding noise here; the
+                // P2 guards branch on such zeros, so suspiciously small values are recomputed with mi.cpp's own expression.
+                if (mi != 0.0 && fabs(mi) < 1e-4 / (dn * dn)) { ks.susp[tid] = 1; ks.any_susp = 1; }
+            }
+            ks.mi[tid] = mi;
+        }
+        __syncthreads();
+        if (ks.any_susp) {  // block-uniform, rare
+            for (int t = 0; t < N_JOINT; ++t)
+                if (ks.susp[t]) exact_pair<NT>(p, ks, bins, region, marg, t, N, nb);
+        }
 
         // ---- dependencies -> alpha, beta, W_r_c (rpf.cpp:416-487) ------------------------------------------
         cf_weights_from_mi(ks, p.flags, tid);
