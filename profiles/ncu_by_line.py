@@ -1,7 +1,8 @@
 #!/usr/bin/env python
 """Attribute an ncu SASS-level source page to CUDA source lines.
 
-usage: ncu_by_line.py <report.ncu-rep> <cubin> <kernel-substring> [top_n]
+usage: ncu_by_line.py <report.ncu-rep> <cubin> <kernel-substring> [top_n] [mangled-substring]
+(the last argument selects one template instantiation in the cubin when the kernel name alone is ambiguous)
 Joins `ncu --page source --csv` (per-SASS-instruction executed counts and stall samples) with the
 `//## File ..., line N` annotations of `nvdisasm -g` (built with -lineinfo) by instruction order."""
 import csv
@@ -15,6 +16,7 @@ from collections import defaultdict
 def main():
     rep, cubin, kern = sys.argv[1:4]
     top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
+    dkey = sys.argv[5] if len(sys.argv) > 5 else kern
     txt = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "-k", f"regex:{kern}"], capture_output=True,
                          text=True).stdout
     rows = list(csv.reader(io.StringIO(txt)))
@@ -32,7 +34,7 @@ def main():
     lines, cur, inside = [], None, False
     for ln in dis:
         if ln.startswith(".text."):
-            inside = kern in ln
+            inside = dkey in ln
             continue
         if not inside:
             continue

@@ -427,23 +427,29 @@ __device__ __forceinline__ void joint_phase(const GeneralParams &p, KBSmall &ks,
             }
         }
         team_sync(team, tn);
-        // sweep: sum n ln n over the cells, zero them
+        // sweep: sum n ln n over the cells, zero them. Counts 0 and 1 contribute nothing (n ln n = 0) and skip the lookup.
 #pragma unroll
         for (int j = 0; j < G; ++j) {
             uint4 *r4 = reinterpret_cast<uint4 *>(th + j * hwn);
             unsigned long long acc = 0ull;
             for (int k = tt; k < hwn >> 2; k += tn) {
                 const uint4 v = r4[k];
-                if ((v.x | v.y | v.z | v.w) == 0u) continue;
+                const unsigned any = v.x | v.y | v.z | v.w;
+                if (any == 0u) continue;
                 r4[k] = make_uint4(0u, 0u, 0u, 0u);
                 const unsigned wv[4] = {v.x, v.y, v.z, v.w};
+                if ((any & 0xfe00fe00u) == 0u) {  // every count below KB_GSM: shared-memory table only
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const unsigned c0 = wv[e] & 0xffffu, c1 = wv[e] >> 16;
-                    acc += hsm[min(c0, static_cast<unsigned>(KB_GSM - 1))];
-                    acc += hsm[min(c1, static_cast<unsigned>(KB_GSM - 1))];
-                    if (c0 >= KB_GSM) acc += p.hq[c0] - hsm[KB_GSM - 1];
-                    if (c1 >= KB_GSM) acc += p.hq[c1] - hsm[KB_GSM - 1];
+                    for (int e = 0; e < 4; ++e) {
+                        const unsigned c0 = wv[e] & 0xffffu, c1 = wv[e] >> 16;
+                        if (c0 > 1u) acc += hsm[c0];
+                        if (c1 > 1u) acc += hsm[c1];
+                    }
+                } else {
+                    for (int e = 0; e < 4; ++e) {
+                        const unsigned c0 = wv[e] & 0xffffu, c1 = wv[e] >> 16;
+                        acc += p.hq[c0] + p.hq[c1];
+                    }
                 }
             }
             acc = warp_sum_u64(acc);
