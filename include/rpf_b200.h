@@ -113,8 +113,9 @@ int rpf_reset_stats(rpf_ctx *ctx);
 /* Per-kernel device time (the reference bills the whole filter to one pbrt profiler category).
  * With profiling on, every kernel launch is bracketed by CUDA events on the context's stream; totals accumulate
  * until rpf_reset_stats. Kernels: per-pixel feature statistics (rpf.cpp:302-353), the fused small-neighbourhood
- * kernel, and the three kernels of the general path (membership + statistics, dependency estimation, blend). */
-enum { RPF_K_PIXEL_STATS = 0, RPF_K_FUSED = 1, RPF_K_NBH_STATS = 2, RPF_K_DEPENDENCY = 3, RPF_K_BLEND = 4, RPF_NUM_KERNELS = 5 };
+ * kernel, and the four kernels of the general path (membership, ordered statistics, dependency estimation, blend). */
+enum { RPF_K_PIXEL_STATS = 0, RPF_K_FUSED = 1, RPF_K_MEMBERSHIP = 2, RPF_K_ORDERED_STATS = 3, RPF_K_DEPENDENCY = 4, RPF_K_BLEND = 5,
+       RPF_NUM_KERNELS = 6 };
 typedef struct rpf_kernel_times_t {
     double ms[RPF_NUM_KERNELS];
     long long launches[RPF_NUM_KERNELS];

@@ -12,6 +12,7 @@
 
 #include "rpf_pixel_kernel.cuh"
 #include "rpf_general.cuh"
+#include "rpf_membership.cuh"
 
 using namespace rpf;
 
@@ -31,6 +32,9 @@ struct rpf_ctx {
     uint32_t *d_mask = nullptr;
     double *d_rec = nullptr;
     uint8_t *d_bins = nullptr;
+    float4 *d_rec16 = nullptr;     // gather-friendly copy of the 16 non-colour planes (general path), valid per upload
+    double4 *d_col4 = nullptr;     // current colours as {r,g,b,0}, rebuilt per general pass
+    bool rec16_valid = false;
     unsigned int *d_work = nullptr;
     size_t mask_bytes = 0, rec_bytes = 0, bins_bytes = 0;
     int kb_static_smem = 0, num_sms = 0;
@@ -134,6 +138,8 @@ extern "C" void rpf_destroy(rpf_ctx *ctx) {
     cudaFree(ctx->d_mask);
     cudaFree(ctx->d_rec);
     cudaFree(ctx->d_bins);
+    cudaFree(ctx->d_rec16);
+    cudaFree(ctx->d_col4);
     cudaFree(ctx->d_work);
     cudaFree(ctx->d_counters);
     cudaFree(ctx->d_dbg_n);
@@ -284,6 +290,7 @@ extern "C" int rpf_create(rpf_ctx **out, const rpf_config *cfg) {
         ctx->kb_static_smem = static_cast<int>(fa.sharedSizeBytes);
         CUC(cudaFuncSetAttribute(dependency_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  227 * 1024 - ctx->kb_static_smem - 1024));
+        CUC(cudaFuncSetAttribute(membership_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CUC(cudaFuncSetAttribute(dependency_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (228 * 1024) / 2 - ctx->kb_static_smem - 1024));
         ctx->num_sms = prop.multiProcessorCount;
@@ -309,6 +316,7 @@ static int after_upload(rpf_ctx *ctx) {
     ctx->launches++;
     CU(ctx, cudaGetLastError());
     ctx->pstat_y0 = ctx->pstat_y1 = 0;
+    ctx->rec16_valid = false;
     ctx->uploaded = true;
     return RPF_OK;
 }
@@ -437,6 +445,20 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
     if (!p.pl.bins_in_smem &&
         (rc = ensure_buffer(ctx, &ctx->d_bins, &ctx->bins_bytes, static_cast<size_t>(p.pl.kb_grid) * NCH * p.pl.nq * 4)) != RPF_OK)
         return rc;
+    if (!ctx->d_rec16) {
+        CU(ctx, cudaMalloc(&ctx->d_rec16, ctx->S * 4 * sizeof(float4)));
+        CU(ctx, cudaMalloc(&ctx->d_col4, ctx->S * sizeof(double4)));
+    }
+    if (!ctx->rec16_valid) {
+        pack_features_kernel<<<static_cast<unsigned>((4 * ctx->S + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_planes, ctx->S, ctx->d_rec16);
+        ctx->launches++;
+        ctx->rec16_valid = true;
+    }
+    pack_colors_kernel<<<static_cast<unsigned>((ctx->S + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_col[ctx->cur], ctx->S, ctx->d_col4);
+    ctx->launches++;
+    CU(ctx, cudaGetLastError());
+    p.rec16 = ctx->d_rec16;
+    p.col4 = ctx->d_col4;
     p.col_in = ctx->d_col[ctx->cur];
     p.col_out = ctx->d_col[ctx->cur ^ 1];
     p.pstat = ctx->d_pstat;
@@ -459,8 +481,28 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
         p.nrows = r0 + rows <= y1 ? static_cast<int>(rows) : y1 - r0;
         const unsigned npx = static_cast<unsigned>(p.nrows * W);
         CU(ctx, cudaMemsetAsync(ctx->d_work, 0, sizeof(unsigned int), ctx->stream));
-        prof_begin(ctx, RPF_K_NBH_STATS);
-        nbh_stats_kernel<<<npx, KA_THREADS, 0, ctx->stream>>>(p);
+        {
+            MembershipParams m{};
+            m.f = p.f;
+            m.pstat = ctx->d_pstat;
+            m.mask = ctx->d_mask;
+            m.box = box;
+            m.row0 = p.row0;
+            m.nrows = p.nrows;
+            m.mw = p.pl.mw;
+            membership_tile(box, m.tx, m.ty);
+            m.tiles_x = (W + m.tx - 1) / m.tx;
+            m.col_rows = m.ty + box - 1;
+            const size_t row_bytes = (static_cast<size_t>(ctx->cfg.spp) * NF + 2) * sizeof(double);
+            m.rb_rows = m.col_rows;
+            while (m.rb_rows > 1 && m.rb_rows * row_bytes > 100 * 1024) m.rb_rows = (m.rb_rows + 1) / 2;
+            const unsigned tiles = static_cast<unsigned>(m.tiles_x) * static_cast<unsigned>((p.nrows + m.ty - 1) / m.ty);
+            prof_begin(ctx, RPF_K_MEMBERSHIP);
+            membership_kernel<<<tiles, m.tx * m.ty, m.rb_rows * row_bytes, ctx->stream>>>(m);
+            prof_end(ctx);
+        }
+        prof_begin(ctx, RPF_K_ORDERED_STATS);
+        ordered_stats_kernel<<<(npx + KO_WARPS - 1) / KO_WARPS, KO_WARPS * 32, 0, ctx->stream>>>(p);
         prof_end(ctx);
         const unsigned gridb = npx < static_cast<unsigned>(p.pl.kb_grid) ? npx : static_cast<unsigned>(p.pl.kb_grid);
         prof_begin(ctx, RPF_K_DEPENDENCY);
@@ -470,7 +512,7 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
         prof_begin(ctx, RPF_K_BLEND);
         blend_kernel<<<npx, KC_THREADS, p.pl.kc_smem, ctx->stream>>>(p);
         prof_end(ctx);
-        ctx->launches += 3;
+        ctx->launches += 4;
         CU(ctx, cudaGetLastError());
     }
     ctx->pixels_filtered += 1ll * (y1 - y0) * W;

@@ -1,7 +1,7 @@
 // rpf_general.cuh -- the general (any neighbourhood size) RPF path: three kernels per ApplyRPFFilter pass.
 //
-//   KA  nbh_stats_kernel   3-sigma membership over the box -> per-pixel acceptance bit mask, N, and the
-//                          neighbourhood mean / sigma / min / max of all 19 channels           [rpf.cpp:556-601]
+//   KA  membership_kernel + ordered_stats_kernel (rpf_membership.cuh): 3-sigma membership over the box -> per-pixel
+//       acceptance bit mask, then N and the neighbourhood mean / sigma / min / max of all 19 channels  [rpf.cpp:556-601]
 //   KB  dependency_kernel  normalise + bin every accepted sample, 96 joint histograms in shared memory
 //                          (shared atomics), mutual information, alpha / beta / W_r_c        [rpf.cpp:603-618,356-488; mi.cpp]
 //   KC  blend_kernel       cross-bilateral weights of the P own samples against the N accepted samples, blend
@@ -12,7 +12,7 @@
 // candidate in HBM (candidate order = reference enumeration order xn, yn, sample: rpf.cpp:562-573), KB and KC
 // regenerate the sample list from it. What must follow the reference's order -- the sequential FP64 sums behind
 // mean and sigma (ops.h:111-144), whose rounding decides bin boundaries -- is done in KA by one lane per channel
-// walking the accepted samples in that order; everything else is order independent (integer counts) or differs
+// walking the accepted samples in that order (ordered_stats_kernel); everything else is order independent (integer counts) or differs
 // from the CPU at the 1e-15 level (sums of logs, sums of weights).
 #pragma once
 #include "rpf_kernels.cuh"
@@ -21,7 +21,6 @@ namespace rpf {
 
 constexpr int REC_M = 0, REC_SD = 19, REC_RLO = 38, REC_RHI = 57, REC_N = 76, REC_ALPHA = 77, REC_BETA = 80, REC_WRC = 92;
 constexpr int REC_DOUBLES = 96;  // per-pixel record in HBM scratch
-constexpr int KA_THREADS = 128, KA_STRIDE = 129;
 constexpr int KB_MAX_WARPS = 16, KB_GSM = 512;
 constexpr int KC_THREADS = 128, KC_SEG_WORDS = 128, KC_IC = 8;
 
@@ -45,6 +44,8 @@ struct GeneralParams {
     const double *col_in;
     double *col_out;
     const double *pstat;
+    const float4 *rec16;   // [S][4]: the 16 non-colour channels of each sample, slot order (rpf_kernels.cuh)
+    const double4 *col4;   // [S]: current colours {r, g, b, 0}
     // Fixed-point entropy tables (unit 2^-43): gq[k] = round(((k+1)ln(k+1) - k ln k) * 2^43), hq[n] = gq[0]+...+gq[n-1]
     // (~ n ln n). Integer sums are exact and order independent, so the atomics-ordered accumulation is deterministic.
     const unsigned long long *gq;
@@ -87,173 +88,6 @@ __device__ __forceinline__ bool candidate_sample(int t, int px, int py, int B, i
     if (xn < 0 || xn >= W || yn < 0 || yn >= H) return false;
     g = static_cast<uint32_t>((static_cast<size_t>(yn) * W + xn) * P + s);
     return true;
-}
-
-// =====================================================================================================
-// KA: membership mask + ordered statistics. One CTA of 128 threads per pixel.
-struct KASmem {
-    float sf[2][16][KA_STRIDE];   // staged non-colour channels (slot order of slot_channel), double buffered
-    double sc[2][NC][KA_STRIDE];  // staged colours
-    double mu[NF], sd3[NF];
-    int wcnt[2][4];
-    int cnt[2];
-    float redf[4][32];
-    double redd[4][6];
-};
-
-__global__ void __launch_bounds__(KA_THREADS) nbh_stats_kernel(const GeneralParams p) {
-    __shared__ KASmem sm;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int W = p.f.W, H = p.f.H, P = p.f.P;
-    const size_t S = p.f.S;
-    const int pl = blockIdx.x;
-    const int py = p.row0 + pl / W, px = pl - (pl / W) * W;
-    const size_t pix = static_cast<size_t>(py) * W + px;
-    const uint32_t base = static_cast<uint32_t>(pix * P);
-    uint32_t *mask = p.mask + static_cast<size_t>(pl) * p.pl.mw;
-
-    if (tid < 2 * NF) {
-        const double v = p.pstat[pix * 24 + tid];
-        if (tid < NF) sm.mu[tid] = v; else sm.sd3[tid - NF] = v;
-    }
-    float mn[16], mx[16];
-    double cmn[NC], cmx[NC];
-#pragma unroll
-    for (int s = 0; s < 16; ++s) { mn[s] = __int_as_float(0x7f800000); mx[s] = __int_as_float(0xff800000); }
-#pragma unroll
-    for (int k = 0; k < NC; ++k) { cmn[k] = __longlong_as_double(0x7ff0000000000000ll); cmx[k] = __longlong_as_double(0xfff0000000000000ll); }
-    double acc = 0.0, sq = 0.0;  // warp 0, lane c < 19: sequential sum and sum of squares of channel c (ops.h:111-144)
-
-    auto stage = [&](int buf, int slot, uint32_t g, const float *feat) {
-        // loads what the membership test has not loaded yet, tracks min / max, writes the staging slot
-#pragma unroll
-        for (int s = 0; s < 16; ++s) {
-            const float v = (feat && s >= 4) ? feat[s - 4] : __ldg(p.f.planes + static_cast<size_t>(slot_channel(s)) * S + g);
-            mn[s] = v < mn[s] ? v : mn[s];
-            mx[s] = mx[s] < v ? v : mx[s];
-            sm.sf[buf][s][slot] = v;
-        }
-#pragma unroll
-        for (int k = 0; k < NC; ++k) {
-            const double v = p.col_in[static_cast<size_t>(k) * S + g];
-            cmn[k] = v < cmn[k] ? v : cmn[k];
-            cmx[k] = cmx[k] < v ? v : cmx[k];
-            sm.sc[buf][k][slot] = v;
-        }
-    };
-    auto chain = [&](int buf) {
-        if (warp == 0 && lane < NCH) {
-            const int n = sm.cnt[buf];
-            const int c = lane;
-            const bool isc = c >= CH_COL && c < CH_COL + NC;
-            const double *pd = sm.sc[buf][isc ? c - CH_COL : 0];
-            const float *pf = sm.sf[buf][isc ? 0 : channel_slot(c)];
-            for (int k = 0; k < n; ++k) {  // one loop for all lanes: colour lanes read doubles, the rest floats
-                const double v = isc ? pd[k] : static_cast<double>(pf[k]);
-                acc = __dadd_rn(acc, v);
-                sq = __dadd_rn(sq, __dmul_rn(v, v));
-            }
-        }
-    };
-
-    // own samples first, unconditionally and in order (rpf.cpp:558). Every round: barrier, stage this round's accepted
-    // samples into buffer round&1, then warp 0 sums the buffer staged one round earlier (made visible by that barrier).
-    int round = 0, nacc = 0;
-    for (int s0 = 0; s0 < P; s0 += KA_THREADS, ++round) {
-        const int buf = round & 1;
-        const int n = min(KA_THREADS, P - s0);
-        __syncthreads();
-        if (tid < n) stage(buf, tid, base + s0 + tid, nullptr);
-        if (tid == 0) sm.cnt[buf] = n;
-        nacc += n;
-        if (round > 0) chain(buf ^ 1);
-    }
-    const int B = p.box, ncand = B * B * P;
-    for (int c0 = 0; c0 < ncand; c0 += KA_THREADS, ++round) {
-        const int buf = round & 1;
-        const int t = c0 + tid;
-        bool accept = false, centre = false, inb = false;
-        uint32_t g = 0;
-        float fv[NF];
-        if (t < ncand) {
-            inb = candidate_sample(t, px, py, B, P, W, H, g, centre);
-            if (inb && !centre) {
-#pragma unroll
-                for (int k = 0; k < NF; ++k) fv[k] = __ldg(p.f.planes + static_cast<size_t>(CH_FEAT + k) * S + g);
-                accept = true;
-#pragma unroll
-                for (int k = 0; k < NF; ++k) {
-                    // allLessThan(|f - mu|, 3 sigma): reject on >= ; a NaN sigma accepts (ops.h:100-107)
-                    const double d = fabs(__dsub_rn(static_cast<double>(fv[k]), sm.mu[k]));
-                    if (d >= sm.sd3[k]) accept = false;
-                }
-            }
-        }
-        const unsigned m = __ballot_sync(0xffffffffu, accept);
-        const unsigned mc = __ballot_sync(0xffffffffu, inb && centre);
-        if (lane == 0) {
-            sm.wcnt[buf][warp] = __popc(m);
-            if ((c0 >> 5) + warp < p.pl.mw) mask[(c0 >> 5) + warp] = m | mc;  // own samples count as members for KB / KC
-        }
-        __syncthreads();
-        int off = 0, tot = 0;
-#pragma unroll
-        for (int w = 0; w < 4; ++w) {
-            const int c = sm.wcnt[buf][w];
-            if (w < warp) off += c;
-            tot += c;
-        }
-        if (accept) stage(buf, off + __popc(m & ((1u << lane) - 1u)), g, fv);
-        if (tid == 0) sm.cnt[buf] = tot;
-        nacc += tot;
-        chain(buf ^ 1);  // the round staged before this one (visible since the barrier above)
-    }
-    // zero the mask tail (mw is rounded up)
-    for (int w = ((ncand + KA_THREADS - 1) / KA_THREADS) * 4 + tid; w < p.pl.mw; w += KA_THREADS) mask[w] = 0u;
-    __syncthreads();
-    chain((round - 1) & 1);
-
-    // min / max over the CTA
-#pragma unroll
-    for (int s = 0; s < 16; ++s) {
-        const float a = warp_min_f(mn[s]), b = warp_max_f(mx[s]);
-        if (lane == 0) { sm.redf[warp][s] = a; sm.redf[warp][16 + s] = b; }
-    }
-#pragma unroll
-    for (int k = 0; k < NC; ++k) {
-        const double a = warp_min(cmn[k]), b = warp_max(cmx[k]);
-        if (lane == 0) { sm.redd[warp][k] = a; sm.redd[warp][NC + k] = b; }
-    }
-    __syncthreads();
-    const int N = nacc;
-    double *rec = p.rec + static_cast<size_t>(pl) * REC_DOUBLES;
-    if (tid < NCH) {
-        const int c = tid;
-        const double n = static_cast<double>(N);
-        const double m = __ddiv_rn(acc, n);
-        double var = __dsub_rn(__ddiv_rn(sq, n), __dmul_rn(m, m));
-        if ((p.flags & FLAG_P3) && !(var > 0.0) && var == var) var = 0.0;  // P3: sqrt(max(0,var)), NaN kept
-        double lo, hi;
-        if (c >= CH_COL && c < CH_COL + NC) {
-            const int k = c - CH_COL;
-            lo = fmin(fmin(sm.redd[0][k], sm.redd[1][k]), fmin(sm.redd[2][k], sm.redd[3][k]));
-            hi = fmax(fmax(sm.redd[0][NC + k], sm.redd[1][NC + k]), fmax(sm.redd[2][NC + k], sm.redd[3][NC + k]));
-        } else {
-            const int s = channel_slot(c);
-            lo = fminf(fminf(sm.redf[0][s], sm.redf[1][s]), fminf(sm.redf[2][s], sm.redf[3][s]));
-            hi = fmaxf(fmaxf(sm.redf[0][16 + s], sm.redf[1][16 + s]), fmaxf(sm.redf[2][16 + s], sm.redf[3][16 + s]));
-        }
-        rec[REC_M + c] = m;
-        rec[REC_SD + c] = __dsqrt_rn(var);
-        rec[REC_RLO + c] = lo;
-        rec[REC_RHI + c] = hi;
-    }
-    if (tid == 32) {
-        rec[REC_N] = static_cast<double>(N);
-        atomicAdd(&p.counters[0], static_cast<unsigned long long>(N));
-        atomicMin(&p.counters[2], static_cast<unsigned long long>(N));
-        atomicMax(&p.counters[3], static_cast<unsigned long long>(N));
-    }
 }
 
 // =====================================================================================================
@@ -606,11 +440,16 @@ __global__ void __launch_bounds__(NT, NT == 512 ? 1 : 2) dependency_kernel(const
                         bool centre;
                         candidate_sample(t, px, py, B, P, W, H, g, centre);
                         double x[NCH];
+                        {
+                            const float4 *r16 = p.rec16 + static_cast<size_t>(g) * 4;
+                            const float4 f0 = __ldg(r16), f1 = __ldg(r16 + 1), f2 = __ldg(r16 + 2), f3 = __ldg(r16 + 3);
+                            const double4 cc = p.col4[g];
+                            const float fs[16] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w,
+                                                  f2.x, f2.y, f2.z, f2.w, f3.x, f3.y, f3.z, f3.w};
+                            x[0] = fs[0]; x[1] = fs[1];
+                            x[2] = cc.x; x[3] = cc.y; x[4] = cc.z;
 #pragma unroll
-                        for (int c = 0; c < NCH; ++c) {
-                            const bool isc = c >= CH_COL && c < CH_COL + NC;
-                            x[c] = isc ? p.col_in[static_cast<size_t>(c - CH_COL) * S + g]
-                                       : static_cast<double>(__ldg(p.f.planes + static_cast<size_t>(c) * S + g));
+                            for (int c = 5; c < NCH; ++c) x[c] = fs[c - 3];
                         }
 #pragma unroll
                         for (int c = 0; c < NCH; ++c) {
@@ -730,16 +569,15 @@ __global__ void __launch_bounds__(KC_THREADS, 4) blend_kernel(const GeneralParam
     }
     __syncthreads();
     auto load_z = [&](uint32_t g, double *z, double *col) {
+        const float4 *r16 = p.rec16 + static_cast<size_t>(g) * 4;
+        const float4 f0 = __ldg(r16), f1 = __ldg(r16 + 1), f2 = __ldg(r16 + 2), f3 = __ldg(r16 + 3);
+        const double4 cc = p.col4[g];
+        const float fs[16] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w, f2.x, f2.y, f2.z, f2.w, f3.x, f3.y, f3.z, f3.w};
+        col[0] = cc.x; col[1] = cc.y; col[2] = cc.z;
 #pragma unroll
         for (int k = 0; k < NWZ; ++k) {
-            double x;
-            if (k < 3) {
-                x = p.col_in[static_cast<size_t>(k) * S + g];
-                col[k] = x;
-            } else {
-                const int c = k < 15 ? CH_FEAT + (k - 3) : CH_POS + (k - 15);
-                x = static_cast<double>(__ldg(p.f.planes + static_cast<size_t>(c) * S + g));
-            }
+            // z order: colour, features (slots 4..15), position (slots 0, 1)
+            const double x = k < 3 ? col[k] : static_cast<double>(k < 15 ? fs[k + 1] : fs[k - 15]);
             z[k] = (x - ks.mz[k]) * ks.scl[k];
         }
     };

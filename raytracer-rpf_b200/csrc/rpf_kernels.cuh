@@ -46,6 +46,27 @@ __global__ void pixel_stats_kernel(FrameView f, int y0, int y1, double *__restri
 }
 
 // ---------------------------------------------------------------------------------------------------
+// Gather-friendly copies for the general path. The planes are structure-of-arrays (one coalesced stream per channel
+// when neighbouring pixels are read together); the general path instead gathers scattered accepted samples, where a
+// sample's channels should share sectors: rec16[g] = the 16 non-colour channels of sample g in slot order (64 B, built
+// once per upload), col4[g] = {r, g, b, 0} of the current colours as doubles (32 B, rebuilt per pass).
+__global__ void pack_features_kernel(const float *__restrict__ planes, size_t S, float4 *__restrict__ rec16) {
+    const size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
+    if (i >= 4 * S) return;
+    const size_t g = i >> 2;
+    const int q = static_cast<int>(i & 3);
+    float v[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) v[k] = planes[static_cast<size_t>(slot_channel(4 * q + k)) * S + g];
+    rec16[i] = make_float4(v[0], v[1], v[2], v[3]);
+}
+__global__ void pack_colors_kernel(const double *__restrict__ col, size_t S, double4 *__restrict__ col4) {
+    const size_t g = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
+    if (g >= S) return;
+    col4[g] = make_double4(col[g], col[S + g], col[2 * S + g], 0.0);
+}
+
+// ---------------------------------------------------------------------------------------------------
 // helpers
 
 __device__ __forceinline__ double warp_min(double v) {

@@ -1,0 +1,208 @@
+// rpf_membership.cuh -- first stage of the general path, two kernels:
+//
+//   membership_kernel     3-sigma membership of every candidate of every pixel (rpf.cpp:556-586, ops.h:100-107) ->
+//                         per-pixel acceptance bit mask in HBM, bit t = candidate t in reference enumeration order
+//                         (xn ascending, yn ascending, sample: rpf.cpp:562-573). A CTA owns a TX x TY tile of pixels,
+//                         one THREAD per pixel with that pixel's mean / 3 sigma in registers; the union of the tile's
+//                         boxes streams through shared memory one column of neighbour pixels at a time, so a sample's
+//                         12 features are fetched from L2 once per tile instead of once per pixel.
+//   ordered_stats_kernel  neighbourhood mean / sigma / min / max of all 19 channels (rpf.cpp:596-601). The sums must
+//                         follow the reference's order (ops.h:111-144 sums sequentially; the rounding of mean and sigma
+//                         decides histogram bin boundaries later), so one WARP per pixel walks the mask in order with
+//                         one lane per channel and two dependent FP64 add chains per lane; 64 warps per SM hide the
+//                         add latency.
+#pragma once
+#include "rpf_general.cuh"
+
+namespace rpf {
+
+constexpr int KM_MAX_THREADS = 128;
+
+// Tile of pixels per CTA for a box size: large boxes amortise the halo over 128 pixels, small ones waste less on it.
+__host__ __device__ inline void membership_tile(int box, int &tx, int &ty) {
+    if (box >= 33) { tx = 16; ty = 8; }
+    else if (box >= 13) { tx = 8; ty = 8; }
+    else { tx = 8; ty = 4; }
+}
+
+struct MembershipParams {
+    FrameView f;
+    const double *pstat;   // [W*H][24] per-pixel feature mean[12], 3 sigma[12]
+    uint32_t *mask;        // [chunk pixels][mw]
+    int box, row0, nrows, mw;
+    int tx, ty, tiles_x;   // tile shape and tiles per row
+    int col_rows;          // ty + box - 1: neighbour-pixel rows per column of the tile's union
+    int rb_rows;           // rows staged in shared memory at a time (col_rows unless spp is very large)
+};
+
+__global__ void __launch_bounds__(KM_MAX_THREADS) membership_kernel(const MembershipParams p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    // [col_rows][P][12] features of one column of neighbour pixels; rows padded by two doubles so that the 2-4 rows a
+    // warp reads at once fall into different banks
+    double *col = reinterpret_cast<double *>(smem);
+    const int RS = p.f.P * NF + 2;
+    const int tid = threadIdx.x;
+    const int W = p.f.W, H = p.f.H, P = p.f.P, B = p.box, bd = (B - 1) / 2;
+    const size_t S = p.f.S;
+    const int tile_x = blockIdx.x % p.tiles_x, tile_y = blockIdx.x / p.tiles_x;
+    const int x0 = tile_x * p.tx, y0 = p.row0 + tile_y * p.ty;
+    const int lx = tid % p.tx, ly = tid / p.tx;
+    const int px = x0 + lx, py = y0 + ly;
+    const bool live = px < W && py < p.row0 + p.nrows;
+
+    double mu[NF], sd3[NF];
+    if (live) {
+        const double *ps = p.pstat + (static_cast<size_t>(py) * W + px) * 24;
+#pragma unroll
+        for (int k = 0; k < NF; ++k) { mu[k] = ps[k]; sd3[k] = ps[NF + k]; }
+    } else {
+#pragma unroll
+        for (int k = 0; k < NF; ++k) { mu[k] = 0.0; sd3[k] = 0.0; }
+    }
+    uint32_t *mrow = p.mask + (static_cast<size_t>(py - p.row0) * W + px) * p.mw;
+    uint32_t buf = 0;
+    int nbits = 0, wi = 0;
+
+    const int nrows = p.col_rows;  // rows of neighbour pixels a column holds for this tile: yn = y0 - bd + r
+    for (int xn = x0 - bd; xn <= x0 + p.tx - 1 + bd; ++xn) {
+        // a column is staged in blocks of rb_rows rows (one block unless spp is very large); ascending blocks keep
+        // every pixel's candidates in enumeration order
+        for (int r0 = 0; r0 < nrows; r0 += p.rb_rows) {
+            const int rbn = min(p.rb_rows, nrows - r0);
+            const int nsamp = rbn * P;
+            __syncthreads();  // previous block fully consumed
+            if (xn >= 0 && xn < W) {
+                for (int i = tid; i < nsamp * NF; i += blockDim.x) {
+                    const int k = i / nsamp, j = i - k * nsamp;  // feature-major: consecutive threads, consecutive samples
+                    const int r = j / P, s = j - r * P;
+                    const int yn = y0 - bd + r0 + r;
+                    double v = 0.0;
+                    if (yn >= 0 && yn < H)
+                        v = static_cast<double>(__ldg(p.f.planes + static_cast<size_t>(CH_FEAT + k) * S +
+                                                      (static_cast<size_t>(yn) * W + xn) * P + s));
+                    col[r * RS + s * NF + k] = v;
+                }
+            }
+            __syncthreads();
+            // this pixel's box covers columns px-bd .. px+bd and rows ly .. ly+B-1 of the column
+            if (live && xn >= px - bd && xn <= px + bd) {
+                const bool xin = xn >= 0 && xn < W;
+                const int by_lo = max(0, r0 - ly), by_hi = min(B, r0 + rbn - ly);
+                for (int by = by_lo; by < by_hi; ++by) {
+                    const int yn = py - bd + by;
+                    const bool inb = xin && yn >= 0 && yn < H;
+                    const bool centre = xn == px && yn == py;
+                    const double *cp = col + (ly + by - r0) * RS;
+                    for (int s = 0; s < P; ++s, cp += NF) {
+                        bool acc = inb;
+                        if (inb && !centre) {
+                            // allLessThan(|f - mu|, 3 sigma): reject on >= ; a NaN sigma accepts (ops.h:100-107)
+#pragma unroll
+                            for (int k = 0; k < 4; ++k)
+                                if (fabs(__dsub_rn(cp[k], mu[k])) >= sd3[k]) acc = false;
+                            // most candidates fail early; skip the rest when no lane running here is still in
+                            if (__ballot_sync(__activemask(), acc)) {
+#pragma unroll
+                                for (int k = 4; k < NF; ++k)
+                                    if (fabs(__dsub_rn(cp[k], mu[k])) >= sd3[k]) acc = false;
+                            }
+                        }
+                        buf |= static_cast<uint32_t>(acc) << nbits;
+                        if (++nbits == 32) { mrow[wi++] = buf; buf = 0; nbits = 0; }
+                    }
+                }
+            }
+        }
+    }
+    if (live) {
+        if (nbits) mrow[wi++] = buf;
+        for (; wi < p.mw; ++wi) mrow[wi] = 0u;
+    }
+}
+
+// =====================================================================================================
+constexpr int KO_WARPS = 4;  // pixels per CTA of the ordered statistics kernel
+
+__global__ void __launch_bounds__(KO_WARPS * 32) ordered_stats_kernel(const GeneralParams p) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int W = p.f.W, P = p.f.P, B = p.box, bd = (B - 1) / 2;
+    const int pl = blockIdx.x * KO_WARPS + warp;
+    if (pl >= p.nrows * W) return;
+    const int py = p.row0 + pl / W, px = pl - (pl / W) * W;
+    const size_t pix = static_cast<size_t>(py) * W + px;
+    const uint32_t base = static_cast<uint32_t>(pix * P);
+    const uint32_t *mask = p.mask + static_cast<size_t>(pl) * p.pl.mw;
+
+    // lane c < 19 owns channel c: its plane pointer, the running sums (ops.h:111-144 order) and extremes
+    const int c = lane < NCH ? lane : 0;
+    const bool isc = c >= CH_COL && c < CH_COL + NC;
+    // gather-friendly copies: 16 lanes read one 64-byte record, the 3 colour lanes one 32-byte record
+    const float *pf = reinterpret_cast<const float *>(p.rec16) + (isc ? 0 : channel_slot(c));
+    const double *pd = reinterpret_cast<const double *>(p.col4) + (isc ? c - CH_COL : 0);
+    double acc = 0.0, sq = 0.0;
+    double lo = __longlong_as_double(0x7ff0000000000000ll), hi = __longlong_as_double(0xfff0000000000000ll);
+    auto take = [&](double v) {
+        acc = __dadd_rn(acc, v);
+        sq = __dadd_rn(sq, __dmul_rn(v, v));
+        lo = v < lo ? v : lo;
+        hi = hi < v ? v : hi;
+    };
+    auto fetch = [&](uint32_t g) { return isc ? pd[static_cast<size_t>(g) * 4] : static_cast<double>(__ldg(pf + static_cast<size_t>(g) * 16)); };
+
+    // own samples first, unconditionally and in order (rpf.cpp:558)
+    int N = P;
+    for (int s = 0; s < P; ++s) take(fetch(base + s));
+
+    // then the mask in candidate order, skipping the centre pixel (already taken). Per mask word the 32 lanes decode
+    // one candidate each and compact the accepted sample indices (in order) into a per-warp list; then every lane
+    // walks that list for its own channel, loads batched eight ahead of the dependent adds.
+    __shared__ uint32_t glist[KO_WARPS][32];
+    const int BP = B * P;
+    const int tc0 = (bd * B + bd) * P;  // candidate numbers of the centre pixel: [tc0, tc0 + P)
+    const int nwords = (B * BP + 31) >> 5;
+    for (int w = 0; w < nwords; ++w) {
+        unsigned bits = mask[w];
+        if (bits == 0u) continue;
+        const int t = w * 32 + lane;
+        const bool on = ((bits >> lane) & 1u) && !(t >= tc0 && t < tc0 + P);
+        const unsigned eff = __ballot_sync(0xffffffffu, on);
+        if (eff == 0u) continue;
+        if (on) {
+            const int bx = t / BP, r = t - bx * BP, by = r / P, s = r - by * P;
+            glist[warp][__popc(eff & ((1u << lane) - 1u))] =
+                static_cast<uint32_t>((static_cast<size_t>(py - bd + by) * W + (px - bd + bx)) * P + s);
+        }
+        __syncwarp();
+        const int cnt = __popc(eff);
+        for (int i0 = 0; i0 < cnt; i0 += 8) {
+            double v[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = fetch(glist[warp][min(i0 + i, cnt - 1)]);
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                if (i0 + i < cnt) take(v[i]);
+        }
+        N += cnt;
+        __syncwarp();
+    }
+
+    double *rec = p.rec + static_cast<size_t>(pl) * REC_DOUBLES;
+    if (lane < NCH) {
+        const double n = static_cast<double>(N);
+        const double m = __ddiv_rn(acc, n);
+        double var = __dsub_rn(__ddiv_rn(sq, n), __dmul_rn(m, m));
+        if ((p.flags & FLAG_P3) && !(var > 0.0) && var == var) var = 0.0;  // P3: sqrt(max(0,var)), NaN kept
+        rec[REC_M + lane] = m;
+        rec[REC_SD + lane] = __dsqrt_rn(var);
+        rec[REC_RLO + lane] = lo;
+        rec[REC_RHI + lane] = hi;
+    }
+    if (lane == 0) {
+        rec[REC_N] = static_cast<double>(N);
+        atomicAdd(&p.counters[0], static_cast<unsigned long long>(N));
+        atomicMin(&p.counters[2], static_cast<unsigned long long>(N));
+        atomicMax(&p.counters[3], static_cast<unsigned long long>(N));
+    }
+}
+
+}  // namespace rpf

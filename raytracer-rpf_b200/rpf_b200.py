@@ -42,11 +42,12 @@ class Stats(C.Structure):
                 ("last_filter_ms", C.c_double)]
 
 
-KERNEL_NAMES = ["pixel_stats_kernel", "rpf_pixel_kernel", "nbh_stats_kernel", "dependency_kernel", "blend_kernel"]
+KERNEL_NAMES = ["pixel_stats_kernel", "rpf_pixel_kernel", "membership_kernel", "ordered_stats_kernel", "dependency_kernel",
+                "blend_kernel"]
 
 
 class KernelTimes(C.Structure):
-    _fields_ = [("ms", C.c_double * 5), ("launches", C.c_longlong * 5)]
+    _fields_ = [("ms", C.c_double * 6), ("launches", C.c_longlong * 6)]
 
 
 _lib = None
@@ -205,7 +206,7 @@ class RPFFilter:
         """{kernel name: (total ms, launches)} since the last reset_stats; needs set_profiling(True)."""
         kt = KernelTimes()
         self._check(lib().rpf_get_kernel_times(self._h, C.byref(kt)))
-        return {KERNEL_NAMES[k]: (kt.ms[k], kt.launches[k]) for k in range(5)}
+        return {KERNEL_NAMES[k]: (kt.ms[k], kt.launches[k]) for k in range(len(KERNEL_NAMES))}
 
     def reset_stats(self):
         self._check(lib().rpf_reset_stats(self._h))
