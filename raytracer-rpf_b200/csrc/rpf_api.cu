@@ -286,12 +286,12 @@ extern "C" int rpf_create(rpf_ctx **out, const rpf_config *cfg) {
     CUC(cudaFuncSetAttribute(rpf_pixel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
     {
         cudaFuncAttributes fa;
-        CUC(cudaFuncGetAttributes(&fa, dependency_kernel<512>));
+        CUC(cudaFuncGetAttributes(&fa, dependency_kernel<1024>));
         ctx->kb_static_smem = static_cast<int>(fa.sharedSizeBytes);
-        CUC(cudaFuncSetAttribute(dependency_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        CUC(cudaFuncSetAttribute(dependency_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  227 * 1024 - ctx->kb_static_smem - 1024));
         CUC(cudaFuncSetAttribute(membership_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        CUC(cudaFuncSetAttribute(dependency_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        CUC(cudaFuncSetAttribute(dependency_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (228 * 1024) / 2 - ctx->kb_static_smem - 1024));
         ctx->num_sms = prop.multiProcessorCount;
         CUC(cudaMalloc(&ctx->d_work, sizeof(unsigned int)));
@@ -379,7 +379,7 @@ static bool plan_general(long long ncap, int spp, int static_smem, GeneralPlan &
     for (int v = 0; v < 2; ++v) {
         const int avail = (limit[v] - L.off_region) & ~15;
         if (avail < atleast(v == 0 ? 2 : 1)) continue;
-        L.nt = v == 0 ? 256 : 512;
+        L.nt = v == 0 ? 512 : 1024;
         L.bins_in_smem = bins_bytes + atleast(8) <= avail;
         const int region = L.bins_in_smem ? avail - bins_bytes : avail;
         L.off_bins = L.bins_in_smem ? L.off_region + region : 0;
@@ -435,8 +435,8 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
     if (rows < 1) rows = 1;
     if (rows > y1 - y0) rows = y1 - y0;
     int occ = 0;
-    if (p.pl.nt == 256) CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dependency_kernel<256>, 256, p.pl.kb_smem));
-    else CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dependency_kernel<512>, 512, p.pl.kb_smem));
+    if (p.pl.nt == 512) CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dependency_kernel<512>, 512, p.pl.kb_smem));
+    else CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dependency_kernel<1024>, 1024, p.pl.kb_smem));
     if (occ < 1) return fail(ctx, RPF_ERR_CUDA, "dependency kernel does not fit on an SM with %d bytes of shared memory", p.pl.kb_smem);
     const long long chunk_px = rows * W;
     p.pl.kb_grid = static_cast<int>(chunk_px < 1ll * occ * ctx->num_sms ? chunk_px : 1ll * occ * ctx->num_sms);
@@ -506,8 +506,8 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
         prof_end(ctx);
         const unsigned gridb = npx < static_cast<unsigned>(p.pl.kb_grid) ? npx : static_cast<unsigned>(p.pl.kb_grid);
         prof_begin(ctx, RPF_K_DEPENDENCY);
-        if (p.pl.nt == 256) dependency_kernel<256><<<gridb, 256, p.pl.kb_smem, ctx->stream>>>(p);
-        else dependency_kernel<512><<<gridb, 512, p.pl.kb_smem, ctx->stream>>>(p);
+        if (p.pl.nt == 512) dependency_kernel<512><<<gridb, 512, p.pl.kb_smem, ctx->stream>>>(p);
+        else dependency_kernel<1024><<<gridb, 1024, p.pl.kb_smem, ctx->stream>>>(p);
         prof_end(ctx);
         prof_begin(ctx, RPF_K_BLEND);
         blend_kernel<<<npx, KC_THREADS, p.pl.kc_smem, ctx->stream>>>(p);

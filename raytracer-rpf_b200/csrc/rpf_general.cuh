@@ -21,7 +21,7 @@ namespace rpf {
 
 constexpr int REC_M = 0, REC_SD = 19, REC_RLO = 38, REC_RHI = 57, REC_N = 76, REC_ALPHA = 77, REC_BETA = 80, REC_WRC = 92;
 constexpr int REC_DOUBLES = 96;  // per-pixel record in HBM scratch
-constexpr int KB_MAX_WARPS = 16, KB_GSM = 512;
+constexpr int KB_MAX_WARPS = 32, KB_GSM = 512;
 constexpr int KC_THREADS = 128, KC_SEG_WORDS = 128, KC_IC = 8;
 
 struct GeneralPlan {
@@ -335,9 +335,10 @@ __device__ void exact_pair(const GeneralParams &p, KBSmall &ks, const uint32_t *
 }
 
 // =====================================================================================================
-// KB: bins + joint histograms + MI + alpha/beta. Persistent CTAs of NT threads (256: two per SM, 512: one per SM).
+// KB: bins + joint histograms + MI + alpha/beta. Persistent CTAs of NT threads (512: two per SM, 1024: one per SM),
+// 64 registers per thread so that 32 warps per SM hide the shared-memory latencies.
 template <int NT>
-__global__ void __launch_bounds__(NT, NT == 512 ? 1 : 2) dependency_kernel(const GeneralParams p) {
+__global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(const GeneralParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ KBSmall ks;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -423,44 +424,34 @@ __global__ void __launch_bounds__(NT, NT == 512 ? 1 : 2) dependency_kernel(const
         }
         __syncthreads();
 
-        // ---- normalise + bin: four slots per thread, packed u8 bins, marginal counts ----------------------
+        // ---- normalise + bin: one slot per thread, u8 bins (channel-major byte arrays), marginal counts ------------
         {
             const unsigned Q = static_cast<unsigned>(ks.Q), uN = static_cast<unsigned>(N);
-            const int nqn = (N + 3) >> 2;
-            for (int q = tid; q < nqn; q += NT) {
-                uint32_t pack[NCH];
+            uint8_t *bin8 = reinterpret_cast<uint8_t *>(bins);
+            const int cstride = nq * 4;
+            for (unsigned m = tid; m < uN; m += NT) {
+                const int t = idx16[(m * Q) % uN];
+                uint32_t g;
+                bool centre;
+                candidate_sample(t, px, py, B, P, W, H, g, centre);
+                const float4 *r16 = p.rec16 + static_cast<size_t>(g) * 4;
+                const double4 cc = p.col4[g];
+                auto put = [&](int c, double x) {
+                    const int b = bin_value(x, c, ks, nb, dnb);
+                    bin8[c * cstride + m] = static_cast<uint8_t>(b);
+                    atomicAdd(&marg[c * L.nbs + b], 1u);
+                };
+                put(CH_COL + 0, cc.x);
+                put(CH_COL + 1, cc.y);
+                put(CH_COL + 2, cc.z);
 #pragma unroll
-                for (int c = 0; c < NCH; ++c) pack[c] = 0u;
-#pragma unroll 1
-                for (int k = 0; k < 4; ++k) {
-                    const unsigned m = 4u * q + k;
-                    if (m < uN) {
-                        const int t = idx16[(m * Q) % uN];
-                        uint32_t g;
-                        bool centre;
-                        candidate_sample(t, px, py, B, P, W, H, g, centre);
-                        double x[NCH];
-                        {
-                            const float4 *r16 = p.rec16 + static_cast<size_t>(g) * 4;
-                            const float4 f0 = __ldg(r16), f1 = __ldg(r16 + 1), f2 = __ldg(r16 + 2), f3 = __ldg(r16 + 3);
-                            const double4 cc = p.col4[g];
-                            const float fs[16] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w,
-                                                  f2.x, f2.y, f2.z, f2.w, f3.x, f3.y, f3.z, f3.w};
-                            x[0] = fs[0]; x[1] = fs[1];
-                            x[2] = cc.x; x[3] = cc.y; x[4] = cc.z;
-#pragma unroll
-                            for (int c = 5; c < NCH; ++c) x[c] = fs[c - 3];
-                        }
-#pragma unroll
-                        for (int c = 0; c < NCH; ++c) {
-                            const int b = bin_value(x[c], c, ks, nb, dnb);
-                            pack[c] |= static_cast<uint32_t>(b) << (8 * k);
-                            atomicAdd(&marg[c * L.nbs + b], 1u);
-                        }
-                    }
+                for (int q = 0; q < 4; ++q) {
+                    const float4 f = __ldg(r16 + q);
+                    put(slot_channel(4 * q + 0), f.x);
+                    put(slot_channel(4 * q + 1), f.y);
+                    put(slot_channel(4 * q + 2), f.z);
+                    put(slot_channel(4 * q + 3), f.w);
                 }
-#pragma unroll
-                for (int c = 0; c < NCH; ++c) bins[c * nq + q] = pack[c];
             }
         }
         __syncthreads();
@@ -482,6 +473,7 @@ __global__ void __launch_bounds__(NT, NT == 512 ? 1 : 2) dependency_kernel(const
                 Gp = 4;
                 sets = 2;
                 while (teams * 2 <= NT / 32 && teams * 2 * 8 <= slots) teams *= 2;
+                if (teams > 8 && teams < NT / 32) teams = 8;  // multi-warp teams use named barriers 1..15
             } else Gp = slots >= 4 ? 4 : (slots >= 2 ? 2 : 1);
             {
                 uint4 *r4 = reinterpret_cast<uint4 *>(region);
