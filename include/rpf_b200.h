@@ -45,6 +45,9 @@ typedef enum rpf_status {
 /* Testing / tuning switch, may be OR-ed into flags: route every box size through the general three-kernel path
  * (membership mask in HBM, shared-atomic histograms) even where the fused shared-memory kernel would serve it. */
 #define RPF_FLAG_FORCE_GENERAL 0x200
+/* Same, and use the large-neighbourhood dependency kernel (u16 bins, u32 cells, slabbed tables: what box*box*spp > 65,535
+ * takes, e.g. 64 spp with boxes 35 / 55) for every box size. Implies RPF_FLAG_FORCE_GENERAL. */
+#define RPF_FLAG_FORCE_LARGE 0x400
 
 typedef struct rpf_ctx rpf_ctx;
 

@@ -13,6 +13,7 @@
 #include "rpf_pixel_kernel.cuh"
 #include "rpf_general.cuh"
 #include "rpf_membership.cuh"
+#include "rpf_large.cuh"
 
 using namespace rpf;
 
@@ -27,7 +28,11 @@ struct rpf_ctx {
     int pstat_y0 = 0, pstat_y1 = 0; // rows with valid per-pixel statistics
     double *d_gtab = nullptr, *d_gpre = nullptr, *d_hln = nullptr;
     unsigned long long *d_gq = nullptr, *d_hq = nullptr;
-    int gtab_n = 0;
+    unsigned long long *d_hql = nullptr;  // n ln n in units of 2^-38 for the large-neighbourhood kernel (rpf_large.cuh)
+    int gtab_n = 0, hql_n = 0;
+    uint8_t *d_big = nullptr;
+    size_t big_bytes = 0;
+    bool force_large = false;
     // general path (rpf_general.cuh): per-chunk scratch in HBM
     uint32_t *d_mask = nullptr;
     double *d_rec = nullptr;
@@ -119,7 +124,9 @@ static bool plan_smem(long long ncap, int spp, int limit, SmemLayout &L) {
 
 static const int kSmemLimit = 227 * 1024 - 6 * 1024;  // minus static PixelSmall and the per-CTA reserve
 
-extern "C" int rpf_max_neighbourhood(void) { return 65535; }
+static const int kLargeMaxCandidates = 1 << 20;  // 2^-38 fixed-point entropy sums stay below 2^64 (rpf_large.cuh)
+
+extern "C" int rpf_max_neighbourhood(void) { return kLargeMaxCandidates; }
 
 extern "C" const char *rpf_last_error(const rpf_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
 
@@ -135,6 +142,8 @@ extern "C" void rpf_destroy(rpf_ctx *ctx) {
     cudaFree(ctx->d_hln);
     cudaFree(ctx->d_gq);
     cudaFree(ctx->d_hq);
+    cudaFree(ctx->d_hql);
+    cudaFree(ctx->d_big);
     cudaFree(ctx->d_mask);
     cudaFree(ctx->d_rec);
     cudaFree(ctx->d_bins);
@@ -253,7 +262,7 @@ extern "C" int rpf_create(rpf_ctx **out, const rpf_config *cfg) {
                     cfg->device);
     rpf_ctx *ctx = new rpf_ctx;
     ctx->cfg = *cfg;
-    ctx->cfg.flags &= ~RPF_FLAG_FORCE_GENERAL;
+    ctx->cfg.flags &= ~(RPF_FLAG_FORCE_GENERAL | RPF_FLAG_FORCE_LARGE);
     if (ctx->cfg.flags == 0) ctx->cfg.flags = RPF_FLAGS_DEFINED;
     ctx->S = 1ull * cfg->width * cfg->height * cfg->spp;
     ctx->npix = cfg->width * cfg->height;
@@ -295,7 +304,11 @@ extern "C" int rpf_create(rpf_ctx **out, const rpf_config *cfg) {
                                  (228 * 1024) / 2 - ctx->kb_static_smem - 1024));
         ctx->num_sms = prop.multiProcessorCount;
         CUC(cudaMalloc(&ctx->d_work, sizeof(unsigned int)));
-        ctx->force_general = (cfg->flags & RPF_FLAG_FORCE_GENERAL) || (getenv("RPF_FORCE_GENERAL") && atoi(getenv("RPF_FORCE_GENERAL")));
+        ctx->force_large = (cfg->flags & RPF_FLAG_FORCE_LARGE) || (getenv("RPF_FORCE_LARGE") && atoi(getenv("RPF_FORCE_LARGE")));
+        ctx->force_general = ctx->force_large || (cfg->flags & RPF_FLAG_FORCE_GENERAL) ||
+                             (getenv("RPF_FORCE_GENERAL") && atoi(getenv("RPF_FORCE_GENERAL")));
+        CUC(cudaFuncSetAttribute(dependency_large_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 227 * 1024 - ctx->kb_static_smem - 1024));
         if (const char *mb = getenv("RPF_SCRATCH_MB")) if (atoll(mb) > 0) ctx->scratch_budget = static_cast<size_t>(atoll(mb)) << 20;
     }
 #undef CUC
@@ -391,6 +404,49 @@ static bool plan_general(long long ncap, int spp, int static_smem, GeneralPlan &
     return false;
 }
 
+// Plan of dependency_large_kernel (rpf_large.cuh): one CTA of 1024 threads per SM; shared memory = small-count table,
+// 19 marginals, and everything else as the histogram region (u32 cells).
+static bool plan_large(long long ncap, int spp, int static_smem, GeneralPlan &L) {
+    if (ncap > kLargeMaxCandidates) return false;
+    L = GeneralPlan{};
+    L.large = 1;
+    L.ncap = static_cast<int>(ncap);
+    L.mw = ((L.ncap + 127) / 128) * 4;
+    L.nq = (L.ncap + 3) / 4;
+    const int nb = bins_for(L.ncap);
+    L.nbs = (nb + 3) & ~3;
+    L.off_gsm = 0;
+    L.off_marg = KB_GSM * 8;
+    L.off_region = align16(L.off_marg + NCH * L.nbs * 4);
+    L.kc_smem = spp * 18 * 8;
+    const int limit = 227 * 1024 - static_smem - 1024;
+    const int avail = (limit - L.off_region) & ~15;
+    if (avail < nb * 4 * 4) return false;
+    L.nt = KL_THREADS;
+    L.region_words = avail / 4;
+    L.kb_smem = L.off_region + avail;
+    return true;
+}
+
+// n ln n in units of 2^-38 for counts up to n (rpf_large.cuh)
+static int ensure_hql(rpf_ctx *ctx, int n) {
+    if (n + 2 <= ctx->hql_n) return RPF_OK;
+    const int m = (n + 2 > KB_GSM ? n + 2 : KB_GSM) + 1;
+    std::vector<unsigned long long> h(m, 0ull);
+    for (int k = 2; k < m; ++k) {
+        const long double a = k;
+        h[k] = static_cast<unsigned long long>(llroundl(a * logl(a) * 274877906944.0L));
+    }
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    cudaFree(ctx->d_hql);
+    ctx->d_hql = nullptr;
+    ctx->hql_n = 0;
+    CU(ctx, cudaMalloc(&ctx->d_hql, m * sizeof(unsigned long long)));
+    CU(ctx, cudaMemcpy(ctx->d_hql, h.data(), m * sizeof(unsigned long long), cudaMemcpyHostToDevice));
+    ctx->hql_n = m;
+    return RPF_OK;
+}
+
 template <class T>
 static int ensure_buffer(rpf_ctx *ctx, T **ptr, size_t *have, size_t need) {
     if (need <= *have) return RPF_OK;
@@ -419,12 +475,14 @@ static int ensure_pstat(rpf_ctx *ctx, const FrameView &f, int y0, int y1) {
 
 static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
     GeneralParams p{};
-    if (!plan_general(1ll * box * box * ctx->cfg.spp, ctx->cfg.spp, ctx->kb_static_smem, p.pl))
-        return fail(ctx, RPF_ERR_UNSUPPORTED,
-                    "neighbourhood of box %d x %d spp = %lld candidates exceeds this build (max %d: 16-bit histogram cells)", box,
-                    ctx->cfg.spp, 1ll * box * box * ctx->cfg.spp, kGeneralMaxCandidates);
+    const long long ncap = 1ll * box * box * ctx->cfg.spp;
+    const bool planned = (!ctx->force_large && plan_general(ncap, ctx->cfg.spp, ctx->kb_static_smem, p.pl)) ||
+                         plan_large(ncap, ctx->cfg.spp, ctx->kb_static_smem, p.pl);
+    if (!planned)
+        return fail(ctx, RPF_ERR_UNSUPPORTED, "neighbourhood of box %d x %d spp = %lld candidates exceeds this build (max %d)", box,
+                    ctx->cfg.spp, ncap, kLargeMaxCandidates);
     if (p.pl.kc_smem > 40 * 1024) return fail(ctx, RPF_ERR_UNSUPPORTED, "spp %d too large for the blend kernel", ctx->cfg.spp);
-    int rc = ensure_gtab(ctx, p.pl.ncap);
+    int rc = p.pl.large ? ensure_hql(ctx, p.pl.ncap) : ensure_gtab(ctx, p.pl.ncap);
     if (rc != RPF_OK) return rc;
     p.f = FrameView{ctx->d_planes, ctx->S, ctx->cfg.width, ctx->cfg.height, ctx->cfg.spp};
     rc = ensure_pstat(ctx, p.f, y0, y1);
@@ -435,14 +493,18 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
     if (rows < 1) rows = 1;
     if (rows > y1 - y0) rows = y1 - y0;
     int occ = 0;
-    if (p.pl.nt == 512) CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dependency_kernel<512>, 512, p.pl.kb_smem));
+    if (p.pl.large) CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dependency_large_kernel, KL_THREADS, p.pl.kb_smem));
+    else if (p.pl.nt == 512) CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dependency_kernel<512>, 512, p.pl.kb_smem));
     else CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dependency_kernel<1024>, 1024, p.pl.kb_smem));
     if (occ < 1) return fail(ctx, RPF_ERR_CUDA, "dependency kernel does not fit on an SM with %d bytes of shared memory", p.pl.kb_smem);
     const long long chunk_px = rows * W;
     p.pl.kb_grid = static_cast<int>(chunk_px < 1ll * occ * ctx->num_sms ? chunk_px : 1ll * occ * ctx->num_sms);
     if ((rc = ensure_buffer(ctx, &ctx->d_mask, &ctx->mask_bytes, static_cast<size_t>(chunk_px) * p.pl.mw * 4)) != RPF_OK) return rc;
     if ((rc = ensure_buffer(ctx, &ctx->d_rec, &ctx->rec_bytes, static_cast<size_t>(chunk_px) * REC_DOUBLES * 8)) != RPF_OK) return rc;
-    if (!p.pl.bins_in_smem &&
+    if (p.pl.large) {
+        p.big_stride = static_cast<size_t>(p.pl.nq) * 168;  // 4 B candidate number + 19 u16 bins per candidate, rows padded to 4
+        if ((rc = ensure_buffer(ctx, &ctx->d_big, &ctx->big_bytes, static_cast<size_t>(p.pl.kb_grid) * p.big_stride)) != RPF_OK) return rc;
+    } else if (!p.pl.bins_in_smem &&
         (rc = ensure_buffer(ctx, &ctx->d_bins, &ctx->bins_bytes, static_cast<size_t>(p.pl.kb_grid) * NCH * p.pl.nq * 4)) != RPF_OK)
         return rc;
     if (!ctx->d_rec16) {
@@ -463,7 +525,8 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
     p.col_out = ctx->d_col[ctx->cur ^ 1];
     p.pstat = ctx->d_pstat;
     p.gq = ctx->d_gq;
-    p.hq = ctx->d_hq;
+    p.hq = p.pl.large ? ctx->d_hql : ctx->d_hq;
+    p.big_scratch = ctx->d_big;
     p.box = box;
     p.flags = ctx->cfg.flags;
     p.seed = seed;
@@ -506,7 +569,8 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
         prof_end(ctx);
         const unsigned gridb = npx < static_cast<unsigned>(p.pl.kb_grid) ? npx : static_cast<unsigned>(p.pl.kb_grid);
         prof_begin(ctx, RPF_K_DEPENDENCY);
-        if (p.pl.nt == 512) dependency_kernel<512><<<gridb, 512, p.pl.kb_smem, ctx->stream>>>(p);
+        if (p.pl.large) dependency_large_kernel<<<gridb, KL_THREADS, p.pl.kb_smem, ctx->stream>>>(p);
+        else if (p.pl.nt == 512) dependency_kernel<512><<<gridb, 512, p.pl.kb_smem, ctx->stream>>>(p);
         else dependency_kernel<1024><<<gridb, 1024, p.pl.kb_smem, ctx->stream>>>(p);
         prof_end(ctx);
         prof_begin(ctx, RPF_K_BLEND);

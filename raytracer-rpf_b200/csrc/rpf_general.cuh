@@ -37,6 +37,7 @@ struct GeneralPlan {
     int region_words;  // capacity of the histogram region in 32-bit words
     int kb_grid;
     int kc_smem;
+    int large;       // 1: dependency_large_kernel (rpf_large.cuh): u32 candidates, u16 bins, u32 cells, slabbed tables
 };
 
 struct GeneralParams {
@@ -56,6 +57,8 @@ struct GeneralParams {
     uint32_t *mask;       // [chunk pixels][mw]
     double *rec;          // [chunk pixels][REC_DOUBLES]
     uint8_t *bins_scratch;  // [kb_grid][19][nq*4] when bins do not fit in shared memory
+    uint8_t *big_scratch;   // rpf_large.cuh: [kb_grid][big_stride] candidate list + u16 bins of one pixel
+    size_t big_stride;
     unsigned int *work_counter;
     GeneralPlan pl;
     int *dbg_n;
@@ -154,6 +157,41 @@ __device__ __forceinline__ int bin_value(double x, int c, const KBSmall &ks, int
         b = __double2int_rz(__dmul_rn(__ddiv_rn(__dsub_rn(z, ks.lo[c]), __dsub_rn(ks.hi[c], ks.lo[c])), dnb));
     }
     return max(min(b, nb - 1), 0);
+}
+
+// Per-pixel constants of the dependency kernels: the slot permutation step, and per channel the normalised extremes and
+// the FMA bin estimate te = x*A + Bc with its trust tolerance. Threads 0..18 own a channel, thread 32 the permutation.
+__device__ __forceinline__ void kb_prepare_pixel(KBSmall &ks, const double *rec, int N, double dnb, int tid) {
+    if (tid == 32) {
+        // slot -> sample permutation step: adjacent slots hold samples far apart in enumeration order, so the lanes
+        // of a warp rarely hit one histogram cell together even for smooth channels
+        int q = static_cast<int>(0.6180339887 * N) | 1;
+        if (q >= N) q = 1;
+        for (;; q += 2) {
+            int a = q, b = N;
+            while (b) { const int r = a % b; a = b; b = r; }
+            if (a == 1) break;
+        }
+        ks.Q = N > 1 ? q % N : 0;
+        if (N > 1 && ks.Q == 0) ks.Q = 1;
+        ks.any_susp = 0;
+    }
+    if (tid < NCH) {
+        const int c = tid;
+        const double m = rec[REC_M + c], sd = rec[REC_SD + c], rlo = rec[REC_RLO + c], rhi = rec[REC_RHI + c];
+        // (x-M)/SD is monotone in x, so the extremes of the normalised channel are the normalised extremes
+        const double lo = normalise(rlo, m, sd), hi = normalise(rhi, m, sd);
+        ks.M[c] = m; ks.SD[c] = sd; ks.lo[c] = lo; ks.hi[c] = hi;
+        const bool flat = hi == lo;
+        ks.flat[c] = flat;
+        const double rr = dnb / (hi - lo), rsd = 1.0 / sd;
+        double A = rsd * rr, Bc = (-m * rsd - lo) * rr;
+        if (flat) { A = 0.0; Bc = 0.5; }
+        if (!flat && !(hi > lo)) A = __longlong_as_double(0x7ff8000000000000ll);  // sigma is NaN: always the exact path
+        ks.A[c] = A;
+        ks.Bc[c] = Bc;
+        ks.tol[c] = 1e-9 + 1e-14 * (fabs(m * A) + fabs(Bc) + fabs(rhi * A) + fabs(rlo * A));
+    }
 }
 
 // rpf.cpp:416-487 from the 96 mutual informations (same code path as phase 6 of the fused kernel)
@@ -372,36 +410,7 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
         int nb = static_cast<int>(__dsqrt_rn(static_cast<double>(N)));  // mi.cpp:53-58
         if (nb < 1) nb = 1;
         const double dnb = static_cast<double>(nb);
-        if (tid == 32) {
-            // slot -> sample permutation step: adjacent slots hold samples far apart in enumeration order, so the lanes
-            // of a warp rarely hit one histogram cell together even for smooth channels
-            int q = static_cast<int>(0.6180339887 * N) | 1;
-            if (q >= N) q = 1;
-            for (;; q += 2) {
-                int a = q, b = N;
-                while (b) { const int r = a % b; a = b; b = r; }
-                if (a == 1) break;
-            }
-            ks.Q = N > 1 ? q % N : 0;
-            if (N > 1 && ks.Q == 0) ks.Q = 1;
-            ks.any_susp = 0;
-        }
-        if (tid < NCH) {
-            const int c = tid;
-            const double m = rec[REC_M + c], sd = rec[REC_SD + c], rlo = rec[REC_RLO + c], rhi = rec[REC_RHI + c];
-            // (x-M)/SD is monotone in x, so the extremes of the normalised channel are the normalised extremes
-            const double lo = normalise(rlo, m, sd), hi = normalise(rhi, m, sd);
-            ks.M[c] = m; ks.SD[c] = sd; ks.lo[c] = lo; ks.hi[c] = hi;
-            const bool flat = hi == lo;
-            ks.flat[c] = flat;
-            const double rr = dnb / (hi - lo), rsd = 1.0 / sd;
-            double A = rsd * rr, Bc = (-m * rsd - lo) * rr;
-            if (flat) { A = 0.0; Bc = 0.5; }
-            if (!flat && !(hi > lo)) A = __longlong_as_double(0x7ff8000000000000ll);  // sigma is NaN: always the exact path
-            ks.A[c] = A;
-            ks.Bc[c] = Bc;
-            ks.tol[c] = 1e-9 + 1e-14 * (fabs(m * A) + fabs(Bc) + fabs(rhi * A) + fabs(rlo * A));
-        }
+        kb_prepare_pixel(ks, rec, N, dnb, tid);
         for (int k = tid; k < N_JOINT; k += NT) { ks.susp[k] = 0; ks.Sab[k] = 0ull; }
         for (int k = tid; k < NCH * L.nbs; k += NT) marg[k] = 0u;
 

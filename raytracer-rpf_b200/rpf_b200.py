@@ -16,6 +16,7 @@ NCH = 19
 FLAGS_DEFINED = 7
 FLAGS_VERBATIM = 0x100
 FLAG_FORCE_GENERAL = 0x200
+FLAG_FORCE_LARGE = 0x400
 
 # every symbol include/rpf_b200.h declares
 ABI_SYMBOLS = [
@@ -106,9 +107,11 @@ def synth_planes(width, height, spp, seed=1234, kind=0, x_off=0, y_off=0, out=No
 class RPFFilter:
     """One device context = one SamplingFilm (reference src/custom/sample_film.h:28-45) resident in HBM."""
 
-    def __init__(self, width, height, spp, device=0, flags=FLAGS_DEFINED, debug=False, force_general=False):
+    def __init__(self, width, height, spp, device=0, flags=FLAGS_DEFINED, debug=False, force_general=False, force_large=False):
         if force_general:
             flags |= FLAG_FORCE_GENERAL
+        if force_large:
+            flags |= FLAG_FORCE_LARGE
         self.W, self.H, self.P = width, height, spp
         self.S = width * height * spp
         self._h = C.c_void_p()

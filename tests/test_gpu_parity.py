@@ -15,9 +15,9 @@ TOL_RELMSE = 1e-5   # north_star
 TOL_TIGHT = 1e-9    # what the FP64 kernels actually deliver
 
 
-def _gpu(planes, W, H, P, boxes, seed, flags=7, colors=None, general=False):
+def _gpu(planes, W, H, P, boxes, seed, flags=7, colors=None, general=False, large=False):
     import rpf_b200
-    f = rpf_b200.RPFFilter(W, H, P, flags=flags, debug=True, force_general=general)
+    f = rpf_b200.RPFFilter(W, H, P, flags=flags, debug=True, force_general=general, force_large=large)
     f.upload(planes)
     if colors is not None:
         f.upload_colors_f64(colors)
@@ -111,12 +111,56 @@ def test_box55_full_neighbourhood():
     _compare(g, o, W, H, P)
 
 
+# The large-neighbourhood dependency kernel (rpf_large.cuh: u32 candidate numbers, u16 bins, u32 cells, slabbed tables).
+@pytest.mark.parametrize("W,H,P,boxes,seed,kind", [
+    (24, 20, 8, [7], 0.5, 0),          # forced: four small tables per pass
+    (30, 24, 8, [17, 9], 0.2, 1),      # forced, degenerate content (flat channels, exact-zero MI recomputation)
+    (20, 16, 32, [41], 0.5, 0),        # forced, same case as the general path above
+    (12, 10, 64, [35], 0.5, 0),        # 78,400 candidates: taken without forcing (BASELINE.json configs[4], box 35)
+    (8, 6, 64, [55], 1.0, 0),          # 193,600 candidates (configs[4], box 55)
+])
+def test_large_kernel_matches_oracle(W, H, P, boxes, seed, kind):
+    import rpf_b200
+    planes = rpf_b200.synth_planes(W, H, P, seed=77, kind=kind)
+    o = ob.oracle_filter(planes, W, H, P, boxes, seed=seed, debug=True)
+    g = _gpu(planes, W, H, P, boxes, seed, large=True)
+    _compare(g, o, W, H, P)
+
+
+def test_large_kernel_beyond_255_bins():
+    """N > 65,536 accepted samples: more than 255 bins per axis (u16 bins), and a joint table (nb*nb u32 cells) that
+    no longer fits in shared memory at once, so it is built in row slabs. Smooth features make every candidate pass
+    the 3-sigma test; 40x40 px x 64 spp inside a 55 box gives N up to 102,400 -> 320 bins, 409 KB per table."""
+    import rpf_b200
+    W, H, P = 40, 40, 64
+    planes = rpf_b200.synth_planes(W, H, P, seed=9, kind=0)
+    planes[7:19] = (planes[7:19] * 0.0 + np.random.default_rng(5).normal(size=(12, W * H * P))).astype(np.float32)
+    rows = (18, 22)
+    o = ob.oracle_filter(planes, W, H, P, [55], seed=0.5, debug=True, rows=rows)
+    import rpf_b200 as rb
+    f = rb.RPFFilter(W, H, P, debug=True)
+    f.upload(planes)
+    f.filter_rows(55, rows[0], rows[1], 0.5)
+    f.swap_colors()
+    got = f.download_colors_f64()
+    dbg = f.download_debug()
+    f.close()
+    sel = np.zeros(W * H, bool)
+    sel[rows[0] * W:rows[1] * W] = True
+    assert np.array_equal(dbg["N"][sel], o["N"][sel])
+    assert dbg["N"][sel].max() > 65536
+    for k in ("alpha", "beta", "wrc"):
+        assert np.abs(dbg[k][sel] - o[k][sel]).max() <= TOL_TIGHT, k
+    ssel = np.repeat(sel, P)
+    assert np.abs(got[:, ssel] - o["colors"][:, ssel]).max() <= TOL_TIGHT
+
+
 def test_unsupported_neighbourhood_is_an_error():
     import rpf_b200
-    f = rpf_b200.RPFFilter(8, 8, 64)
-    f.upload(rpf_b200.synth_planes(8, 8, 64, seed=1, kind=0))
+    f = rpf_b200.RPFFilter(4, 4, 64)
+    f.upload(rpf_b200.synth_planes(4, 4, 64, seed=1, kind=0))
     with pytest.raises(rpf_b200.RPFError, match="exceeds this build"):
-        f.apply([35], 0.5)   # 35*35*64 = 78,400 candidates > 65,535
+        f.apply([129], 0.5)   # 129*129*64 = 1,065,024 candidates > 2^20
     f.close()
 
 
