@@ -167,21 +167,9 @@ def main():
     ctx = rpf_b200.RPFFilter(W, lh, P, device=local_rank)
     ctx.upload(planes)
     ctx.synchronize()
-    o0, o1 = band.local_own
-
-    class DevView:  # zero-copy torch view of the context's colour planes for the halo exchange
-        def __init__(self, ptr):
-            self.__cuda_array_interface__ = {"shape": (3, S_loc), "typestr": "<f8", "data": (ptr, False), "version": 2}
 
     def step():
-        for i, b in enumerate(boxes):
-            ctx.filter_rows(b, o0, o1, args.seed)
-            if world > 1 and i + 1 < len(boxes):
-                ctx.synchronize()
-                nxt = torch.as_tensor(DevView(ctx.color_ptr(1)), device=f"cuda:{local_rank}")
-                bands.exchange_halos(dist, band, boxes[i + 1], nxt, row)
-                torch.cuda.synchronize()
-            ctx.swap_colors()
+        bands.run_passes(ctx, band, boxes, args.seed, dist, local_rank)
 
     def barrier():
         ctx.synchronize()

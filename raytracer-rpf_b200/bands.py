@@ -87,3 +87,27 @@ def halo_bytes(band, next_box, row_elems, itemsize=8):
     for _, (s0, s1), _ in halo_plan(band, next_box):
         n += 3 * (s1 - s0) * row_elems * itemsize
     return n
+
+
+class DeviceColors:
+    """Zero-copy view of a context's colour planes ([3][S] doubles in HBM) for torch.distributed."""
+
+    def __init__(self, ptr, n):
+        self.__cuda_array_interface__ = {"shape": (3, n), "typestr": "<f8", "data": (ptr, False), "version": 2}
+
+
+def run_passes(ctx, band, boxes, seed, dist=None, device=0):
+    """The loop of rpf.cpp:767-775 over one row band on one GPU: each pass filters the owned rows, then the freshly
+    written colour rows within b_delta(next box) of a band edge go to the neighbouring ranks (NCCL send/recv over
+    NVLink) before the buffers swap. ctx: rpf_b200.RPFFilter holding the band plus its halo rows."""
+    import torch
+    o0, o1 = band.local_own
+    row = ctx.W * ctx.P
+    for i, b in enumerate(boxes):
+        ctx.filter_rows(b, o0, o1, seed)
+        if dist is not None and band.world > 1 and i + 1 < len(boxes):
+            ctx.synchronize()
+            nxt = torch.as_tensor(DeviceColors(ctx.color_ptr(1), ctx.S), device=f"cuda:{device}")
+            exchange_halos(dist, band, boxes[i + 1], nxt, row)
+            torch.cuda.synchronize(device)
+        ctx.swap_colors()
