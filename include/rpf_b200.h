@@ -110,6 +110,26 @@ int rpf_download_debug(rpf_ctx *ctx, int *nbh, double *alpha, double *beta, doub
  * per-pixel mean of the current colours weighted by nothing but rayWeight==1; rgb = [height*width][3] floats. */
 int rpf_reconstruct_box(rpf_ctx *ctx, float *rgb);
 
+/* Film reconstruction for ANY pbrt filter: replaces the serial tail of RPFIntegrator::Render,
+ * rpf.cpp:776-804 = Film::GetFilmTile + FilmTile::AddSample per sample (core/film.h:121-161) + Film::MergeFilmTile
+ * (core/film.cpp:117-130) + the arithmetic of Film::WriteImage (core/film.cpp:169-205: XYZ->RGB, / filterWeightSum,
+ * max(0,.), * scale), all in Float with the reference's operation order: bit-identical to the reference image.
+ * The caller hands over what the Film holds: bounds, filter radius, the 16x16 filter table, scale, luminance clamp. */
+typedef struct rpf_film_desc {
+    int sample_x0, sample_y0;   /* raster coordinates of the context's sample pixel (0,0): Film::GetSampleBounds().pMin */
+    int pixel_x0, pixel_y0, pixel_x1, pixel_y1; /* Film::croppedPixelBounds */
+    float radius_x, radius_y;   /* filter->radius */
+    float filter_table[256];    /* Film::filterTable (core/film.cpp:69-77), see rpf_film_filter_table */
+    float scale;                /* Film::scale */
+    float max_sample_luminance; /* Film::maxSampleLuminance (INFINITY by default) */
+} rpf_film_desc;
+/* ray_weight: host [width*height*spp] (SampleData::rayWeight, sd.h:59) or NULL for 1. rgb: host
+ * [(pixel_y1-pixel_y0)*(pixel_x1-pixel_x0)][3] floats, the buffer Film::WriteImage hands to the image writer. */
+int rpf_reconstruct_film(rpf_ctx *ctx, const rpf_film_desc *film, const float *ray_weight, float *rgb);
+/* Host helper: the Film constructor's filter table (core/film.cpp:69-77) for pbrt's box (kind 0, filters/box.cpp:41)
+ * or gaussian (kind 1, filters/gaussian.h:52-66, gaussian.cpp:41-43) filter. Other filters: evaluate them yourself. */
+int rpf_film_filter_table(int kind, float radius_x, float radius_y, float alpha, float table[256]);
+
 int rpf_get_stats(rpf_ctx *ctx, rpf_stats_t *out);
 int rpf_reset_stats(rpf_ctx *ctx);
 

@@ -42,3 +42,45 @@ extern "C" int host_apply_rpf_b200(int W, int H, int P, const float *planes, dou
     if (nan_channels) *nan_channels = rep.nanChannels;
     return 0;
 }
+
+// Filter + Film reconstruction through the host C++: a gaussian pbrt filter described to MakeFilmDescB200 by a stand-in
+// with the interface of pbrt::Filter (radius, Evaluate), rayWeight carried by the SampleData records.
+namespace {
+struct HarnessGaussian {  // interface of core/filter.h:47-58; values supplied by the test (the reference filter's table)
+    struct { float x, y; } radius;
+    const float *table;
+    mutable int calls = 0;
+    float Evaluate(const Point2f &) const { return table[calls++]; }
+};
+}  // namespace
+
+extern "C" int host_apply_rpf_film_b200(int W, int H, int P, const float *planes, const float *ray_weight, const int *boxes, int n_boxes,
+                                        double seed, float rx, float ry, const float *table, float scale, float max_lum,
+                                        float *rgb /* [H*W][3] */, char *err, int err_len) {
+    Bounds2i bounds(Point2i(0, 0), Point2i(W, H));
+    SamplingFilm sf(bounds);
+    const size_t S = static_cast<size_t>(W) * H * P;
+    for (int y = 0; y < H; ++y)
+        for (int x = 0; x < W; ++x)
+            for (int s = 0; s < P; ++s) {
+                const size_t i = (static_cast<size_t>(y) * W + x) * P + s;
+                SampleData sd;
+                for (int c = 0; c < 19; ++c) sd.data[c] = planes[c * S + i];
+                sd.rayWeight = ray_weight ? ray_weight[i] : 1;
+                sf.AddSample(Point2i(x, y), sd);
+            }
+    RPFB200Options opt;
+    opt.boxSizes.assign(boxes, boxes + n_boxes);
+    opt.sigmaSeed = seed;
+    HarnessGaussian filt;
+    filt.radius.x = rx; filt.radius.y = ry; filt.table = table;
+    const rpf_film_desc fd = MakeFilmDescB200(filt, bounds, bounds, scale, max_lum);
+    std::vector<float> out;
+    std::string error;
+    if (!ApplyRPFFilterAndFilmB200(sf, opt, fd, &out, nullptr, &error)) {
+        if (err && err_len > 0) { std::snprintf(err, err_len, "%s", error.c_str()); }
+        return -1;
+    }
+    std::copy(out.begin(), out.end(), rgb);
+    return 0;
+}

@@ -750,6 +750,49 @@ extern "C" int rpf_reconstruct_box(rpf_ctx *ctx, float *rgb) {
     return rpf_synchronize(ctx);
 }
 
+extern "C" int rpf_reconstruct_film(rpf_ctx *ctx, const rpf_film_desc *film, const float *ray_weight, float *rgb) {
+    if (!ctx || !film || !rgb) return fail(ctx, RPF_ERR_INVALID, "rpf_reconstruct_film: null argument");
+    if (!ctx->uploaded) return fail(ctx, RPF_ERR_STATE, "rpf_reconstruct_film: no samples uploaded");
+    const long long pw = 1ll * film->pixel_x1 - film->pixel_x0, ph = 1ll * film->pixel_y1 - film->pixel_y0;
+    if (pw <= 0 || ph <= 0 || pw * ph > (1ll << 30) || !(film->radius_x > 0.f) || !(film->radius_y > 0.f))
+        return fail(ctx, RPF_ERR_INVALID, "rpf_reconstruct_film: empty pixel bounds or non-positive filter radius");
+    CU(ctx, cudaSetDevice(ctx->cfg.device));
+    // scratch in the dead "next" colour buffer (3*S doubles): [ray weights S floats][table 256 floats][rgb 3*pw*ph floats]
+    const size_t need = (ctx->S + 256 + 3ull * pw * ph) * sizeof(float);
+    float *scratch = reinterpret_cast<float *>(ctx->d_col[ctx->cur ^ 1]);
+    float *own = nullptr;
+    if (need > 3 * ctx->S * sizeof(double)) {
+        CU(ctx, cudaMalloc(&own, need));
+        scratch = own;
+    }
+    FilmParams p{};
+    p.planes = ctx->d_planes;
+    p.col = ctx->d_col[ctx->cur];
+    p.S = ctx->S;
+    p.W = ctx->cfg.width; p.H = ctx->cfg.height; p.P = ctx->cfg.spp;
+    p.sx0 = film->sample_x0; p.sy0 = film->sample_y0;
+    p.px0 = film->pixel_x0; p.py0 = film->pixel_y0; p.px1 = film->pixel_x1; p.py1 = film->pixel_y1;
+    p.rx = film->radius_x; p.ry = film->radius_y; p.scale = film->scale; p.max_lum = film->max_sample_luminance;
+    float *d_table = scratch + ctx->S;
+    p.table = d_table;
+    p.rgb = d_table + 256;
+    cudaError_t e = cudaMemcpyAsync(d_table, film->filter_table, 256 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess && ray_weight) {
+        e = cudaMemcpyAsync(scratch, ray_weight, ctx->S * sizeof(float), cudaMemcpyHostToDevice, ctx->stream);
+        p.ray_weight = scratch;
+    }
+    if (e == cudaSuccess) {
+        const unsigned n = static_cast<unsigned>(pw * ph);
+        film_reconstruct_kernel<<<(n + 127) / 128, 128, 0, ctx->stream>>>(p);
+        ctx->launches++;
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(rgb, p.rgb, 3ull * pw * ph * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
+    int rc = e == cudaSuccess ? rpf_synchronize(ctx) : fail(ctx, RPF_ERR_CUDA, "rpf_reconstruct_film: %s", cudaGetErrorString(e));
+    if (own) { cudaStreamSynchronize(ctx->stream); cudaFree(own); }
+    return rc;
+}
+
 extern "C" int rpf_get_stats(rpf_ctx *ctx, rpf_stats_t *out) {
     if (!ctx || !out) return RPF_ERR_INVALID;
     int rc = rpf_synchronize(ctx);

@@ -137,4 +137,83 @@ __global__ void reconstruct_box_kernel(const double *__restrict__ col, size_t S,
     rgb[t] = acc / static_cast<float>(P);
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Film reconstruction, any pbrt filter: FilmTile::AddSample (film.h:121-161) + Film::MergeFilmTile
+// (film.cpp:117-130) + Film::WriteImage (film.cpp:169-205) as a gather. One thread per output pixel walks the sample
+// pixels that can reach it in the order the reference adds them (rpf.cpp:783-786: x outer, y inner, sample order) and
+// accumulates in Float with the reference's operation order and no FMA contraction, so the image is bit-identical to
+// the reference's single FilmTile. A sample is assumed to lie within one pixel of the pixel that stores it (pFilm =
+// pixel + [0,1) offset in every pbrt sampler).
+struct FilmParams {
+    const float *planes;   // [19][S]; planes 0,1 = pFilm
+    const double *col;     // [3][S] current colours
+    const float *ray_weight;  // [S] or null (= 1)
+    size_t S;
+    int W, H, P;           // sample extent held by the context
+    int sx0, sy0;          // raster coordinates of the context's sample pixel (0,0) (sampleBounds.pMin)
+    int px0, py0, px1, py1;  // croppedPixelBounds
+    float rx, ry, scale, max_lum;
+    const float *table;    // [16*16] Film::filterTable
+    float *rgb;            // [(py1-py0)*(px1-px0)][3]
+};
+
+__global__ void film_reconstruct_kernel(const FilmParams p) {
+    const int pw = p.px1 - p.px0, ph = p.py1 - p.py0;
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= pw * ph) return;
+    const int x = p.px0 + t % pw, y = p.py0 + t / pw;
+    const float irx = __fdiv_rn(1.f, p.rx), iry = __fdiv_rn(1.f, p.ry);  // filter.h:52
+    float sum[3] = {0.f, 0.f, 0.f}, fws = 0.f;
+    const int xs_lo = max(static_cast<int>(floorf(x + 0.5f - p.rx)) - 2 - p.sx0, 0);
+    const int xs_hi = min(static_cast<int>(ceilf(x + 0.5f + p.rx)) + 1 - p.sx0, p.W - 1);
+    const int ys_lo = max(static_cast<int>(floorf(y + 0.5f - p.ry)) - 2 - p.sy0, 0);
+    const int ys_hi = min(static_cast<int>(ceilf(y + 0.5f + p.ry)) + 1 - p.sy0, p.H - 1);
+    for (int xs = xs_lo; xs <= xs_hi; ++xs)
+        for (int ys = ys_lo; ys <= ys_hi; ++ys) {
+            const size_t g0 = (static_cast<size_t>(ys) * p.W + xs) * p.P;
+            for (int s = 0; s < p.P; ++s) {
+                const size_t g = g0 + s;
+                const float dx = __fsub_rn(p.planes[g], 0.5f), dy = __fsub_rn(p.planes[p.S + g], 0.5f);  // pFilmDiscrete
+                const int p0x = max(static_cast<int>(ceilf(__fsub_rn(dx, p.rx))), p.px0);
+                const int p1x = min(static_cast<int>(floorf(__fadd_rn(dx, p.rx))) + 1, p.px1);
+                const int p0y = max(static_cast<int>(ceilf(__fsub_rn(dy, p.ry))), p.py0);
+                const int p1y = min(static_cast<int>(floorf(__fadd_rn(dy, p.ry))) + 1, p.py1);
+                if (x < p0x || x >= p1x || y < p0y || y >= p1y) continue;
+                float L[3] = {static_cast<float>(p.col[g]), static_cast<float>(p.col[p.S + g]), static_cast<float>(p.col[2 * p.S + g])};
+                const float lum = __fadd_rn(__fadd_rn(__fmul_rn(0.212671f, L[0]), __fmul_rn(0.715160f, L[1])), __fmul_rn(0.072169f, L[2]));
+                if (lum > p.max_lum) {  // film.h:125-126
+                    const float a = __fdiv_rn(p.max_lum, lum);
+#pragma unroll
+                    for (int k = 0; k < 3; ++k) L[k] = __fmul_rn(L[k], a);
+                }
+                const float fx = fabsf(__fmul_rn(__fmul_rn(__fsub_rn(static_cast<float>(x), dx), irx), 16.f));
+                const float fy = fabsf(__fmul_rn(__fmul_rn(__fsub_rn(static_cast<float>(y), dy), iry), 16.f));
+                const int ifx = min(static_cast<int>(floorf(fx)), 15), ify = min(static_cast<int>(floorf(fy)), 15);
+                const float fw = p.table[ify * 16 + ifx];
+                const float sw = p.ray_weight ? p.ray_weight[g] : 1.f;
+#pragma unroll
+                for (int k = 0; k < 3; ++k) sum[k] = __fadd_rn(sum[k], __fmul_rn(__fmul_rn(L[k], sw), fw));  // film.h:157
+                fws = __fadd_rn(fws, fw);
+            }
+        }
+    // MergeFilmTile: contribSum -> XYZ (spectrum.h:62-66), added to a zero pixel; WriteImage: XYZ -> RGB (spectrum.h:56-60)
+    auto dot3 = [](float a, float b, float c, float u, float v, float w) {
+        return __fadd_rn(__fadd_rn(__fmul_rn(a, u), __fmul_rn(b, v)), __fmul_rn(c, w));
+    };
+    float xyz[3], rgb[3];
+    xyz[0] = __fadd_rn(0.f, dot3(0.412453f, 0.357580f, 0.180423f, sum[0], sum[1], sum[2]));
+    xyz[1] = __fadd_rn(0.f, dot3(0.212671f, 0.715160f, 0.072169f, sum[0], sum[1], sum[2]));
+    xyz[2] = __fadd_rn(0.f, dot3(0.019334f, 0.119193f, 0.950227f, sum[0], sum[1], sum[2]));
+    rgb[0] = __fsub_rn(__fsub_rn(__fmul_rn(3.240479f, xyz[0]), __fmul_rn(1.537150f, xyz[1])), __fmul_rn(0.498535f, xyz[2]));
+    rgb[1] = __fadd_rn(__fadd_rn(__fmul_rn(-0.969256f, xyz[0]), __fmul_rn(1.875991f, xyz[1])), __fmul_rn(0.041556f, xyz[2]));
+    rgb[2] = __fadd_rn(__fsub_rn(__fmul_rn(0.055648f, xyz[0]), __fmul_rn(0.204043f, xyz[1])), __fmul_rn(1.057311f, xyz[2]));
+    if (fws != 0.f) {
+        const float inv = __fdiv_rn(1.f, fws);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) rgb[k] = fmaxf(0.f, __fmul_rn(rgb[k], inv));
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) p.rgb[static_cast<size_t>(t) * 3 + k] = __fmul_rn(__fadd_rn(rgb[k], 0.f), p.scale);  // splats are zero
+}
+
 }  // namespace rpf

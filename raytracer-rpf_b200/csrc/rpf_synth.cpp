@@ -4,6 +4,7 @@
 // The 19 planes follow SampleData::data (reference src/custom/sd.h:62-94).
 #include "../../include/rpf_b200.h"
 
+#include <algorithm>
 #include <cmath>
 #include <cstdint>
 #include <thread>
@@ -101,5 +102,20 @@ extern "C" int rpf_synth_planes(int width, int height, int spp, unsigned long lo
     for (unsigned t = 1; t < nt; ++t) th.emplace_back(work, static_cast<int>(t));
     work(0);
     for (auto &t : th) t.join();
+    return RPF_OK;
+}
+
+// Film constructor's filter table (reference core/film.cpp:69-77) for the box and gaussian filters
+// (filters/box.cpp:41, filters/gaussian.h:52-66, filters/gaussian.cpp:41-43). Float arithmetic like the reference.
+extern "C" int rpf_film_filter_table(int kind, float radius_x, float radius_y, float alpha, float table[256]) {
+    if (!table || (kind != 0 && kind != 1) || !(radius_x > 0.f) || !(radius_y > 0.f)) return RPF_ERR_INVALID;
+    const float expX = std::exp(-alpha * radius_x * radius_x), expY = std::exp(-alpha * radius_y * radius_y);
+    auto gaussian = [&](float d, float expv) { return std::max(0.f, float(std::exp(-alpha * d * d) - expv)); };
+    int offset = 0;
+    for (int y = 0; y < 16; ++y)
+        for (int x = 0; x < 16; ++x, ++offset) {
+            const float px = (x + 0.5f) * radius_x / 16, py = (y + 0.5f) * radius_y / 16;
+            table[offset] = kind == 0 ? 1.f : gaussian(px, expX) * gaussian(py, expY);
+        }
     return RPF_OK;
 }

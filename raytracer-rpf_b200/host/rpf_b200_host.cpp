@@ -17,7 +17,8 @@ bool failed(std::string *error, const std::string &what, const rpf_ctx *ctx) {
 }
 }  // namespace
 
-bool ApplyRPFFilterB200(SamplingFilm &film, const RPFB200Options &opt, RPFB200Report *report, std::string *error) {
+static bool run(SamplingFilm &film, const RPFB200Options &opt, const rpf_film_desc *fdesc, std::vector<float> *rgb,
+                RPFB200Report *report, std::string *error) {
     const int W = film.getWidth(), H = film.getHeight();
     if (W <= 0 || H <= 0 || film.samples.empty() || film.samples[0].empty()) {
         if (error) *error = "empty SamplingFilm";
@@ -68,6 +69,15 @@ bool ApplyRPFFilterB200(SamplingFilm &film, const RPFB200Options &opt, RPFB200Re
     if (rpf_download_colors_f64(ctx.get(), colours.data()) != RPF_OK) return failed(error, "rpf_download_colors_f64", ctx.get());
     rpf_stats_t st{};
     if (rpf_get_stats(ctx.get(), &st) != RPF_OK) return failed(error, "rpf_get_stats", ctx.get());
+    if (fdesc && rgb) {  // rpf.cpp:776-804 on the device, samples still resident
+        std::vector<float> rayWeight(S);
+        for (int x = 0; x < W; ++x)
+            for (int y = 0; y < H; ++y)
+                for (size_t s = 0; s < spp; ++s) rayWeight[(static_cast<size_t>(y) * W + x) * spp + s] = film.samples[x][y][s].rayWeight;
+        rgb->resize(3 * static_cast<size_t>(fdesc->pixel_x1 - fdesc->pixel_x0) * (fdesc->pixel_y1 - fdesc->pixel_y0));
+        if (rpf_reconstruct_film(ctx.get(), fdesc, rayWeight.data(), rgb->data()) != RPF_OK)
+            return failed(error, "rpf_reconstruct_film", ctx.get());
+    }
 
     // rpf.cpp:715,732: only the three colour slots change
     for (int x = 0; x < W; ++x)
@@ -85,6 +95,19 @@ bool ApplyRPFFilterB200(SamplingFilm &film, const RPFB200Options &opt, RPFB200Re
         report->filterMs = st.last_filter_ms;
     }
     return true;
+}
+
+bool ApplyRPFFilterB200(SamplingFilm &film, const RPFB200Options &opt, RPFB200Report *report, std::string *error) {
+    return run(film, opt, nullptr, nullptr, report, error);
+}
+
+bool ApplyRPFFilterAndFilmB200(SamplingFilm &film, const RPFB200Options &opt, const rpf_film_desc &fdesc, std::vector<float> *rgb,
+                               RPFB200Report *report, std::string *error) {
+    if (!rgb) {
+        if (error) *error = "ApplyRPFFilterAndFilmB200: rgb is null";
+        return false;
+    }
+    return run(film, opt, &fdesc, rgb, report, error);
 }
 
 }  // namespace pbrt

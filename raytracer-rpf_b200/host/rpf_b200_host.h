@@ -12,6 +12,7 @@
 #include <vector>
 
 #include "custom/sample_film.h"
+#include "rpf_b200.h"
 
 namespace pbrt {
 
@@ -33,6 +34,37 @@ struct RPFB200Report {
 // (no CUDA device, ragged sample counts, neighbourhood above rpf_max_neighbourhood(), CUDA errors).
 bool ApplyRPFFilterB200(SamplingFilm &samplingFilm, const RPFB200Options &options, RPFB200Report *report,
                         std::string *error);
+
+// Same, and the Film reconstruction that follows in Render (rpf.cpp:776-804: FilmTile::AddSample per sample with
+// SampleData::rayWeight, MergeFilmTile, WriteImage arithmetic) also runs on the GPU while the samples are resident:
+// *rgb receives the buffer Film::WriteImage would hand to pbrt::WriteImage (core/film.cpp:210), bit for bit,
+// [(pixel_y1-pixel_y0)*(pixel_x1-pixel_x0)][3] floats. The caller then calls pbrt::WriteImage(film->filename, rgb->data(),
+// film->croppedPixelBounds, film->fullResolution) itself.
+bool ApplyRPFFilterAndFilmB200(SamplingFilm &samplingFilm, const RPFB200Options &options, const rpf_film_desc &film,
+                               std::vector<float> *rgb, RPFB200Report *report, std::string *error);
+
+// What the GPU needs to know about a pbrt Film, from its public parts: the filter (core/film.h:78, filter.h:47-58), the
+// bounds, and the two private scalars the caller passes in (Film "scale" and "maxsampleluminance" scene parameters,
+// core/film.cpp:213-251). The table is the Film constructor's (core/film.cpp:69-77). A template so that this header does
+// not depend on pbrt's core/filter.h: FilterT = pbrt::Filter.
+template <class FilterT, class Bounds2iT>
+rpf_film_desc MakeFilmDescB200(const FilterT &filter, const Bounds2iT &sampleBounds, const Bounds2iT &croppedPixelBounds, float scale,
+                               float maxSampleLuminance) {
+    rpf_film_desc d{};
+    d.sample_x0 = sampleBounds.pMin.x; d.sample_y0 = sampleBounds.pMin.y;
+    d.pixel_x0 = croppedPixelBounds.pMin.x; d.pixel_y0 = croppedPixelBounds.pMin.y;
+    d.pixel_x1 = croppedPixelBounds.pMax.x; d.pixel_y1 = croppedPixelBounds.pMax.y;
+    d.radius_x = filter.radius.x; d.radius_y = filter.radius.y;
+    int offset = 0;
+    for (int y = 0; y < 16; ++y)
+        for (int x = 0; x < 16; ++x, ++offset) {
+            decltype(filter.radius.x) px = (x + 0.5f) * filter.radius.x / 16, py = (y + 0.5f) * filter.radius.y / 16;
+            d.filter_table[offset] = filter.Evaluate({px, py});
+        }
+    d.scale = scale;
+    d.max_sample_luminance = maxSampleLuminance;
+    return d;
+}
 
 }  // namespace pbrt
 #endif

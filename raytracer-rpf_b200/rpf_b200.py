@@ -24,7 +24,7 @@ ABI_SYMBOLS = [
     "rpf_filter", "rpf_filter_rows", "rpf_swap_colors", "rpf_color_device_ptr", "rpf_stream", "rpf_synchronize",
     "rpf_download_colors", "rpf_download_colors_f64", "rpf_download_debug", "rpf_reconstruct_box",
     "rpf_get_stats", "rpf_reset_stats", "rpf_set_profiling", "rpf_get_kernel_times", "rpf_max_neighbourhood",
-    "rpf_synth_planes",
+    "rpf_synth_planes", "rpf_reconstruct_film", "rpf_film_filter_table",
 ]
 
 
@@ -41,6 +41,22 @@ class Stats(C.Structure):
     _fields_ = [("pixels_filtered", C.c_longlong), ("nbh_sum", C.c_longlong), ("nbh_min", C.c_int),
                 ("nbh_max", C.c_int), ("nan_channels", C.c_longlong), ("kernel_launches", C.c_longlong),
                 ("last_filter_ms", C.c_double)]
+
+
+class FilmDesc(C.Structure):
+    """rpf_film_desc: what pbrt's Film holds (core/film.h:58-105)."""
+    _fields_ = [("sample_x0", C.c_int), ("sample_y0", C.c_int), ("pixel_x0", C.c_int), ("pixel_y0", C.c_int),
+                ("pixel_x1", C.c_int), ("pixel_y1", C.c_int), ("radius_x", C.c_float), ("radius_y", C.c_float),
+                ("filter_table", C.c_float * 256), ("scale", C.c_float), ("max_sample_luminance", C.c_float)]
+
+
+def film_filter_table(kind, rx, ry, alpha=2.0):
+    """Film::filterTable (core/film.cpp:69-77) for pbrt's box (kind 0) or gaussian (kind 1) filter."""
+    t = np.empty(256, np.float32)
+    rc = lib().rpf_film_filter_table(kind, C.c_float(rx), C.c_float(ry), C.c_float(alpha), _p(t))
+    if rc != 0:
+        raise RPFError(f"rpf_film_filter_table failed ({rc})")
+    return t
 
 
 KERNEL_NAMES = ["pixel_stats_kernel", "rpf_pixel_kernel", "membership_kernel", "ordered_stats_kernel", "dependency_kernel",
@@ -171,6 +187,18 @@ class RPFFilter:
     def reconstruct_box(self):
         out = np.empty((self.H, self.W, 3), np.float32)
         self._check(lib().rpf_reconstruct_box(self._h, _p(out)))
+        return out
+
+    def reconstruct_film(self, table, rx, ry, pixel_bounds=None, sample_origin=(0, 0), scale=1.0,
+                         max_sample_luminance=float("inf"), ray_weight=None):
+        """Film reconstruction with any filter (rpf.cpp:776-804 -> core/film.h:121-161, film.cpp:117-130,169-205).
+        pixel_bounds = (x0, y0, x1, y1) croppedPixelBounds, default the context's extent. Returns [h, w, 3] float32."""
+        x0, y0, x1, y1 = pixel_bounds or (sample_origin[0], sample_origin[1], sample_origin[0] + self.W, sample_origin[1] + self.H)
+        d = FilmDesc(sample_origin[0], sample_origin[1], x0, y0, x1, y1, rx, ry, (C.c_float * 256)(*np.asarray(table, np.float32)),
+                     scale, max_sample_luminance)
+        out = np.empty((y1 - y0, x1 - x0, 3), np.float32)
+        rw = None if ray_weight is None else np.ascontiguousarray(ray_weight, np.float32)
+        self._check(lib().rpf_reconstruct_film(self._h, C.byref(d), None if rw is None else _p(rw), _p(out)))
         return out
 
     # -- the filter --------------------------------------------------------------------------------

@@ -94,5 +94,40 @@ def main():
     print("golden fixtures written to", GOLD)
 
 
+# Film reconstruction cases, from oracle/_ref/libref_film.so = the reference's own film.h / film.cpp /
+# filters lines. (W, H, P, filter kind, rx, ry, alpha, pixel bounds, scale, max luminance, ray weights?, synth kind)
+FILM_CASES = [
+    (24, 18, 8, 0, 0.5, 0.5, 0.0, (0, 0, 24, 18), 1.0, float("inf"), False, 0),    # pbrt default box filter
+    (24, 18, 8, 1, 2.0, 2.0, 2.0, (0, 0, 24, 18), 1.0, float("inf"), False, 0),    # sample.pbrt's gaussian
+    (20, 14, 4, 1, 1.5, 2.5, 1.0, (2, 1, 18, 12), 0.5, 0.8, True, 1),              # crop, scale, luminance clamp, ray weights
+    (9, 7, 3, 0, 1.0, 1.0, 0.0, (0, 0, 9, 7), 2.0, float("inf"), True, 0),         # wide box filter
+]
+
+
+def film_inputs(i, W, H, P, kind, with_rw):
+    planes = synth(W, H, P, 4000 + i, kind)
+    rng = np.random.default_rng(900 + i)
+    col = planes[2:5].astype(np.float64) * rng.uniform(0.5, 1.5, size=(3, W * H * P))  # doubles that are not floats
+    rw = rng.uniform(0.25, 1.0, size=W * H * P).astype(np.float32) if with_rw else None
+    return planes[0:2].copy(), col, rw
+
+
+def film_main():
+    os.makedirs(GOLD, exist_ok=True)
+    assert ob.ref_film() is not None, "build oracle/_ref first (make -C oracle)"
+    for i, (W, H, P, fk, rx, ry, alpha, bounds, scale, mx, with_rw, kind) in enumerate(FILM_CASES):
+        pfilm, col, rw = film_inputs(i, W, H, P, kind, with_rw)
+        rgb, table = ob.ref_film_reconstruct(W, H, P, pfilm, col, rw, fk, rx, ry, alpha, bounds, scale, mx)
+        np.savez_compressed(os.path.join(GOLD, f"film_case{i}.npz"), pfilm=pfilm, colors=col,
+                            ray_weight=rw if rw is not None else np.zeros(0, np.float32), rgb=rgb, table=table,
+                            meta=np.array([W, H, P, fk, *bounds]), fmeta=np.array([rx, ry, alpha, scale, mx], np.float32))
+    print("film fixtures written to", GOLD)
+
+
 if __name__ == "__main__":
-    main()
+    import sys
+    if len(sys.argv) > 1 and sys.argv[1] == "film":
+        film_main()
+    else:
+        main()
+        film_main()

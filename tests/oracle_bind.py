@@ -140,3 +140,49 @@ def ref_filter(planes, W, H, P, box, colors=None, threads=1):
     col = np.ascontiguousarray(planes[2:5].astype(np.float64) if colors is None else colors, dtype=np.float64).copy()
     flag = ref().ref_apply_rpf_filter(W, H, P, _p(planes), _p(col), box, threads, 0.002)
     return col, flag
+
+
+# ---- Film reconstruction -----------------------------------------------------------------------
+def ref_film():
+    """oracle/_ref/libref_film.so: the reference's FilmTile::AddSample / MergeFilmTile / WriteImage lines, or None."""
+    path = os.path.join(ORACLE_DIR, "_ref", "libref_film.so")
+    if not os.path.exists(path):
+        return None
+    lib = C.CDLL(path)
+    lib.ref_film_reconstruct.argtypes = ([C.c_int] * 5 + [C.c_void_p] * 3 + [C.c_int] + [C.c_float] * 3 + [C.c_int] * 4 +
+                                         [C.c_float] * 2 + [C.c_void_p] * 2)
+    return lib
+
+
+def ref_film_reconstruct(W, H, P, pfilm, colors, ray_weight, kind, rx, ry, alpha, bounds, scale, max_lum):
+    pfilm = np.ascontiguousarray(pfilm, np.float32)
+    colors = np.ascontiguousarray(colors, np.float64)
+    rw = None if ray_weight is None else np.ascontiguousarray(ray_weight, np.float32)
+    x0, y0, x1, y1 = bounds
+    rgb = np.empty((y1 - y0, x1 - x0, 3), np.float32)
+    table = np.empty(256, np.float32)
+    ref_film().ref_film_reconstruct(W, H, P, 0, 0, _p(pfilm), _p(colors), None if rw is None else _p(rw), kind, rx, ry, alpha,
+                                    x0, y0, x1, y1, scale, max_lum, _p(rgb), _p(table))
+    return rgb, table
+
+
+def oracle_film_table(kind, rx, ry, alpha):
+    lib = oracle()
+    lib.rpf_oracle_film_table.argtypes = [C.c_int] + [C.c_float] * 3 + [C.c_void_p]
+    t = np.empty(256, np.float32)
+    lib.rpf_oracle_film_table(kind, rx, ry, alpha, _p(t))
+    return t
+
+
+def oracle_film(W, H, P, pfilm, colors, ray_weight, table, rx, ry, bounds, scale, max_lum):
+    lib = oracle()
+    lib.rpf_oracle_film.argtypes = ([C.c_int] * 3 + [C.c_void_p] * 4 + [C.c_float] * 2 + [C.c_int] * 4 + [C.c_float] * 2 + [C.c_void_p])
+    pfilm = np.ascontiguousarray(pfilm, np.float32)
+    colors = np.ascontiguousarray(colors, np.float64)
+    rw = None if ray_weight is None else np.ascontiguousarray(ray_weight, np.float32)
+    table = np.ascontiguousarray(table, np.float32)
+    x0, y0, x1, y1 = bounds
+    rgb = np.empty((y1 - y0, x1 - x0, 3), np.float32)
+    lib.rpf_oracle_film(W, H, P, _p(pfilm), _p(colors), None if rw is None else _p(rw), _p(table), rx, ry, x0, y0, x1, y1,
+                        scale, max_lum, _p(rgb))
+    return rgb
