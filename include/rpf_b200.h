@@ -155,6 +155,19 @@ int rpf_max_neighbourhood(void);
 int rpf_synth_planes(int width, int height, int spp, unsigned long long seed, int kind, int x_off, int y_off,
                      float *planes /* [19][width*height*spp] */);
 
+/* Feature-buffer files: lossless dump / load of what the integrator emits per sample, replacing
+ * the lossy debug EXRs of visualizeSF (rpf.cpp:37-101). Host side only; layout in raytracer-rpf_b200/csrc/rpf_io.cpp. */
+typedef struct rpf_buffer_info {
+    int width, height, spp;
+    int sample_x0, sample_y0; /* sampleBounds.pMin */
+    int has_ray_weight;       /* out of rpf_buffer_info_read; ignored by rpf_buffer_write */
+} rpf_buffer_info;
+int rpf_buffer_write(const char *path, const rpf_buffer_info *info, const float *const planes[RPF_NUM_CHANNELS],
+                     const float *ray_weight /* may be NULL */);
+int rpf_buffer_info_read(const char *path, rpf_buffer_info *info);
+/* planes: [19][width*height*spp] contiguous; ray_weight: [width*height*spp] or NULL (filled with 1 if the file has none) */
+int rpf_buffer_read(const char *path, float *planes, float *ray_weight);
+
 #ifdef __cplusplus
 }
 #endif

@@ -84,3 +84,21 @@ extern "C" int host_apply_rpf_film_b200(int W, int H, int P, const float *planes
     std::copy(out.begin(), out.end(), rgb);
     return 0;
 }
+
+// The dump hook over a real reference SamplingFilm (host code only, no GPU).
+extern "C" int host_dump_sampling_film(int W, int H, int P, const float *planes, const float *ray_weight, const char *path) {
+    Bounds2i bounds(Point2i(0, 0), Point2i(W, H));
+    SamplingFilm sf(bounds);
+    const size_t S = static_cast<size_t>(W) * H * P;
+    for (int y = 0; y < H; ++y)
+        for (int x = 0; x < W; ++x)
+            for (int s = 0; s < P; ++s) {
+                const size_t i = (static_cast<size_t>(y) * W + x) * P + s;
+                SampleData sd;
+                for (int c = 0; c < 19; ++c) sd.data[c] = planes[c * S + i];
+                sd.rayWeight = ray_weight[i];
+                sf.AddSample(Point2i(x, y), sd);
+            }
+    std::string error;
+    return DumpSamplingFilmB200(sf, 0, 0, path, &error) ? 0 : -1;
+}

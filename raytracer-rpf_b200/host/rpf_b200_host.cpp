@@ -97,6 +97,38 @@ static bool run(SamplingFilm &film, const RPFB200Options &opt, const rpf_film_de
     return true;
 }
 
+bool DumpSamplingFilmB200(const SamplingFilm &film, int sampleX0, int sampleY0, const std::string &path, std::string *error) {
+    const int W = film.getWidth(), H = film.getHeight();
+    const size_t spp = (W > 0 && H > 0 && !film.samples.empty() && !film.samples[0].empty()) ? film.samples[0][0].size() : 0;
+    if (spp == 0) {
+        if (error) *error = "empty SamplingFilm";
+        return false;
+    }
+    const size_t S = static_cast<size_t>(W) * H * spp;
+    std::vector<float> planes(static_cast<size_t>(RPF_NUM_CHANNELS) * S), rayWeight(S);
+    for (int x = 0; x < W; ++x)
+        for (int y = 0; y < H; ++y) {
+            const SampleDataSet &px = film.samples[x][y];
+            if (px.size() != spp) {
+                if (error) *error = "SamplingFilm has a ragged sample count";
+                return false;
+            }
+            const size_t base = (static_cast<size_t>(y) * W + x) * spp;
+            for (size_t s = 0; s < spp; ++s) {
+                for (int c = 0; c < RPF_NUM_CHANNELS; ++c) planes[c * S + base + s] = static_cast<float>(px[s].data[c]);
+                rayWeight[base + s] = px[s].rayWeight;
+            }
+        }
+    const float *ptrs[RPF_NUM_CHANNELS];
+    for (int c = 0; c < RPF_NUM_CHANNELS; ++c) ptrs[c] = planes.data() + c * S;
+    rpf_buffer_info info{W, H, static_cast<int>(spp), sampleX0, sampleY0, 1};
+    if (rpf_buffer_write(path.c_str(), &info, ptrs, rayWeight.data()) != RPF_OK) {
+        if (error) *error = "cannot write " + path;
+        return false;
+    }
+    return true;
+}
+
 bool ApplyRPFFilterB200(SamplingFilm &film, const RPFB200Options &opt, RPFB200Report *report, std::string *error) {
     return run(film, opt, nullptr, nullptr, report, error);
 }

@@ -43,6 +43,10 @@ bool ApplyRPFFilterB200(SamplingFilm &samplingFilm, const RPFB200Options &option
 bool ApplyRPFFilterAndFilmB200(SamplingFilm &samplingFilm, const RPFB200Options &options, const rpf_film_desc &film,
                                std::vector<float> *rgb, RPFB200Report *report, std::string *error);
 
+// Dump hook: writes the SamplingFilm as a feature-buffer file (include/rpf_b200.h rpf_buffer_write;
+// lossless, unlike the debug EXRs of visualizeSF, rpf.cpp:37-101) so a frame rendered once can be filtered anywhere.
+bool DumpSamplingFilmB200(const SamplingFilm &samplingFilm, int sampleX0, int sampleY0, const std::string &path, std::string *error);
+
 // What the GPU needs to know about a pbrt Film, from its public parts: the filter (core/film.h:78, filter.h:47-58), the
 // bounds, and the two private scalars the caller passes in (Film "scale" and "maxsampleluminance" scene parameters,
 // core/film.cpp:213-251). The table is the Film constructor's (core/film.cpp:69-77). A template so that this header does

@@ -25,6 +25,7 @@ ABI_SYMBOLS = [
     "rpf_download_colors", "rpf_download_colors_f64", "rpf_download_debug", "rpf_reconstruct_box",
     "rpf_get_stats", "rpf_reset_stats", "rpf_set_profiling", "rpf_get_kernel_times", "rpf_max_neighbourhood",
     "rpf_synth_planes", "rpf_reconstruct_film", "rpf_film_filter_table",
+    "rpf_buffer_write", "rpf_buffer_info_read", "rpf_buffer_read",
 ]
 
 
@@ -57,6 +58,36 @@ def film_filter_table(kind, rx, ry, alpha=2.0):
     if rc != 0:
         raise RPFError(f"rpf_film_filter_table failed ({rc})")
     return t
+
+
+class BufferInfo(C.Structure):
+    _fields_ = [("width", C.c_int), ("height", C.c_int), ("spp", C.c_int), ("sample_x0", C.c_int), ("sample_y0", C.c_int),
+                ("has_ray_weight", C.c_int)]
+
+
+def write_buffer(path, planes, width, height, spp, ray_weight=None, sample_origin=(0, 0)):
+    """Feature-buffer file (csrc/rpf_io.cpp): 19 float32 planes + optional ray weights."""
+    assert planes.dtype == np.float32 and planes.shape == (NCH, width * height * spp) and planes.flags.c_contiguous
+    info = BufferInfo(width, height, spp, sample_origin[0], sample_origin[1], 0)
+    ptrs = (C.c_void_p * NCH)(*[planes[c].ctypes.data for c in range(NCH)])
+    rw = None if ray_weight is None else np.ascontiguousarray(ray_weight, np.float32)
+    rc = lib().rpf_buffer_write(path.encode(), C.byref(info), ptrs, None if rw is None else _p(rw))
+    if rc != 0:
+        raise RPFError(f"rpf_buffer_write({path}) failed ({rc})")
+
+
+def read_buffer(path):
+    """-> (planes [19, S] float32, ray_weight [S] float32, info dict)"""
+    info = BufferInfo()
+    rc = lib().rpf_buffer_info_read(path.encode(), C.byref(info))
+    if rc != 0:
+        raise RPFError(f"{path}: not a feature-buffer file ({rc})")
+    S = info.width * info.height * info.spp
+    planes, rw = np.empty((NCH, S), np.float32), np.empty(S, np.float32)
+    rc = lib().rpf_buffer_read(path.encode(), _p(planes), _p(rw))
+    if rc != 0:
+        raise RPFError(f"{path}: truncated or unreadable ({rc})")
+    return planes, rw, {k: getattr(info, k) for k, _ in BufferInfo._fields_}
 
 
 KERNEL_NAMES = ["pixel_stats_kernel", "rpf_pixel_kernel", "membership_kernel", "ordered_stats_kernel", "dependency_kernel",

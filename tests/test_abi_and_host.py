@@ -96,3 +96,54 @@ def test_host_cpp_reports_missing_device():
     rc = lib.host_apply_rpf_b200(W, H, P, planes.ctypes.data_as(C.c_void_p), col.ctypes.data_as(C.c_void_p),
                                  bx.ctypes.data_as(C.c_void_p), 1, C.c_double(0.5), 0, None, None, err, 512)
     assert rc == -1 and b"rpf_create" in err.value
+
+
+def test_feature_buffer_file_round_trip(tmp_path):
+    """lossless dump / load of the per-sample feature buffer (host code, no GPU)."""
+    import numpy as np
+    import rpf_b200
+    W, H, P = 9, 7, 3
+    planes = rpf_b200.synth_planes(W, H, P, seed=5, kind=1)
+    rw = np.linspace(0.1, 1.0, W * H * P).astype(np.float32)
+    path = str(tmp_path / "frame.rpfb")
+    rpf_b200.write_buffer(path, planes, W, H, P, ray_weight=rw, sample_origin=(-2, 3))
+    got, grw, info = rpf_b200.read_buffer(path)
+    assert np.array_equal(got, planes) and np.array_equal(grw, rw)
+    assert info == dict(width=W, height=H, spp=P, sample_x0=-2, sample_y0=3, has_ray_weight=1)
+    # no ray weights stored -> ones
+    rpf_b200.write_buffer(path, planes, W, H, P)
+    _, grw, info = rpf_b200.read_buffer(path)
+    assert info["has_ray_weight"] == 0 and np.all(grw == 1.0)
+    # truncated file and foreign file are errors, not garbage
+    raw = open(path, "rb").read()
+    open(path, "wb").write(raw[:len(raw) // 2])
+    import pytest
+    with pytest.raises(rpf_b200.RPFError, match="truncated"):
+        rpf_b200.read_buffer(path)
+    open(path, "wb").write(b"EXR!" + raw[4:])
+    with pytest.raises(rpf_b200.RPFError, match="not a feature-buffer"):
+        rpf_b200.read_buffer(path)
+
+
+def test_host_cpp_dump_hook_round_trip(tmp_path):
+    """DumpSamplingFilmB200 over a real reference SamplingFilm -> file -> read_buffer gives the samples back."""
+    import ctypes as C
+    import os
+    import numpy as np
+    import pytest
+    import oracle_bind as ob
+    import rpf_b200
+    path = os.path.join(ob.ORACLE_DIR, "_ref", "libhost_harness.so")
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref/libhost_harness.so was not built (needs /root/reference at build time)")
+    lib = C.CDLL(path)
+    if not hasattr(lib, "host_dump_sampling_film"):
+        pytest.skip("prebuilt harness predates the dump hook")
+    W, H, P = 6, 5, 4
+    planes = rpf_b200.synth_planes(W, H, P, seed=8, kind=0)
+    rw = np.linspace(0.5, 1.0, W * H * P).astype(np.float32)
+    out = str(tmp_path / "dump.rpfb")
+    lib.host_dump_sampling_film.argtypes = [C.c_int] * 3 + [C.c_void_p] * 2 + [C.c_char_p]
+    assert lib.host_dump_sampling_film(W, H, P, planes.ctypes.data, rw.ctypes.data, out.encode()) == 0
+    got, grw, info = rpf_b200.read_buffer(out)
+    assert np.array_equal(got, planes) and np.array_equal(grw, rw) and info["spp"] == P
