@@ -122,6 +122,7 @@ __global__ void __launch_bounds__(KM_MAX_THREADS) membership_kernel(const Member
 
 // =====================================================================================================
 constexpr int KO_WARPS = 4;  // pixels per CTA of the ordered statistics kernel
+constexpr int KO_GROUP = 8;  // mask words decoded per round
 
 __global__ void __launch_bounds__(KO_WARPS * 32) ordered_stats_kernel(const GeneralParams p) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -156,31 +157,48 @@ __global__ void __launch_bounds__(KO_WARPS * 32) ordered_stats_kernel(const Gene
     // then the mask in candidate order, skipping the centre pixel (already taken). Per mask word the 32 lanes decode
     // one candidate each and compact the accepted sample indices (in order) into a per-warp list; then every lane
     // walks that list for its own channel, loads batched eight ahead of the dependent adds.
-    __shared__ uint32_t glist[KO_WARPS][32];
+    // KO_GROUP mask words (KO_GROUP*32 candidates) are decoded per round, so that the dependent gather below runs over a
+    // few dozen samples at a time with two batches of loads in flight instead of the handful one mask word holds.
+    __shared__ uint32_t glist[KO_WARPS][KO_GROUP * 32];
+    uint32_t *gl = glist[warp];
     const int BP = B * P;
     const int tc0 = (bd * B + bd) * P;  // candidate numbers of the centre pixel: [tc0, tc0 + P)
     const int nwords = (B * BP + 31) >> 5;
-    for (int w = 0; w < nwords; ++w) {
-        unsigned bits = mask[w];
-        if (bits == 0u) continue;
-        const int t = w * 32 + lane;
-        const bool on = ((bits >> lane) & 1u) && !(t >= tc0 && t < tc0 + P);
-        const unsigned eff = __ballot_sync(0xffffffffu, on);
-        if (eff == 0u) continue;
-        if (on) {
-            const int bx = t / BP, r = t - bx * BP, by = r / P, s = r - by * P;
-            glist[warp][__popc(eff & ((1u << lane) - 1u))] =
-                static_cast<uint32_t>((static_cast<size_t>(py - bd + by) * W + (px - bd + bx)) * P + s);
+    for (int w0 = 0; w0 < nwords; w0 += KO_GROUP) {
+        const unsigned myw = (lane < KO_GROUP && w0 + lane < nwords) ? mask[w0 + lane] : 0u;
+        if (__ballot_sync(0xffffffffu, myw != 0u) == 0u) continue;
+        int cnt = 0;
+#pragma unroll
+        for (int j = 0; j < KO_GROUP; ++j) {
+            const unsigned bits = __shfl_sync(0xffffffffu, myw, j);
+            if (bits == 0u) continue;  // warp-uniform
+            const int t = (w0 + j) * 32 + lane;
+            const bool on = ((bits >> lane) & 1u) && !(t >= tc0 && t < tc0 + P);
+            const unsigned eff = __ballot_sync(0xffffffffu, on);
+            if (on) {
+                const int bx = t / BP, r = t - bx * BP, by = r / P, s = r - by * P;
+                gl[cnt + __popc(eff & ((1u << lane) - 1u))] =
+                    static_cast<uint32_t>((static_cast<size_t>(py - bd + by) * W + (px - bd + bx)) * P + s);
+            }
+            cnt += __popc(eff);
         }
         __syncwarp();
-        const int cnt = __popc(eff);
-        for (int i0 = 0; i0 < cnt; i0 += 8) {
-            double v[8];
+        if (cnt) {
+            double v[8], u[8];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) v[i] = fetch(glist[warp][min(i0 + i, cnt - 1)]);
+            for (int i = 0; i < 8; ++i) v[i] = fetch(gl[min(i, cnt - 1)]);
+            for (int i0 = 0; i0 < cnt; i0 += 16) {
 #pragma unroll
-            for (int i = 0; i < 8; ++i)
-                if (i0 + i < cnt) take(v[i]);
+                for (int i = 0; i < 8; ++i) u[i] = fetch(gl[min(i0 + 8 + i, cnt - 1)]);
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                    if (i0 + i < cnt) take(v[i]);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) v[i] = fetch(gl[min(i0 + 16 + i, cnt - 1)]);
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                    if (i0 + 8 + i < cnt) take(u[i]);
+            }
         }
         N += cnt;
         __syncwarp();
