@@ -14,6 +14,7 @@
 #include "rpf_general.cuh"
 #include "rpf_membership.cuh"
 #include "rpf_large.cuh"
+#include "rpf_blend_wide.cuh"
 
 using namespace rpf;
 
@@ -300,10 +301,11 @@ extern "C" int rpf_create(rpf_ctx **out, const rpf_config *cfg) {
         CUC(cudaFuncSetAttribute(dependency_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  227 * 1024 - ctx->kb_static_smem - 1024));
         CUC(cudaFuncSetAttribute(membership_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CUC(cudaFuncSetAttribute(blend_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
         CUC(cudaFuncSetAttribute(dependency_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (228 * 1024) / 2 - ctx->kb_static_smem - 1024));
         ctx->num_sms = prop.multiProcessorCount;
-        CUC(cudaMalloc(&ctx->d_work, sizeof(unsigned int)));
+        CUC(cudaMalloc(&ctx->d_work, 2 * sizeof(unsigned int)));
         ctx->force_large = (cfg->flags & RPF_FLAG_FORCE_LARGE) || (getenv("RPF_FORCE_LARGE") && atoi(getenv("RPF_FORCE_LARGE")));
         ctx->force_general = ctx->force_large || (cfg->flags & RPF_FLAG_FORCE_GENERAL) ||
                              (getenv("RPF_FORCE_GENERAL") && atoi(getenv("RPF_FORCE_GENERAL")));
@@ -373,18 +375,23 @@ static const int kGeneralMaxCandidates = 65535;  // u16 candidate numbers and hi
 // after the fixed tables goes to the histogram region (more slots = more warp teams); the bin bytes stay in shared
 // memory only if eight full-size histograms still fit beside them, otherwise they go to an L2-resident per-CTA scratch.
 static bool plan_general(long long ncap, int spp, int static_smem, GeneralPlan &L) {
-    if (ncap > kGeneralMaxCandidates) return false;
+    if (ncap > kLargeMaxCandidates) return false;
+    L = GeneralPlan{};
     L.ncap = static_cast<int>(ncap);
     L.mw = ((L.ncap + 127) / 128) * 4;
-    L.nq = (L.ncap + 3) / 4;
-    const int nb = bins_for(L.ncap);
+    // Beyond 65,535 candidates this kernel still serves every pixel whose ACCEPTED count N stays within 65,535 (u16
+    // cells, u8 bins): candidate numbers then go to a 32-bit list in HBM and the per-sample sizes are capped at 65,535.
+    L.idx_global = ncap > kGeneralMaxCandidates;
+    const int neff = L.idx_global ? kGeneralMaxCandidates : L.ncap;
+    L.nq = (neff + 3) / 4;
+    const int nb = bins_for(neff);
     L.nbs = (nb + 3) & ~3;
     L.hw = (((nb * nb + 1) / 2) + 3) & ~3;
     L.off_gsm = 0;
     L.off_marg = KB_GSM * 8;
     L.off_region = align16(L.off_marg + NCH * L.nbs * 4);
     L.kc_smem = spp * 18 * 8;
-    const int idx_bytes = align16(2 * L.ncap);
+    const int idx_bytes = L.idx_global ? 0 : align16(2 * L.ncap);
     const int bins_bytes = NCH * L.nq * 4;
     const int hist_bytes = L.hw * 4;
     auto atleast = [&](int n) { const int h = n * hist_bytes; return h > idx_bytes ? h : idx_bytes; };
@@ -476,13 +483,20 @@ static int ensure_pstat(rpf_ctx *ctx, const FrameView &f, int y0, int y1) {
 static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
     GeneralParams p{};
     const long long ncap = 1ll * box * box * ctx->cfg.spp;
-    const bool planned = (!ctx->force_large && plan_general(ncap, ctx->cfg.spp, ctx->kb_static_smem, p.pl)) ||
-                         plan_large(ncap, ctx->cfg.spp, ctx->kb_static_smem, p.pl);
-    if (!planned)
+    // Up to 65,535 candidates: dependency_kernel. Beyond: dependency_kernel for the pixels that accept at most 65,535
+    // samples and dependency_large_kernel (plan pl_large) for the rest. RPF_FLAG_FORCE_LARGE: the large kernel only.
+    GeneralPlan pl_large{};
+    bool use_small = !ctx->force_large && plan_general(ncap, ctx->cfg.spp, ctx->kb_static_smem, p.pl);
+    const bool use_large = (!use_small || p.pl.idx_global) && plan_large(ncap, ctx->cfg.spp, ctx->kb_static_smem, pl_large);
+    if (use_small && p.pl.idx_global && !use_large) use_small = false;
+    if (!use_small && !use_large)
         return fail(ctx, RPF_ERR_UNSUPPORTED, "neighbourhood of box %d x %d spp = %lld candidates exceeds this build (max %d)", box,
                     ctx->cfg.spp, ncap, kLargeMaxCandidates);
-    if (p.pl.kc_smem > 40 * 1024) return fail(ctx, RPF_ERR_UNSUPPORTED, "spp %d too large for the blend kernel", ctx->cfg.spp);
-    int rc = p.pl.large ? ensure_hql(ctx, p.pl.ncap) : ensure_gtab(ctx, p.pl.ncap);
+    if (!use_small) p.pl = pl_large;
+    if ((KW_THREADS * KW_ZS + ctx->cfg.spp * 18) * 8 > 100 * 1024) return fail(ctx, RPF_ERR_UNSUPPORTED, "spp %d too large for the blend kernel", ctx->cfg.spp);
+    int rc = RPF_OK;
+    if (use_large) rc = ensure_hql(ctx, pl_large.ncap);
+    if (rc == RPF_OK && use_small) rc = ensure_gtab(ctx, p.pl.idx_global ? kGeneralMaxCandidates : p.pl.ncap);
     if (rc != RPF_OK) return rc;
     p.f = FrameView{ctx->d_planes, ctx->S, ctx->cfg.width, ctx->cfg.height, ctx->cfg.spp};
     rc = ensure_pstat(ctx, p.f, y0, y1);
@@ -492,19 +506,35 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
     long long rows = static_cast<long long>(ctx->scratch_budget / (per_pixel * W));
     if (rows < 1) rows = 1;
     if (rows > y1 - y0) rows = y1 - y0;
-    int occ = 0;
-    if (p.pl.large) CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dependency_large_kernel, KL_THREADS, p.pl.kb_smem));
-    else if (p.pl.nt == 512) CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dependency_kernel<512>, 512, p.pl.kb_smem));
-    else CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dependency_kernel<1024>, 1024, p.pl.kb_smem));
-    if (occ < 1) return fail(ctx, RPF_ERR_CUDA, "dependency kernel does not fit on an SM with %d bytes of shared memory", p.pl.kb_smem);
     const long long chunk_px = rows * W;
-    p.pl.kb_grid = static_cast<int>(chunk_px < 1ll * occ * ctx->num_sms ? chunk_px : 1ll * occ * ctx->num_sms);
+    auto grid_for = [&](GeneralPlan &L) -> int {
+        int occ = 0;
+        cudaError_t e;
+        if (L.large) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dependency_large_kernel, KL_THREADS, L.kb_smem);
+        else if (L.nt == 512) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dependency_kernel<512>, 512, L.kb_smem);
+        else e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dependency_kernel<1024>, 1024, L.kb_smem);
+        if (e != cudaSuccess || occ < 1) return 0;
+        L.kb_grid = static_cast<int>(chunk_px < 1ll * occ * ctx->num_sms ? chunk_px : 1ll * occ * ctx->num_sms);
+        return L.kb_grid;
+    };
+    if (!grid_for(p.pl) || (use_small && use_large && !grid_for(pl_large)))
+        return fail(ctx, RPF_ERR_CUDA, "dependency kernel does not fit on an SM with %d bytes of shared memory", p.pl.kb_smem);
     if ((rc = ensure_buffer(ctx, &ctx->d_mask, &ctx->mask_bytes, static_cast<size_t>(chunk_px) * p.pl.mw * 4)) != RPF_OK) return rc;
     if ((rc = ensure_buffer(ctx, &ctx->d_rec, &ctx->rec_bytes, static_cast<size_t>(chunk_px) * REC_DOUBLES * 8)) != RPF_OK) return rc;
-    if (p.pl.large) {
-        p.big_stride = static_cast<size_t>(p.pl.nq) * 168;  // 4 B candidate number + 19 u16 bins per candidate, rows padded to 4
-        if ((rc = ensure_buffer(ctx, &ctx->d_big, &ctx->big_bytes, static_cast<size_t>(p.pl.kb_grid) * p.big_stride)) != RPF_OK) return rc;
-    } else if (!p.pl.bins_in_smem &&
+    // big_scratch per persistent CTA: the large kernel keeps 4 B candidate number + 19 u16 bins per candidate (rows padded
+    // to 4); dependency_kernel beyond 65,535 candidates keeps its 32-bit candidate list there
+    const GeneralPlan &PL = use_large ? (use_small ? pl_large : p.pl) : p.pl;
+    size_t big_stride = 0;
+    int big_grid = 0;
+    if (use_large) { big_stride = static_cast<size_t>(PL.nq) * 168; big_grid = PL.kb_grid; }
+    if (use_small && p.pl.idx_global) {
+        const size_t st = (static_cast<size_t>(p.pl.ncap) * 4 + 15) & ~static_cast<size_t>(15);
+        if (st > big_stride) big_stride = st;
+        if (p.pl.kb_grid > big_grid) big_grid = p.pl.kb_grid;
+    }
+    p.big_stride = big_stride;
+    if (big_stride && (rc = ensure_buffer(ctx, &ctx->d_big, &ctx->big_bytes, static_cast<size_t>(big_grid) * big_stride)) != RPF_OK) return rc;
+    if (use_small && !p.pl.bins_in_smem &&
         (rc = ensure_buffer(ctx, &ctx->d_bins, &ctx->bins_bytes, static_cast<size_t>(p.pl.kb_grid) * NCH * p.pl.nq * 4)) != RPF_OK)
         return rc;
     if (!ctx->d_rec16) {
@@ -526,8 +556,10 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
     p.pstat = ctx->d_pstat;
     p.gq = ctx->d_gq;
     p.hq = p.pl.large ? ctx->d_hql : ctx->d_hq;
+    p.large_min_n = 0;
     p.big_scratch = ctx->d_big;
     p.box = box;
+    p.cd = make_cand_decode(box, ctx->cfg.spp);
     p.flags = ctx->cfg.flags;
     p.seed = seed;
     p.mask = ctx->d_mask;
@@ -543,7 +575,7 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
         p.row0 = r0;
         p.nrows = r0 + rows <= y1 ? static_cast<int>(rows) : y1 - r0;
         const unsigned npx = static_cast<unsigned>(p.nrows * W);
-        CU(ctx, cudaMemsetAsync(ctx->d_work, 0, sizeof(unsigned int), ctx->stream));
+        CU(ctx, cudaMemsetAsync(ctx->d_work, 0, 2 * sizeof(unsigned int), ctx->stream));
         {
             MembershipParams m{};
             m.f = p.f;
@@ -572,9 +604,22 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
         if (p.pl.large) dependency_large_kernel<<<gridb, KL_THREADS, p.pl.kb_smem, ctx->stream>>>(p);
         else if (p.pl.nt == 512) dependency_kernel<512><<<gridb, 512, p.pl.kb_smem, ctx->stream>>>(p);
         else dependency_kernel<1024><<<gridb, 1024, p.pl.kb_smem, ctx->stream>>>(p);
+        if (use_small && use_large) {  // the pixels dependency_kernel left: more than 65,535 accepted samples
+            GeneralParams q = p;
+            q.pl = pl_large;
+            q.hq = ctx->d_hql;
+            q.large_min_n = kGeneralMaxCandidates + 1;
+            q.work_counter = ctx->d_work + 1;
+            const unsigned gridl = npx < static_cast<unsigned>(pl_large.kb_grid) ? npx : static_cast<unsigned>(pl_large.kb_grid);
+            dependency_large_kernel<<<gridl, KL_THREADS, pl_large.kb_smem, ctx->stream>>>(q);
+            ctx->launches++;
+        }
         prof_end(ctx);
         prof_begin(ctx, RPF_K_BLEND);
-        blend_kernel<<<npx, KC_THREADS, p.pl.kc_smem, ctx->stream>>>(p);
+        // few samples per pixel: a thread per neighbour with the own samples' accumulators in registers; many: own samples
+        // across threads, neighbours staged through shared memory (rpf_blend_wide.cuh)
+        if (ctx->cfg.spp > 16) blend_wide_kernel<<<npx, KW_THREADS, (KW_THREADS * KW_ZS + ctx->cfg.spp * 18) * 8, ctx->stream>>>(p);
+        else blend_kernel<<<npx, KC_THREADS, p.pl.kc_smem, ctx->stream>>>(p);
         prof_end(ctx);
         ctx->launches += 4;
         CU(ctx, cudaGetLastError());

@@ -37,11 +37,35 @@ struct GeneralPlan {
     int region_words;  // capacity of the histogram region in 32-bit words
     int kb_grid;
     int kc_smem;
+    int idx_global;  // 1: box*box*spp > 65,535: candidate numbers are 32-bit and live in big_scratch; pixels with N > 65,535 are left
+                     //    to dependency_large_kernel
     int large;       // 1: dependency_large_kernel (rpf_large.cuh): u32 candidates, u16 bins, u32 cells, slabbed tables
 };
 
+// Candidate number t -> (box column bx, box row by, sample s) without integer division: t / d = (t * ceil(2^40 / d)) >> 40,
+// exact while t * d < 2^40 (t < 2^20 candidates, d = box*spp or spp < 2^20).
+struct CandDecode {
+    unsigned long long mBP, mP;
+    int BP, P;
+};
+inline CandDecode make_cand_decode(int box, int spp) {
+    CandDecode d;
+    d.BP = box * spp;
+    d.P = spp;
+    d.mBP = ((1ull << 40) + d.BP - 1) / d.BP;
+    d.mP = ((1ull << 40) + d.P - 1) / d.P;
+    return d;
+}
+__device__ __forceinline__ void cand_split(const CandDecode &d, int t, int &bx, int &by, int &s) {
+    bx = static_cast<int>((static_cast<unsigned long long>(t) * d.mBP) >> 40);
+    const int r = t - bx * d.BP;
+    by = static_cast<int>((static_cast<unsigned long long>(r) * d.mP) >> 40);
+    s = r - by * d.P;
+}
+
 struct GeneralParams {
     FrameView f;
+    CandDecode cd;
     const double *col_in;
     double *col_out;
     const double *pstat;
@@ -59,6 +83,7 @@ struct GeneralParams {
     uint8_t *bins_scratch;  // [kb_grid][19][nq*4] when bins do not fit in shared memory
     uint8_t *big_scratch;   // rpf_large.cuh: [kb_grid][big_stride] candidate list + u16 bins of one pixel
     size_t big_stride;
+    int large_min_n;        // dependency_large_kernel skips pixels with fewer accepted samples (0: takes all)
     unsigned int *work_counter;
     GeneralPlan pl;
     int *dbg_n;
@@ -83,9 +108,11 @@ __device__ __forceinline__ float warp_max_f(float v) {
 }
 
 // candidate t -> global sample index, or false when the neighbour pixel is out of bounds (rpf.cpp:569)
-__device__ __forceinline__ bool candidate_sample(int t, int px, int py, int B, int P, int W, int H, uint32_t &g, bool &centre) {
-    const int BP = B * P, bd = (B - 1) / 2;
-    const int bx = t / BP, r = t - bx * BP, by = r / P, s = r - by * P;
+__device__ __forceinline__ bool candidate_sample(const CandDecode &cd, int t, int px, int py, int B, int P, int W, int H, uint32_t &g,
+                                                 bool &centre) {
+    const int bd = (B - 1) / 2;
+    int bx, by, s;
+    cand_split(cd, t, bx, by, s);
     const int xn = px - bd + bx, yn = py - bd + by;
     centre = (xn == px) && (yn == py);
     if (xn < 0 || xn >= W || yn < 0 || yn >= H) return false;
@@ -387,6 +414,7 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
     unsigned *marg = reinterpret_cast<unsigned *>(smem + L.off_marg);  // [19][nbs]
     unsigned *region = reinterpret_cast<unsigned *>(smem + L.off_region);
     unsigned short *idx16 = reinterpret_cast<unsigned short *>(region);
+    uint32_t *idx32 = reinterpret_cast<uint32_t *>(p.big_scratch + static_cast<size_t>(blockIdx.x) * p.big_stride);
     uint32_t *bins = L.bins_in_smem ? reinterpret_cast<uint32_t *>(smem + L.off_bins)
                                     : reinterpret_cast<uint32_t *>(p.bins_scratch + static_cast<size_t>(blockIdx.x) * NCH * L.nq * 4);
     const int nq = L.nq;
@@ -407,6 +435,7 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
 
         // ---- per-channel constants --------------------------------------------------------------------
         const int N = static_cast<int>(rec[REC_N]);
+        if (N > 65535) continue;  // block-uniform: u16 cells / u8 bins stop here; dependency_large_kernel takes the pixel
         int nb = static_cast<int>(__dsqrt_rn(static_cast<double>(N)));  // mi.cpp:53-58
         if (nb < 1) nb = 1;
         const double dnb = static_cast<double>(nb);
@@ -427,7 +456,8 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
                 while (bits) {
                     const int b = __ffs(bits) - 1;
                     bits &= bits - 1;
-                    idx16[off++] = static_cast<unsigned short>(w * 32 + b);
+                    if (L.idx_global) idx32[off++] = static_cast<uint32_t>(w * 32 + b);
+                    else idx16[off++] = static_cast<unsigned short>(w * 32 + b);
                 }
             }
         }
@@ -439,10 +469,11 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
             uint8_t *bin8 = reinterpret_cast<uint8_t *>(bins);
             const int cstride = nq * 4;
             for (unsigned m = tid; m < uN; m += NT) {
-                const int t = idx16[(m * Q) % uN];
+                const unsigned slot = (m * Q) % uN;
+                const int t = L.idx_global ? static_cast<int>(idx32[slot]) : idx16[slot];
                 uint32_t g;
                 bool centre;
-                candidate_sample(t, px, py, B, P, W, H, g, centre);
+                candidate_sample(p.cd, t, px, py, B, P, W, H, g, centre);
                 const float4 *r16 = p.rec16 + static_cast<size_t>(g) * 4;
                 const double4 cc = p.col4[g];
                 auto put = [&](int c, double x) {
@@ -611,7 +642,7 @@ __global__ void __launch_bounds__(KC_THREADS, 4) blend_kernel(const GeneralParam
                 const int t = seg * (KC_SEG_WORDS * 32) + segidx[n];
                 uint32_t g;
                 bool centre;
-                candidate_sample(t, px, py, B, P, W, H, g, centre);
+                candidate_sample(p.cd, t, px, py, B, P, W, H, g, centre);
                 double zj[NWZ], cj[NC];
                 load_z(g, zj, cj);
 #pragma unroll

@@ -113,6 +113,7 @@ __global__ void __launch_bounds__(KL_THREADS, 1) dependency_large_kernel(const G
         double *rec = p.rec + static_cast<size_t>(pl) * REC_DOUBLES;
 
         const int N = static_cast<int>(rec[REC_N]);
+        if (N < p.large_min_n) continue;  // block-uniform: dependency_kernel has done this pixel
         int nb = static_cast<int>(__dsqrt_rn(static_cast<double>(N)));  // mi.cpp:53-58
         if (nb < 1) nb = 1;
         const double dnb = static_cast<double>(nb);
@@ -146,7 +147,7 @@ __global__ void __launch_bounds__(KL_THREADS, 1) dependency_large_kernel(const G
                 const int t = static_cast<int>(sc.idx[(m * Q) % uN]);
                 uint32_t g;
                 bool centre;
-                candidate_sample(t, px, py, B, P, W, H, g, centre);
+                candidate_sample(p.cd, t, px, py, B, P, W, H, g, centre);
                 const float4 *r16 = p.rec16 + static_cast<size_t>(g) * 4;
                 const double4 cc = p.col4[g];
                 auto put = [&](int c, double x) {

@@ -60,7 +60,7 @@ __global__ void __launch_bounds__(KM_MAX_THREADS) membership_kernel(const Member
         for (int k = 0; k < NF; ++k) { mu[k] = 0.0; sd3[k] = 0.0; }
     }
     uint32_t *mrow = p.mask + (static_cast<size_t>(py - p.row0) * W + px) * p.mw;
-    uint32_t buf = 0;
+    unsigned long long buf = 0ull;
     int nbits = 0, wi = 0;
 
     const int nrows = p.col_rows;  // rows of neighbour pixels a column holds for this tile: yn = y0 - bd + r
@@ -93,29 +93,41 @@ __global__ void __launch_bounds__(KM_MAX_THREADS) membership_kernel(const Member
                     const bool inb = xin && yn >= 0 && yn < H;
                     const bool centre = xn == px && yn == py;
                     const double *cp = col + (ly + by - r0) * RS;
-                    for (int s = 0; s < P; ++s, cp += NF) {
-                        bool acc = inb;
-                        if (inb && !centre) {
-                            // allLessThan(|f - mu|, 3 sigma): reject on >= ; a NaN sigma accepts (ops.h:100-107)
+                    // a neighbour pixel's P acceptance bits are collected in a register and appended to the 64-bit
+                    // bit buffer at once (chunks of 32 samples when spp is larger)
+                    for (int s0 = 0; s0 < P; s0 += 32) {
+                        const int ns = min(32, P - s0);
+                        uint32_t bits = 0u;
+                        for (int s = 0; s < ns; ++s, cp += NF) {
+                            bool acc = inb;
+                            if (inb && !centre) {
+                                // allLessThan(|f - mu|, 3 sigma): reject on >= ; a NaN sigma accepts (ops.h:100-107)
 #pragma unroll
-                            for (int k = 0; k < 4; ++k)
-                                if (fabs(__dsub_rn(cp[k], mu[k])) >= sd3[k]) acc = false;
-                            // most candidates fail early; skip the rest when no lane running here is still in
-                            if (__ballot_sync(__activemask(), acc)) {
-#pragma unroll
-                                for (int k = 4; k < NF; ++k)
+                                for (int k = 0; k < 4; ++k)
                                     if (fabs(__dsub_rn(cp[k], mu[k])) >= sd3[k]) acc = false;
+                                // most candidates fail early; skip the rest when no lane running here is still in
+                                if (__ballot_sync(__activemask(), acc)) {
+#pragma unroll
+                                    for (int k = 4; k < NF; ++k)
+                                        if (fabs(__dsub_rn(cp[k], mu[k])) >= sd3[k]) acc = false;
+                                }
                             }
+                            bits |= static_cast<uint32_t>(acc) << s;
                         }
-                        buf |= static_cast<uint32_t>(acc) << nbits;
-                        if (++nbits == 32) { mrow[wi++] = buf; buf = 0; nbits = 0; }
+                        buf |= static_cast<unsigned long long>(bits) << nbits;
+                        nbits += ns;
+                        if (nbits >= 32) {
+                            mrow[wi++] = static_cast<uint32_t>(buf);
+                            buf >>= 32;
+                            nbits -= 32;
+                        }
                     }
                 }
             }
         }
     }
     if (live) {
-        if (nbits) mrow[wi++] = buf;
+        if (nbits) mrow[wi++] = static_cast<uint32_t>(buf);
         for (; wi < p.mw; ++wi) mrow[wi] = 0u;
     }
 }
@@ -176,7 +188,8 @@ __global__ void __launch_bounds__(KO_WARPS * 32) ordered_stats_kernel(const Gene
             const bool on = ((bits >> lane) & 1u) && !(t >= tc0 && t < tc0 + P);
             const unsigned eff = __ballot_sync(0xffffffffu, on);
             if (on) {
-                const int bx = t / BP, r = t - bx * BP, by = r / P, s = r - by * P;
+                int bx, by, s;
+                cand_split(p.cd, t, bx, by, s);
                 gl[cnt + __popc(eff & ((1u << lane) - 1u))] =
                     static_cast<uint32_t>((static_cast<size_t>(py - bd + by) * W + (px - bd + bx)) * P + s);
             }

@@ -127,7 +127,22 @@ def test_large_kernel_matches_oracle(W, H, P, boxes, seed, kind):
     _compare(g, o, W, H, P)
 
 
-def test_large_kernel_beyond_255_bins():
+@pytest.mark.parametrize("W,H,P,boxes,seed", [
+    (12, 10, 64, [35], 0.5),      # 78,400 candidates, N <= 7,680: dependency_kernel with the 32-bit candidate list in HBM
+    (10, 8, 64, [55, 35], 1.0),   # 193,600 / 78,400 candidates
+    (16, 12, 32, [47], 0.3),      # 70,688 candidates
+])
+def test_many_candidates_few_accepted(W, H, P, boxes, seed):
+    """box*box*spp beyond 65,535 while every pixel accepts fewer samples: the regular dependency kernel serves them."""
+    import rpf_b200
+    planes = rpf_b200.synth_planes(W, H, P, seed=91, kind=0)
+    o = ob.oracle_filter(planes, W, H, P, boxes, seed=seed, debug=True)
+    g = _gpu(planes, W, H, P, boxes, seed)
+    _compare(g, o, W, H, P)
+
+
+@pytest.mark.parametrize("rows", [(18, 22), (0, 2)], ids=["all-large", "mixed"])
+def test_large_kernel_beyond_255_bins(rows):
     """N > 65,536 accepted samples: more than 255 bins per axis (u16 bins), and a joint table (nb*nb u32 cells) that
     no longer fits in shared memory at once, so it is built in row slabs. Smooth features make every candidate pass
     the 3-sigma test; 40x40 px x 64 spp inside a 55 box gives N up to 102,400 -> 320 bins, 409 KB per table."""
@@ -135,7 +150,8 @@ def test_large_kernel_beyond_255_bins():
     W, H, P = 40, 40, 64
     planes = rpf_b200.synth_planes(W, H, P, seed=9, kind=0)
     planes[7:19] = (planes[7:19] * 0.0 + np.random.default_rng(5).normal(size=(12, W * H * P))).astype(np.float32)
-    rows = (18, 22)
+    # rows 18-21: every pixel accepts more than 65,535 samples (dependency_large_kernel); rows 0-1: corner pixels stay
+    # below (dependency_kernel), the middle of the row above, so both kernels share one pass
     o = ob.oracle_filter(planes, W, H, P, [55], seed=0.5, debug=True, rows=rows)
     import rpf_b200 as rb
     f = rb.RPFFilter(W, H, P, debug=True)
@@ -149,6 +165,8 @@ def test_large_kernel_beyond_255_bins():
     sel[rows[0] * W:rows[1] * W] = True
     assert np.array_equal(dbg["N"][sel], o["N"][sel])
     assert dbg["N"][sel].max() > 65536
+    if rows[0] == 0:
+        assert dbg["N"][sel].min() <= 65535
     for k in ("alpha", "beta", "wrc"):
         assert np.abs(dbg[k][sel] - o[k][sel]).max() <= TOL_TIGHT, k
     ssel = np.repeat(sel, P)
