@@ -39,9 +39,26 @@ def parse():
     ap.add_argument("--spp", type=int, default=8)
     ap.add_argument("--boxes", default=os.environ.get("RPF_BENCH_BOXES", "55,35,17,7"))
     ap.add_argument("--seed", type=float, default=0.002, help="sigma_fc_seed, reference literal rpf.cpp:533")
+    ap.add_argument("--config", default=None, choices=["sample720", "fullhd", "4k16", "stress64"],
+                    help="BASELINE.json configs[1..4]: 1280x720x8 (default), 1920x1080x8, 3840x2160x16, 1920x1080x64")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
+
+
+CONFIGS = {"sample720": (1280, 720, 8), "fullhd": (1920, 1080, 8), "4k16": (3840, 2160, 16), "stress64": (1920, 1080, 64)}
+
+
+def measured_traffic(kernel, workload_key):
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture (profiles/r1/traffic.json,
+    written by tools/traffic_from_ncu.py): dram__bytes_read.sum + dram__bytes_write.sum, averaged over the launches of
+    one step. None when no capture exists for this workload."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1", "traffic.json")) as f:
+            t = json.load(f)
+        return t[workload_key][kernel]["dram_bytes_per_launch"]
+    except Exception:
+        return None
 
 
 def peaks():
@@ -128,6 +145,8 @@ def cpu_reference_run(args, boxes, steps, warmup):
 
 def main():
     args = parse()
+    if args.config:
+        args.width, args.height, args.spp = CONFIGS[args.config]
     boxes = [int(b) for b in args.boxes.split(",")]
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -240,7 +259,8 @@ def main():
         k_ms, k_n = kern[dom]["ms_total"], kern[dom]["launches"]
         achieved = alg_bytes / (k_ms * 1e-3) / 1e9
         upd = 96 * st["nbh_sum"]  # joint-histogram updates in the timed region: 96 MI pairs x N per pixel-pass
-        roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+        roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": measured_traffic(dom, f"{W}x{H}x{P}:{','.join(map(str, boxes))}") if world == 1 else None,
                 "peak_source": peak_src, "kernel": dom, "kernel_ms_per_launch": k_ms / k_n, "launches_timed": k_n,
                 "algorithmic_bytes_per_launch": alg_bytes / k_n,
                 "note": "the path is bound by shared-memory atomic / FP64 issue, not HBM (DESIGN.md section 4)",
