@@ -165,6 +165,12 @@ def main():
             "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
         return
 
+    # The contract is ONE JSON line on stdout. Libraries write there too (NCCL prints its version banner on fd 1), so the
+    # real stdout is kept aside for the result and fd 1 points at stderr for everything else.
+    sys.stdout.flush()
+    result_fd = os.dup(1)
+    os.dup2(2, 1)
+
     import torch
     import bands
     import rpf_b200
@@ -284,7 +290,8 @@ def main():
         dist.barrier()
         dist.destroy_process_group()
     if rank == 0:
-        print(json.dumps(res))
+        sys.stdout.flush()
+        os.write(result_fd, (json.dumps(res) + "\n").encode())
 
 
 if __name__ == "__main__":

@@ -34,6 +34,7 @@ struct rpf_ctx {
     uint8_t *d_big = nullptr;
     size_t big_bytes = 0;
     bool force_large = false;
+    int blend_wide_min = 17;  // spp from which blend_wide_kernel replaces blend_kernel (RPF_BLEND_WIDE_MIN overrides)
     // general path (rpf_general.cuh): per-chunk scratch in HBM
     uint32_t *d_mask = nullptr;
     double *d_rec = nullptr;
@@ -311,6 +312,7 @@ extern "C" int rpf_create(rpf_ctx **out, const rpf_config *cfg) {
                              (getenv("RPF_FORCE_GENERAL") && atoi(getenv("RPF_FORCE_GENERAL")));
         CUC(cudaFuncSetAttribute(dependency_large_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  227 * 1024 - ctx->kb_static_smem - 1024));
+        if (const char *bw = getenv("RPF_BLEND_WIDE_MIN")) if (atoi(bw) > 0) ctx->blend_wide_min = atoi(bw);
         if (const char *mb = getenv("RPF_SCRATCH_MB")) if (atoll(mb) > 0) ctx->scratch_budget = static_cast<size_t>(atoll(mb)) << 20;
     }
 #undef CUC
@@ -618,7 +620,7 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
         prof_begin(ctx, RPF_K_BLEND);
         // few samples per pixel: a thread per neighbour with the own samples' accumulators in registers; many: own samples
         // across threads, neighbours staged through shared memory (rpf_blend_wide.cuh)
-        if (ctx->cfg.spp > 16) blend_wide_kernel<<<npx, KW_THREADS, (KW_THREADS * KW_ZS + ctx->cfg.spp * 18) * 8, ctx->stream>>>(p);
+        if (ctx->cfg.spp >= ctx->blend_wide_min) blend_wide_kernel<<<npx, KW_THREADS, (KW_THREADS * KW_ZS + ctx->cfg.spp * 18) * 8, ctx->stream>>>(p);
         else blend_kernel<<<npx, KC_THREADS, p.pl.kc_smem, ctx->stream>>>(p);
         prof_end(ctx);
         ctx->launches += 4;
