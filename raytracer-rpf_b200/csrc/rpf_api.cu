@@ -41,6 +41,7 @@ struct rpf_ctx {
     uint8_t *d_bins = nullptr;
     float4 *d_rec16 = nullptr;     // gather-friendly copy of the 16 non-colour planes (general path), valid per upload
     double4 *d_col4 = nullptr;     // current colours as {r,g,b,0}, rebuilt per general pass
+    double *d_rec19 = nullptr;     // all 19 channels as doubles per sample (ordered_stats_kernel); colours rebuilt per pass
     bool rec16_valid = false;
     unsigned int *d_work = nullptr;
     size_t mask_bytes = 0, rec_bytes = 0, bins_bytes = 0;
@@ -151,6 +152,7 @@ extern "C" void rpf_destroy(rpf_ctx *ctx) {
     cudaFree(ctx->d_bins);
     cudaFree(ctx->d_rec16);
     cudaFree(ctx->d_col4);
+    cudaFree(ctx->d_rec19);
     cudaFree(ctx->d_work);
     cudaFree(ctx->d_counters);
     cudaFree(ctx->d_dbg_n);
@@ -542,17 +544,20 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
     if (!ctx->d_rec16) {
         CU(ctx, cudaMalloc(&ctx->d_rec16, ctx->S * 4 * sizeof(float4)));
         CU(ctx, cudaMalloc(&ctx->d_col4, ctx->S * sizeof(double4)));
+        CU(ctx, cudaMalloc(&ctx->d_rec19, ctx->S * REC19 * sizeof(double)));
     }
     if (!ctx->rec16_valid) {
         pack_features_kernel<<<static_cast<unsigned>((4 * ctx->S + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_planes, ctx->S, ctx->d_rec16);
-        ctx->launches++;
+        pack_rec19_kernel<<<static_cast<unsigned>((ctx->S * REC19 + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_planes, ctx->S, ctx->d_rec19);
+        ctx->launches += 2;
         ctx->rec16_valid = true;
     }
-    pack_colors_kernel<<<static_cast<unsigned>((ctx->S + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_col[ctx->cur], ctx->S, ctx->d_col4);
+    pack_colors_kernel<<<static_cast<unsigned>((ctx->S + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_col[ctx->cur], ctx->S, ctx->d_col4, ctx->d_rec19);
     ctx->launches++;
     CU(ctx, cudaGetLastError());
     p.rec16 = ctx->d_rec16;
     p.col4 = ctx->d_col4;
+    p.rec19 = ctx->d_rec19;
     p.col_in = ctx->d_col[ctx->cur];
     p.col_out = ctx->d_col[ctx->cur ^ 1];
     p.pstat = ctx->d_pstat;

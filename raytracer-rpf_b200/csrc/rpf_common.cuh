@@ -13,6 +13,7 @@ constexpr int N_JOINT = 96;             // MI pairs of rpf.cpp:416-442
 constexpr int N_TASK = N_JOINT + NCH;   // + one marginal histogram per channel
 constexpr int N_GROUP = 4;              // task groups of 32 lanes: 3 joint groups + the marginals
 constexpr int THREADS = 128;
+constexpr int REC19 = 20;               // doubles per sample of the all-double gather record (19 channels + pad)
 constexpr int NWZ = 17;                 // channels entering the weights: pos(2) + colour(3) + features(12)
 
 constexpr int FLAG_P1 = 1, FLAG_P2 = 2, FLAG_P3 = 4;

@@ -71,6 +71,7 @@ struct GeneralParams {
     const double *pstat;
     const float4 *rec16;   // [S][4]: the 16 non-colour channels of each sample, slot order (rpf_kernels.cuh)
     const double4 *col4;   // [S]: current colours {r, g, b, 0}
+    const double *rec19;   // [S][REC19]: all 19 channels as doubles, channel order (ordered_stats_kernel)
     // Fixed-point entropy tables (unit 2^-43): gq[k] = round(((k+1)ln(k+1) - k ln k) * 2^43), hq[n] = gq[0]+...+gq[n-1]
     // (~ n ln n). Integer sums are exact and order independent, so the atomics-ordered accumulation is deterministic.
     const unsigned long long *gq;
@@ -96,10 +97,13 @@ __device__ __forceinline__ float warp_min_f(float v) {
     for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
     return v;
 }
+// 64-bit warp sum from three hardware integer reductions (REDUX) over 22-bit slices: a slice sum of 32 lanes stays
+// below 2^27, and the slices add back up exactly.
 __device__ __forceinline__ unsigned long long warp_sum_u64(unsigned long long v) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    return v;
+    const unsigned s0 = __reduce_add_sync(0xffffffffu, static_cast<unsigned>(v) & 0x3fffffu);
+    const unsigned s1 = __reduce_add_sync(0xffffffffu, static_cast<unsigned>(v >> 22) & 0x3fffffu);
+    const unsigned s2 = __reduce_add_sync(0xffffffffu, static_cast<unsigned>(v >> 44));
+    return static_cast<unsigned long long>(s0) + (static_cast<unsigned long long>(s1) << 22) + (static_cast<unsigned long long>(s2) << 44);
 }
 __device__ __forceinline__ float warp_max_f(float v) {
 #pragma unroll
@@ -331,8 +335,11 @@ __device__ __forceinline__ void joint_phase(const GeneralParams &p, KBSmall &ks,
         for (int j = 0; j < G; ++j) {
             uint4 *r4 = reinterpret_cast<uint4 *>(th + j * hwn);
             unsigned long long acc = 0ull;
-            for (int k = tt; k < hwn >> 2; k += tn) {
-                const uint4 v = r4[k];
+            const int nk = hwn >> 2;
+            uint4 vnext = tt < nk ? r4[tt] : make_uint4(0u, 0u, 0u, 0u);
+            for (int k = tt; k < nk; k += tn) {
+                const uint4 v = vnext;  // the next cells are already on their way while these are looked up
+                if (k + tn < nk) vnext = r4[k + tn];
                 const unsigned any = v.x | v.y | v.z | v.w;
                 if (any == 0u) continue;
                 r4[k] = make_uint4(0u, 0u, 0u, 0u);

@@ -60,10 +60,25 @@ __global__ void pack_features_kernel(const float *__restrict__ planes, size_t S,
     for (int k = 0; k < 4; ++k) v[k] = planes[static_cast<size_t>(slot_channel(4 * q + k)) * S + g];
     rec16[i] = make_float4(v[0], v[1], v[2], v[3]);
 }
-__global__ void pack_colors_kernel(const double *__restrict__ col, size_t S, double4 *__restrict__ col4) {
+// rec19[g] = all 19 channels of sample g as doubles in channel order (+1 pad, 160 B): ordered_stats_kernel gives lane c
+// channel c, and with this copy a gathered sample is ONE 8-byte load per lane on one code path (no float/double split).
+__global__ void pack_colors_kernel(const double *__restrict__ col, size_t S, double4 *__restrict__ col4, double *__restrict__ rec19) {
     const size_t g = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
     if (g >= S) return;
-    col4[g] = make_double4(col[g], col[S + g], col[2 * S + g], 0.0);
+    const double r = col[g], gg = col[S + g], b = col[2 * S + g];
+    col4[g] = make_double4(r, gg, b, 0.0);
+    rec19[g * REC19 + CH_COL] = r;
+    rec19[g * REC19 + CH_COL + 1] = gg;
+    rec19[g * REC19 + CH_COL + 2] = b;
+}
+__global__ void pack_rec19_kernel(const float *__restrict__ planes, size_t S, double *__restrict__ rec19) {
+    const size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
+    if (i >= S * REC19) return;
+    const size_t g = i / REC19;
+    const int c = static_cast<int>(i - g * REC19);
+    if (c >= NCH) { rec19[i] = 0.0; return; }
+    if (c >= CH_COL && c < CH_COL + NC) return;  // colours: pack_colors_kernel, every pass
+    rec19[i] = static_cast<double>(planes[static_cast<size_t>(c) * S + g]);
 }
 
 // ---------------------------------------------------------------------------------------------------

@@ -148,10 +148,7 @@ __global__ void __launch_bounds__(KO_WARPS * 32) ordered_stats_kernel(const Gene
 
     // lane c < 19 owns channel c: its plane pointer, the running sums (ops.h:111-144 order) and extremes
     const int c = lane < NCH ? lane : 0;
-    const bool isc = c >= CH_COL && c < CH_COL + NC;
-    // gather-friendly copies: 16 lanes read one 64-byte record, the 3 colour lanes one 32-byte record
-    const float *pf = reinterpret_cast<const float *>(p.rec16) + (isc ? 0 : channel_slot(c));
-    const double *pd = reinterpret_cast<const double *>(p.col4) + (isc ? c - CH_COL : 0);
+    const double *pr = p.rec19 + c;  // all-double record: one 8-byte load per lane and sample
     double acc = 0.0, sq = 0.0;
     double lo = __longlong_as_double(0x7ff0000000000000ll), hi = __longlong_as_double(0xfff0000000000000ll);
     auto take = [&](double v) {
@@ -160,7 +157,7 @@ __global__ void __launch_bounds__(KO_WARPS * 32) ordered_stats_kernel(const Gene
         lo = v < lo ? v : lo;
         hi = hi < v ? v : hi;
     };
-    auto fetch = [&](uint32_t g) { return isc ? pd[static_cast<size_t>(g) * 4] : static_cast<double>(__ldg(pf + static_cast<size_t>(g) * 16)); };
+    auto fetch = [&](uint32_t g) { return __ldg(pr + static_cast<size_t>(g) * REC19); };
 
     // own samples first, unconditionally and in order (rpf.cpp:558)
     int N = P;
