@@ -34,7 +34,7 @@ struct rpf_ctx {
     uint8_t *d_big = nullptr;
     size_t big_bytes = 0;
     bool force_large = false;
-    int blend_wide_min = 17;  // spp from which blend_wide_kernel replaces blend_kernel (RPF_BLEND_WIDE_MIN overrides)
+    int blend_wide_min = 16;  // spp from which blend_wide_kernel replaces blend_kernel (RPF_BLEND_WIDE_MIN overrides)
     // general path (rpf_general.cuh): per-chunk scratch in HBM
     uint32_t *d_mask = nullptr;
     double *d_rec = nullptr;
