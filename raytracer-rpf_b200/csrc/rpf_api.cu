@@ -597,7 +597,8 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
             m.col_rows = m.ty + box - 1;
             const size_t row_bytes = (static_cast<size_t>(ctx->cfg.spp) * NF + 2) * sizeof(double);
             m.rb_rows = m.col_rows;
-            while (m.rb_rows > 1 && m.rb_rows * row_bytes > 100 * 1024) m.rb_rows = (m.rb_rows + 1) / 2;
+            const size_t memb_kb = getenv("RPF_MEMB_SMEM_KB") ? static_cast<size_t>(atoi(getenv("RPF_MEMB_SMEM_KB"))) : 40;  // 40 KB per CTA: five CTAs per SM (82 vs 87 ms at box 55)
+            while (m.rb_rows > 1 && m.rb_rows * row_bytes > memb_kb * 1024) m.rb_rows = (m.rb_rows + 1) / 2;
             const unsigned tiles = static_cast<unsigned>(m.tiles_x) * static_cast<unsigned>((p.nrows + m.ty - 1) / m.ty);
             prof_begin(ctx, RPF_K_MEMBERSHIP);
             membership_kernel<<<tiles, m.tx * m.ty, m.rb_rows * row_bytes, ctx->stream>>>(m);

@@ -244,3 +244,28 @@ def test_host_cpp_through_reference_samplingfilm():
     o = ob.oracle_filter(planes, W, H, P, boxes, seed=seed)
     assert np.abs(col - o["colors"]).max() <= TOL_TIGHT
     assert nans.value == o["nan_count"] and mean.value > P
+
+
+def test_row_chunks_and_staging_blocks_do_not_change_the_result(monkeypatch):
+    """The general path works through the frame in chunks of rows sized by a scratch budget (RPF_SCRATCH_MB), and the
+    membership kernel stages a column of neighbour pixels in blocks of rows sized by RPF_MEMB_SMEM_KB. Tiny budgets
+    force many chunks and blocks; the colours must be bit-identical to the default configuration."""
+    import rpf_b200
+    W, H, P = 40, 33, 8
+    planes = rpf_b200.synth_planes(W, H, P, seed=17, kind=0)
+
+    def run():
+        f = rpf_b200.RPFFilter(W, H, P)
+        f.upload(planes)
+        f.apply([17, 9], 0.5)
+        out = f.download_colors_f64()
+        launches = f.stats()["kernel_launches"]
+        f.close()
+        return out, launches
+
+    ref, n_ref = run()
+    monkeypatch.setenv("RPF_SCRATCH_MB", "1")     # 1 MiB of mask + records: a few rows per chunk
+    monkeypatch.setenv("RPF_MEMB_SMEM_KB", "4")   # a handful of neighbour rows per staging block
+    got, n_got = run()
+    assert n_got > n_ref                          # really chunked
+    assert np.array_equal(ref, got)
