@@ -303,11 +303,26 @@ __device__ __forceinline__ void joint_phase(const GeneralParams &p, KBSmall &ks,
         const uint32_t *bb[G];
 #pragma unroll
         for (int j = 0; j < G; ++j) { int aa, b; task_channels(t0 + sub + j, aa, b); bb[j] = bins + b * nq; }
+        // the packed bins of the next round are requested before this round's atomics go out: when the bins live in the
+        // L2-resident scratch (large neighbourhoods) their latency is what the loop would otherwise wait for
+        uint32_t wa_n = 0u, wb_n[G];
+#pragma unroll
+        for (int j = 0; j < G; ++j) wb_n[j] = 0u;
+        if (tt < nfull) {
+            wa_n = ba[tt];
+#pragma unroll
+            for (int j = 0; j < G; ++j) wb_n[j] = bb[j][tt];
+        }
         for (int q = tt; q < nfull; q += tn) {
-            const uint32_t wa = ba[q];
+            const uint32_t wa = wa_n;
             uint32_t wb[G];
 #pragma unroll
-            for (int j = 0; j < G; ++j) wb[j] = bb[j][q];
+            for (int j = 0; j < G; ++j) wb[j] = wb_n[j];
+            if (q + tn < nfull) {
+                wa_n = ba[q + tn];
+#pragma unroll
+                for (int j = 0; j < G; ++j) wb_n[j] = bb[j][q + tn];
+            }
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 const unsigned ca = ((wa >> (8 * k)) & 255u) * nb;
