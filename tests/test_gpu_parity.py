@@ -269,3 +269,34 @@ def test_row_chunks_and_staging_blocks_do_not_change_the_result(monkeypatch):
     got, n_got = run()
     assert n_got > n_ref                          # really chunked
     assert np.array_equal(ref, got)
+
+
+def test_full_size_frame_spot_checked_against_oracle():
+    """BASELINE.json configs[1] at full size (1280x720, 8 spp, boxes 55/35/17/7). The oracle cannot filter the whole
+    frame in test time, but the filter is local: a pixel after the four passes depends on samples within 27+17+8+3 = 55
+    pixels. So the oracle filters a 134x134 crop generated on its own (the synthetic generator is counter based) and its
+    central 24x24 pixels must equal the GPU's full-frame result. Also: two GPU runs are bit-identical."""
+    import rpf_b200
+    W, H, P, boxes, seed = 1280, 720, 8, [55, 35, 17, 7], 0.5
+    halo = sum((b - 1) // 2 for b in boxes)
+    win, x0, y0 = 24, 611, 333
+    planes = rpf_b200.synth_planes(W, H, P, seed=1234, kind=0)
+    f = rpf_b200.RPFFilter(W, H, P)
+    f.upload(planes)
+    f.apply(boxes, seed)
+    got = f.download_colors_f64()
+    f.upload(planes)
+    f.apply(boxes, seed)
+    again = f.download_colors_f64()
+    st = f.stats()
+    f.close()
+    assert np.array_equal(got, again), "two runs differ: the atomics-ordered sums are supposed to be order independent"
+    assert st["nan_channels"] == 0
+    cw = win + 2 * halo
+    crop = rpf_b200.synth_planes(cw, cw, P, seed=1234, kind=0, x_off=x0 - halo, y_off=y0 - halo)
+    full = planes.reshape(19, H, W, P)[:, y0 - halo:y0 + win + halo, x0 - halo:x0 + win + halo]
+    assert np.array_equal(crop.reshape(19, cw, cw, P), full)  # the crop is the same data
+    o = ob.oracle_filter(crop, cw, cw, P, boxes, seed=seed)["colors"].reshape(3, cw, cw, P)[:, halo:halo + win, halo:halo + win]
+    g = got.reshape(3, H, W, P)[:, y0:y0 + win, x0:x0 + win]
+    assert np.abs(g - o).max() <= TOL_TIGHT * max(1.0, np.abs(o).max())
+    assert np.abs(g - planes[2:5].reshape(3, H, W, P)[:, y0:y0 + win, x0:x0 + win]).max() > 1e-3
