@@ -41,6 +41,8 @@ def parse():
     ap.add_argument("--seed", type=float, default=0.002, help="sigma_fc_seed, reference literal rpf.cpp:533")
     ap.add_argument("--config", default=None, choices=["sample720", "fullhd", "4k16", "stress64"],
                     help="BASELINE.json configs[1..4]: 1280x720x8 (default), 1920x1080x8, 3840x2160x16, 1920x1080x64")
+    ap.add_argument("--subsample", type=float, default=1.0,
+                    help="optional neighbour subsampling (keep probability; 1 = off = the reference's semantics and the default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -152,6 +154,8 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     workload = f"synthetic all-noisy feature buffer {args.width}x{args.height} {args.spp} spp, boxes {boxes}, sigma seed {args.seed}"
+    if args.subsample < 1.0:
+        workload += f", neighbour subsampling keep {args.subsample} (NOT the reference's semantics)"
 
     if args.impl == "reference":
         if rank != 0:
@@ -190,6 +194,8 @@ def main():
     rpf_b200.synth_planes(W, lh, P, seed=1234, kind=0, x_off=0, y_off=band.buf0, out=planes)
     out_host = torch.empty((3, S_loc), dtype=torch.float32, pin_memory=True)
     ctx = rpf_b200.RPFFilter(W, lh, P, device=local_rank)
+    if args.subsample < 1.0:
+        ctx.set_subsampling(args.subsample, 1234, band.buf0)
     ctx.upload(planes)
     ctx.synchronize()
 

@@ -92,6 +92,12 @@ int rpf_filter(rpf_ctx *ctx, const int *box_sizes, int n_iter, double sigma_fc_s
  * [y0,y1) of the next buffer are whatever the caller puts there (halo exchange) or stale. */
 int rpf_filter_rows(rpf_ctx *ctx, int box_size, double sigma_fc_seed, int y0, int y1);
 int rpf_swap_colors(rpf_ctx *ctx);
+/* Optional, not in the reference (which takes every sample of the box, rpf.cpp:556-586, README.md:27): random neighbour
+ * subsampling as in Sen & Darabi. A neighbour sample that passed the 3-sigma test stays with probability
+ * keep_probability, decided by the counter-based RNG of include/rpf_subsample.h from (rng_seed, box size, centre pixel,
+ * neighbour pixel, sample number) in GLOBAL coordinates -- the CPU oracle and every row band draw the same stream.
+ * global_row0 = global row of this context's row 0. keep_probability >= 1 switches it off (the default). */
+int rpf_set_subsampling(rpf_ctx *ctx, double keep_probability, unsigned long long rng_seed, int global_row0);
 /* Device pointers to the colour planes, [3][width*height*spp] doubles: which = 0 current, 1 next.
  * For halo exchange by the host (NCCL send/recv or peer copies between row bands). */
 int rpf_color_device_ptr(rpf_ctx *ctx, int which, double **out);

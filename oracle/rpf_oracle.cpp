@@ -6,6 +6,7 @@
 // without FMA contraction (-ffp-contract=off) so sums and products round like the
 // reference's x86-64 -O3 build.
 #include "rpf_oracle.h"
+#include "../include/rpf_subsample.h"
 
 #include <atomic>
 #include <cmath>
@@ -168,7 +169,13 @@ struct PixelScratch {
 };
 
 // One pixel of rpf.cpp:556-723. Returns number of NaN colour channels written.
-int filter_pixel(const Frame &f, int px, int py, int box, double seed, int flags, double *col_out,
+struct Subsample {
+    uint32_t keep_q24 = RPF_SUBSAMPLE_ALL;
+    uint64_t seed = 0;
+    int row0 = 0;
+};
+
+int filter_pixel(const Frame &f, int px, int py, int box, double seed, int flags, const Subsample &sub, double *col_out,
                  PixelScratch &s, int *n_out, double *alpha_out, double *beta_out, double *wrc_out) {
     const int P = f.P, W = f.W, H = f.H;
     const size_t base = (static_cast<size_t>(py) * W + px) * P;
@@ -189,6 +196,7 @@ int filter_pixel(const Frame &f, int px, int py, int box, double seed, int flags
     s.nbh.clear();
     for (int i = 0; i < P; ++i) s.nbh.push_back(base + i);
     const int bd = (box - 1) / 2;  // rpf.cpp:561
+    const uint64_t ckey = rpf_subsample_centre_key(sub.seed, box, px, py + sub.row0);
     for (int xn = px - bd; xn <= px + bd; ++xn) {
         for (int yn = py - bd; yn <= py + bd; ++yn) {
             if (xn == px && yn == py) continue;
@@ -200,6 +208,8 @@ int filter_pixel(const Frame &f, int px, int py, int box, double seed, int flags
                     const double d = std::fabs(f.value(CH_FEAT + k, nb + i) - mu[k]);
                     if (d >= sd3[k]) { ok = false; break; }
                 }
+                // optional neighbour subsampling (not in the reference): shared counter-based RNG, global coordinates
+                if (ok && sub.keep_q24 < RPF_SUBSAMPLE_ALL) ok = rpf_subsample_keep(ckey, sub.keep_q24, xn, yn + sub.row0, i);
                 if (ok) s.nbh.push_back(nb + i);
             }
         }
@@ -285,6 +295,12 @@ extern "C" int rpf_oracle_filter(rpf_oracle_args *a) {
     int nt = a->n_threads > 0 ? a->n_threads : static_cast<int>(std::thread::hardware_concurrency());
     if (nt < 1) nt = 1;
     std::atomic<long long> nan_total{0};
+    Subsample sub;
+    if (a->subsample_keep_q24 > 0 && a->subsample_keep_q24 < RPF_SUBSAMPLE_ALL) {
+        sub.keep_q24 = a->subsample_keep_q24;
+        sub.seed = a->subsample_seed;
+        sub.row0 = a->global_row0;
+    }
     for (int it = 0; it < a->n_iter; ++it) {
         const int box = a->box_sizes[it];
         const bool last = it == a->n_iter - 1;
@@ -303,7 +319,7 @@ extern "C" int rpf_oracle_filter(rpf_oracle_args *a) {
                 for (int x = bx; x < bx + T && x < x1; ++x)
                     for (int y = by; y < by + T && y < y1; ++y) {
                         const size_t p = static_cast<size_t>(y) * W + x;
-                        nans += filter_pixel(f, x, y, box, a->sigma_fc_seed, a->flags, nxt.data(), s,
+                        nans += filter_pixel(f, x, y, box, a->sigma_fc_seed, a->flags, sub, nxt.data(), s,
                                              last && a->nbh_size ? a->nbh_size + p : nullptr,
                                              last && a->alpha ? a->alpha + p * 3 : nullptr,
                                              last && a->beta ? a->beta + p * 12 : nullptr,

@@ -49,6 +49,11 @@ typedef struct rpf_oracle_args {
     double *beta;            /* [W*H][12] */
     double *wrc;             /* [W*H]     */
     long long nan_count;     /* out: number of NaN colour channels written (P4: counted, never fatal) */
+    /* Neighbour subsampling (not in the reference; include/rpf_subsample.h is the RNG both sides call):
+     * keep_q24 = floor(keep probability * 2^24), 0 or >= 2^24 = keep every sample that passes the 3-sigma test. */
+    unsigned int subsample_keep_q24;
+    unsigned long long subsample_seed;
+    int global_row0;         /* global row of local row 0 (row bands) */
 } rpf_oracle_args;
 
 /* returns 0 on success, <0 on bad arguments */

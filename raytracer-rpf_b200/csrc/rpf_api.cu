@@ -34,6 +34,7 @@ struct rpf_ctx {
     uint8_t *d_big = nullptr;
     size_t big_bytes = 0;
     bool force_large = false;
+    SubsampleParams sub{0ull, RPF_SUBSAMPLE_ALL, 0};
     int blend_wide_min = 16;  // spp from which blend_wide_kernel replaces blend_kernel (RPF_BLEND_WIDE_MIN overrides)
     // general path (rpf_general.cuh): per-chunk scratch in HBM
     uint32_t *d_mask = nullptr;
@@ -409,7 +410,6 @@ static bool plan_general(long long ncap, int spp, int static_smem, GeneralPlan &
         L.off_bins = L.bins_in_smem ? L.off_region + region : 0;
         L.region_words = region / 4;
         L.kb_smem = L.off_region + avail;
-        L.G = 0;
         return true;
     }
     return false;
@@ -592,6 +592,7 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
             m.row0 = p.row0;
             m.nrows = p.nrows;
             m.mw = p.pl.mw;
+            m.sub = ctx->sub;
             membership_tile(box, m.tx, m.ty);
             m.tiles_x = (W + m.tx - 1) / m.tx;
             m.col_rows = m.ty + box - 1;
@@ -665,6 +666,7 @@ static int launch_rows(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
     p.dbg_beta = ctx->d_dbg_beta;
     p.dbg_wrc = ctx->d_dbg_wrc;
     p.counters = ctx->d_counters;
+    p.sub = ctx->sub;
     const unsigned grid = static_cast<unsigned>((y1 - y0) * ctx->cfg.width);
     prof_begin(ctx, RPF_K_FUSED);
     rpf_pixel_kernel<<<grid, THREADS, p.sm.total, ctx->stream>>>(p);
@@ -696,6 +698,14 @@ extern "C" int rpf_filter_rows(rpf_ctx *ctx, int box_size, double sigma_fc_seed,
     if (rc != RPF_OK) return rc;
     CU(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
     ctx->timing_pending = true;
+    return RPF_OK;
+}
+
+extern "C" int rpf_set_subsampling(rpf_ctx *ctx, double keep_probability, unsigned long long rng_seed, int global_row0) {
+    if (!ctx || !(keep_probability > 0.0)) return fail(ctx, RPF_ERR_INVALID, "rpf_set_subsampling: keep probability must be in (0, 1]");
+    ctx->sub.keep_q24 = keep_probability >= 1.0 ? RPF_SUBSAMPLE_ALL : static_cast<unsigned>(keep_probability * (1 << 24));
+    ctx->sub.seed = rng_seed;
+    ctx->sub.row_g0 = global_row0;
     return RPF_OK;
 }
 

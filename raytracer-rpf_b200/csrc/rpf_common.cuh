@@ -4,6 +4,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "../../include/rpf_subsample.h"
+
 namespace rpf {
 
 constexpr int NCH = 19;
@@ -17,6 +19,13 @@ constexpr int REC19 = 20;               // doubles per sample of the all-double 
 constexpr int NWZ = 17;                 // channels entering the weights: pos(2) + colour(3) + features(12)
 
 constexpr int FLAG_P1 = 1, FLAG_P2 = 2, FLAG_P3 = 4;
+
+// Optional neighbour subsampling (include/rpf_subsample.h): keep_q24 >= RPF_SUBSAMPLE_ALL switches it off.
+struct SubsampleParams {
+    unsigned long long seed;
+    unsigned keep_q24;
+    int row_g0;   // global row of this context's row 0 (row bands)
+};
 
 // Device view of the frame: 19 float planes, each S = W*H*P samples, index (y*W+x)*P+s.
 struct FrameView {
@@ -48,6 +57,7 @@ struct FilterParams {
     int *dbg_n;             // optional per-pixel outputs (may be null)
     double *dbg_alpha, *dbg_beta, *dbg_wrc;
     unsigned long long *counters;  // [0] sum N, [1] NaN channels, [2] min N, [3] max N
+    SubsampleParams sub;
 };
 
 // Non-colour channels are staged as floats in slots 0..15: slot -> channel.

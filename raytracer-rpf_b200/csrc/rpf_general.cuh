@@ -1,11 +1,12 @@
-// rpf_general.cuh -- the general (any neighbourhood size) RPF path: three kernels per ApplyRPFFilter pass.
+// rpf_general.cuh -- the general (any neighbourhood size) RPF path: four kernels per ApplyRPFFilter pass.
 //
 //   KA  membership_kernel + ordered_stats_kernel (rpf_membership.cuh): 3-sigma membership over the box -> per-pixel
 //       acceptance bit mask, then N and the neighbourhood mean / sigma / min / max of all 19 channels  [rpf.cpp:556-601]
 //   KB  dependency_kernel  normalise + bin every accepted sample, 96 joint histograms in shared memory
 //                          (shared atomics), mutual information, alpha / beta / W_r_c        [rpf.cpp:603-618,356-488; mi.cpp]
+//       (beyond 65,535 accepted samples: dependency_large_kernel, rpf_large.cuh)
 //   KC  blend_kernel       cross-bilateral weights of the P own samples against the N accepted samples, blend
-//                                                                                              [rpf.cpp:627-717]
+//       (16 spp and more: blend_wide_kernel, rpf_blend_wide.cuh)                               [rpf.cpp:627-717]
 //
 // The fused one-CTA-per-pixel kernel (rpf_pixel_kernel.cuh) keeps the whole neighbourhood in shared memory and
 // lane-private histograms, which stops at N = 1279. Here nothing per-sample is resident: KA leaves one bit per
@@ -28,7 +29,6 @@ struct GeneralPlan {
     int ncap;        // box*box*spp candidates
     int mw;          // mask words per pixel (multiple of 4)
     int nq;          // ceil(ncap/4): words per channel of packed u8 bins
-    int G;           // unused (the kernel picks 4, 2 or 1 tables at a time per pixel from the actual table size)
     int nt;          // threads per CTA of the dependency kernel: 256 (two CTAs per SM) or 512
     int hw;          // words per joint histogram (two u16 cells per word), multiple of 4
     int nbs;         // words per marginal histogram

@@ -33,6 +33,7 @@ struct MembershipParams {
     int tx, ty, tiles_x;   // tile shape and tiles per row
     int col_rows;          // ty + box - 1: neighbour-pixel rows per column of the tile's union
     int rb_rows;           // rows staged in shared memory at a time (col_rows unless spp is very large)
+    SubsampleParams sub;
 };
 
 __global__ void __launch_bounds__(KM_MAX_THREADS) membership_kernel(const MembershipParams p) {
@@ -59,6 +60,8 @@ __global__ void __launch_bounds__(KM_MAX_THREADS) membership_kernel(const Member
 #pragma unroll
         for (int k = 0; k < NF; ++k) { mu[k] = 0.0; sd3[k] = 0.0; }
     }
+    const bool subsampled = p.sub.keep_q24 < RPF_SUBSAMPLE_ALL;
+    const uint64_t ckey = subsampled ? rpf_subsample_centre_key(p.sub.seed, B, px, py + p.sub.row_g0) : 0ull;
     uint32_t *mrow = p.mask + (static_cast<size_t>(py - p.row0) * W + px) * p.mw;
     unsigned long long buf = 0ull;
     int nbits = 0, wi = 0;
@@ -111,6 +114,7 @@ __global__ void __launch_bounds__(KM_MAX_THREADS) membership_kernel(const Member
                                     for (int k = 4; k < NF; ++k)
                                         if (fabs(__dsub_rn(cp[k], mu[k])) >= sd3[k]) acc = false;
                                 }
+                                if (subsampled && acc) acc = rpf_subsample_keep(ckey, p.sub.keep_q24, xn, yn + p.sub.row_g0, s0 + s);
                             }
                             bits |= static_cast<uint32_t>(acc) << s;
                         }

@@ -115,6 +115,9 @@ __global__ void __launch_bounds__(THREADS, 4) rpf_pixel_kernel(const FilterParam
                     const double d = fabs(__dsub_rn(static_cast<double>(fv[k]), ps.mu[k]));
                     if (d >= ps.sd3[k]) acc = false;
                 }
+                if (acc && p.sub.keep_q24 < RPF_SUBSAMPLE_ALL)
+                    acc = rpf_subsample_keep(rpf_subsample_centre_key(p.sub.seed, B, px, py + p.sub.row_g0), p.sub.keep_q24, xn,
+                                             yn + p.sub.row_g0, s);
             }
         }
         const unsigned m = __ballot_sync(0xffffffffu, acc);

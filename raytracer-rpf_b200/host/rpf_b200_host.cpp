@@ -59,6 +59,8 @@ static bool run(SamplingFilm &film, const RPFB200Options &opt, const rpf_film_de
     if (rpf_create(&raw, &cfg) != RPF_OK) return failed(error, "rpf_create", nullptr);
     std::unique_ptr<rpf_ctx, CtxDeleter> ctx(raw);
 
+    if (opt.keepProbability < 1.0 && rpf_set_subsampling(ctx.get(), opt.keepProbability, opt.rngSeed, 0) != RPF_OK)
+        return failed(error, "rpf_set_subsampling", ctx.get());
     const float *ptrs[RPF_NUM_CHANNELS];
     for (int c = 0; c < RPF_NUM_CHANNELS; ++c) ptrs[c] = planes.data() + c * S;
     if (rpf_upload(ctx.get(), ptrs) != RPF_OK) return failed(error, "rpf_upload", ctx.get());

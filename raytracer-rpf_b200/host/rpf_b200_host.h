@@ -21,6 +21,8 @@ struct RPFB200Options {
     double sigmaSeed = 0.002;      // rpf.cpp:533
     int device = 0;                // CUDA device ordinal
     int flags = 0;                 // RPF_FLAG_* of include/rpf_b200.h; 0 = REF_DEFINED
+    double keepProbability = 1.0;  // < 1: random neighbour subsampling (rpf_set_subsampling; not the reference's semantics)
+    unsigned long long rngSeed = 0;
 };
 
 struct RPFB200Report {

@@ -25,7 +25,7 @@ ABI_SYMBOLS = [
     "rpf_download_colors", "rpf_download_colors_f64", "rpf_download_debug", "rpf_reconstruct_box",
     "rpf_get_stats", "rpf_reset_stats", "rpf_set_profiling", "rpf_get_kernel_times", "rpf_max_neighbourhood",
     "rpf_synth_planes", "rpf_reconstruct_film", "rpf_film_filter_table",
-    "rpf_buffer_write", "rpf_buffer_info_read", "rpf_buffer_read",
+    "rpf_buffer_write", "rpf_buffer_info_read", "rpf_buffer_read", "rpf_set_subsampling",
 ]
 
 
@@ -239,6 +239,10 @@ class RPFFilter:
 
     def filter_rows(self, box, y0, y1, sigma_fc_seed=0.002):
         self._check(lib().rpf_filter_rows(self._h, box, sigma_fc_seed, y0, y1))
+
+    def set_subsampling(self, keep_probability, rng_seed=0, global_row0=0):
+        """Random neighbour subsampling (include/rpf_subsample.h); keep_probability >= 1 switches it off."""
+        self._check(lib().rpf_set_subsampling(self._h, C.c_double(keep_probability), C.c_ulonglong(rng_seed), global_row0))
 
     def swap_colors(self):
         self._check(lib().rpf_swap_colors(self._h))

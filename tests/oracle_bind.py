@@ -20,6 +20,7 @@ class OracleArgs(C.Structure):
         ("y0", C.c_int), ("y1", C.c_int), ("x0", C.c_int), ("x1", C.c_int),
         ("nbh_size", C.c_void_p), ("alpha", C.c_void_p), ("beta", C.c_void_p), ("wrc", C.c_void_p),
         ("nan_count", C.c_longlong),
+        ("subsample_keep_q24", C.c_uint), ("subsample_seed", C.c_ulonglong), ("global_row0", C.c_int),
     ]
 
 
@@ -75,7 +76,8 @@ def _p(a):
 
 
 def oracle_filter(planes, W, H, P, boxes, seed=0.002, flags=DEFINED, colors=None, threads=0,
-                  rows=None, cols=None, debug=False):
+                  rows=None, cols=None, debug=False, subsample=None):
+    # subsample = (keep probability, rng seed, global row of local row 0) or None
     """planes: float32 [19, W*H*P]. Returns dict(colors=[3,S] float64, N, alpha, beta, wrc, nan_count)."""
     planes = np.ascontiguousarray(planes, dtype=np.float32)
     S = W * H * P
@@ -88,6 +90,10 @@ def oracle_filter(planes, W, H, P, boxes, seed=0.002, flags=DEFINED, colors=None
     a.n_iter, a.sigma_fc_seed, a.flags, a.n_threads = len(bx), seed, flags, threads
     a.y0, a.y1 = rows if rows else (0, 0)
     a.x0, a.x1 = cols if cols else (0, 0)
+    if subsample is not None:
+        a.subsample_keep_q24 = int(subsample[0] * (1 << 24))
+        a.subsample_seed = subsample[1]
+        a.global_row0 = subsample[2] if len(subsample) > 2 else 0
     out = {}
     if debug:
         out["N"] = np.zeros(W * H, np.int32)

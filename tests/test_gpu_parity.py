@@ -300,3 +300,54 @@ def test_full_size_frame_spot_checked_against_oracle():
     g = got.reshape(3, H, W, P)[:, y0:y0 + win, x0:x0 + win]
     assert np.abs(g - o).max() <= TOL_TIGHT * max(1.0, np.abs(o).max())
     assert np.abs(g - planes[2:5].reshape(3, H, W, P)[:, y0:y0 + win, x0:x0 + win]).max() > 1e-3
+
+
+# Neighbour subsampling (rpf_set_subsampling; not in the reference): the oracle and the kernels call the same
+# counter-based RNG (include/rpf_subsample.h), so they must agree on N exactly and on everything else as tightly as before.
+@pytest.mark.parametrize("W,H,P,boxes,keep,general", [
+    (40, 28, 8, [7], 0.5, False),        # fused kernel
+    (40, 28, 8, [7], 0.5, True),         # membership kernel
+    (36, 30, 8, [17, 7], 0.25, False),   # general pass then fused pass: a different subset per box size
+    (12, 10, 64, [35], 0.1, False),      # more than 65,535 candidates, 64 samples per pixel (two staging chunks of 32)
+    (24, 20, 8, [9], 1.0, False),        # keep = 1: off
+])
+def test_subsampled_neighbourhoods_match_oracle(W, H, P, boxes, keep, general):
+    import rpf_b200
+    planes = rpf_b200.synth_planes(W, H, P, seed=51, kind=0)
+    o = ob.oracle_filter(planes, W, H, P, boxes, seed=0.5, debug=True, subsample=(keep, 99))
+    f = rpf_b200.RPFFilter(W, H, P, debug=True, force_general=general)
+    f.set_subsampling(keep, 99)
+    f.upload(planes)
+    f.apply(boxes, 0.5)
+    g = dict(colors=f.download_colors_f64(), **f.download_debug())
+    g["stats"] = f.stats()
+    f.close()
+    _compare(g, o, W, H, P)
+    full = ob.oracle_filter(planes, W, H, P, boxes, seed=0.5, debug=True)
+    if keep < 1.0:
+        assert g["N"].sum() < 0.8 * full["N"].sum()
+    else:
+        assert np.array_equal(g["N"], full["N"])
+
+
+def test_subsampling_is_the_same_in_a_row_band():
+    """A band with global_row0 set draws the stream of the full frame (global coordinates)."""
+    import rpf_b200
+    W, H, P, y0, y1, halo = 32, 30, 8, 10, 20, 8
+    planes = rpf_b200.synth_planes(W, H, P, seed=5, kind=0)
+    f = rpf_b200.RPFFilter(W, H, P)
+    f.set_subsampling(0.4, 7)
+    f.upload(planes)
+    f.apply([17], 0.5)
+    full = f.download_colors_f64().reshape(3, H, W * P)[:, y0:y1]
+    f.close()
+    b0, b1 = y0 - halo, y1 + halo
+    band_planes = np.ascontiguousarray(planes.reshape(19, H, W * P)[:, b0:b1]).reshape(19, -1)
+    f = rpf_b200.RPFFilter(W, b1 - b0, P)
+    f.set_subsampling(0.4, 7, global_row0=b0)
+    f.upload(band_planes)
+    f.filter_rows(17, y0 - b0, y1 - b0, 0.5)
+    f.swap_colors()
+    band = f.download_colors_f64().reshape(3, b1 - b0, W * P)[:, y0 - b0:y1 - b0]
+    f.close()
+    assert np.array_equal(full, band)

@@ -98,3 +98,26 @@ def test_oracle_against_live_reference_code():
     assert ob.ref().ref_within_3sigma(ob._p(f), ob._p(m), ob._p(np.full(12, 10.0))) == 1
     assert ob.ref().ref_within_3sigma(ob._p(m), ob._p(m), ob._p(np.zeros(12))) == 0
     assert ob.ref().ref_within_3sigma(ob._p(f), ob._p(m), ob._p(np.full(12, np.nan))) == 1
+
+
+def test_oracle_subsampling_off_is_the_reference_and_on_thins_the_neighbourhood():
+    """Neighbour subsampling is an extension (include/rpf_subsample.h). Off (keep >= 1) it must leave the pinned
+    behaviour untouched; on, own samples always stay (rpf.cpp:558) and about `keep` of the others."""
+    import sys, os
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "raytracer-rpf_b200"))
+    import rpf_b200
+    W, H, P = 20, 16, 8
+    planes = rpf_b200.synth_planes(W, H, P, seed=3, kind=0)
+    a = ob.oracle_filter(planes, W, H, P, [7], seed=0.5, debug=True)
+    b = ob.oracle_filter(planes, W, H, P, [7], seed=0.5, debug=True, subsample=(1.0, 5))
+    c = ob.oracle_filter(planes, W, H, P, [7], seed=0.5, debug=True, subsample=(0.5, 5))
+    d = ob.oracle_filter(planes, W, H, P, [7], seed=0.5, debug=True, subsample=(0.5, 6))
+    assert np.array_equal(a["colors"], b["colors"]) and np.array_equal(a["N"], b["N"])
+    others_all, others_half = a["N"].sum() - P * W * H, c["N"].sum() - P * W * H
+    assert (c["N"] >= P).all() and 0.45 < others_half / others_all < 0.55
+    assert not np.array_equal(c["N"], d["N"])  # another seed, another subset
+    # a band of the frame with global_row0 draws the full frame's stream
+    y0, y1, halo = 6, 10, 3
+    band = np.ascontiguousarray(planes.reshape(19, H, W * P)[:, y0 - halo:y1 + halo]).reshape(19, -1)
+    e = ob.oracle_filter(band, W, y1 - y0 + 2 * halo, P, [7], seed=0.5, rows=(halo, halo + y1 - y0), subsample=(0.5, 5, y0 - halo))
+    assert np.array_equal(e["colors"].reshape(3, -1, W * P)[:, halo:halo + y1 - y0], c["colors"].reshape(3, H, W * P)[:, y0:y1])
