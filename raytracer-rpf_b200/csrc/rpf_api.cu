@@ -375,8 +375,9 @@ extern "C" int rpf_upload_colors_f64(rpf_ctx *ctx, const double *rgb) {
 // ---- general path (rpf_general.cuh) ----------------------------------------------------------------------
 static const int kGeneralMaxCandidates = 65535;  // u16 candidate numbers and histogram cells, u8 bins (nb <= 255)
 
-// Shared-memory plan of the dependency kernel for ncap = box*box*spp candidates. Two CTAs of 256 threads per SM when
-// at least two full-size histograms fit in half an SM's shared memory, else one CTA of 512 threads. Whatever is left
+// Shared-memory plan of the dependency kernel for ncap = box*box*spp candidates. Two CTAs of 512 threads per SM when
+// one full-size histogram (the rare pixel that accepts every candidate) fits in half an SM's shared memory, else one CTA
+// of 1024 threads (box 55 at 8 spp: 355 vs 419 ms with two CTAs). Whatever is left
 // after the fixed tables goes to the histogram region (more slots = more warp teams); the bin bytes stay in shared
 // memory only if eight full-size histograms still fit beside them, otherwise they go to an L2-resident per-CTA scratch.
 static bool plan_general(long long ncap, int spp, int static_smem, GeneralPlan &L) {
@@ -403,7 +404,7 @@ static bool plan_general(long long ncap, int spp, int static_smem, GeneralPlan &
     const int limit[2] = {(228 * 1024) / 2 - static_smem - 1024, 227 * 1024 - static_smem - 1024};
     for (int v = 0; v < 2; ++v) {
         const int avail = (limit[v] - L.off_region) & ~15;
-        if (avail < atleast(v == 0 ? 2 : 1)) continue;
+        if (avail < atleast(1)) continue;
         L.nt = v == 0 ? 512 : 1024;
         L.bins_in_smem = bins_bytes + atleast(8) <= avail;
         const int region = L.bins_in_smem ? avail - bins_bytes : avail;
@@ -564,6 +565,7 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
     p.gq = ctx->d_gq;
     p.hq = p.pl.large ? ctx->d_hql : ctx->d_hq;
     p.large_min_n = 0;
+    p.pl.tune = getenv("RPF_KB_TUNE") ? atoi(getenv("RPF_KB_TUNE")) : 0;
     p.big_scratch = ctx->d_big;
     p.box = box;
     p.cd = make_cand_decode(box, ctx->cfg.spp);

@@ -37,6 +37,7 @@ struct GeneralPlan {
     int region_words;  // capacity of the histogram region in 32-bit words
     int kb_grid;
     int kc_smem;
+    int tune;        // experiment knob (RPF_KB_TUNE)
     int idx_global;  // 1: box*box*spp > 65,535: candidate numbers are 32-bit and live in big_scratch; pixels with N > 65,535 are left
                      //    to dependency_large_kernel
     int large;       // 1: dependency_large_kernel (rpf_large.cuh): u32 candidates, u16 bins, u32 cells, slabbed tables
@@ -533,9 +534,18 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
             int Gp, sets = 1, teams = 1;
             if (slots >= 8) {
                 Gp = 4;
-                sets = 2;
-                while (teams * 2 <= NT / 32 && teams * 2 * 8 <= slots) teams *= 2;
-                if (teams > 8 && teams < NT / 32) teams = 8;  // multi-warp teams use named barriers 1..15
+                // One set of tables per team; as many teams as fit (more independent teams hide more latency: 8 teams
+                // of 2 warps beat 4 of 4 by 10-20 %), then as many tables per team as still fit. Multi-warp teams
+                // synchronise on named barriers 1..15, so at most 8 of them.
+                sets = 1;
+                auto teams_for = [&](int g) {
+                    int t = 1;
+                    while (t * 2 <= NT / 32 && t * 2 * g <= slots) t *= 2;
+                    if (t > 8 && t < NT / 32) t = 8;
+                    return t;
+                };
+                const int t2 = teams_for(2), t4 = teams_for(4);
+                if (t4 == t2) { Gp = 4; teams = t4; } else { Gp = 2; teams = t2; }
             } else Gp = slots >= 4 ? 4 : (slots >= 2 ? 2 : 1);
             {
                 uint4 *r4 = reinterpret_cast<uint4 *>(region);
