@@ -565,7 +565,6 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
     p.gq = ctx->d_gq;
     p.hq = p.pl.large ? ctx->d_hql : ctx->d_hq;
     p.large_min_n = 0;
-    p.pl.tune = getenv("RPF_KB_TUNE") ? atoi(getenv("RPF_KB_TUNE")) : 0;
     p.big_scratch = ctx->d_big;
     p.box = box;
     p.cd = make_cand_decode(box, ctx->cfg.spp);

@@ -37,7 +37,6 @@ struct GeneralPlan {
     int region_words;  // capacity of the histogram region in 32-bit words
     int kb_grid;
     int kc_smem;
-    int tune;        // experiment knob (RPF_KB_TUNE)
     int idx_global;  // 1: box*box*spp > 65,535: candidate numbers are 32-bit and live in big_scratch; pixels with N > 65,535 are left
                      //    to dependency_large_kernel
     int large;       // 1: dependency_large_kernel (rpf_large.cuh): u32 candidates, u16 bins, u32 cells, slabbed tables
@@ -546,7 +545,7 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
                 };
                 const int t2 = teams_for(2), t4 = teams_for(4);
                 if (t4 == t2) { Gp = 4; teams = t4; } else { Gp = 2; teams = t2; }
-            } else Gp = slots >= 4 ? 4 : (slots >= 2 ? 2 : 1);
+            } else Gp = slots >= 4 ? 4 : (slots >= 2 ? 2 : 1);  // few large tables: one team (splitting it does not pay, L2-bound)
             {
                 uint4 *r4 = reinterpret_cast<uint4 *>(region);
                 for (int k = tid; k < (teams * sets * Gp * hwn) >> 2; k += NT) r4[k] = make_uint4(0u, 0u, 0u, 0u);
