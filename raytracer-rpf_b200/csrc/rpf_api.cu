@@ -297,14 +297,16 @@ extern "C" int rpf_create(rpf_ctx **out, const rpf_config *cfg) {
         CUC(cudaMalloc(&ctx->d_dbg_wrc, 1ull * ctx->npix * sizeof(double)));
         CUC(cudaMemset(ctx->d_dbg_n, 0, ctx->npix * sizeof(int)));
     }
-    CUC(cudaFuncSetAttribute(rpf_pixel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
+    CUC(cudaFuncSetAttribute(rpf_pixel_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
+    CUC(cudaFuncSetAttribute(rpf_pixel_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
     {
         cudaFuncAttributes fa;
         CUC(cudaFuncGetAttributes(&fa, dependency_kernel<1024>));
         ctx->kb_static_smem = static_cast<int>(fa.sharedSizeBytes);
         CUC(cudaFuncSetAttribute(dependency_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  227 * 1024 - ctx->kb_static_smem - 1024));
-        CUC(cudaFuncSetAttribute(membership_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CUC(cudaFuncSetAttribute(membership_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CUC(cudaFuncSetAttribute(membership_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CUC(cudaFuncSetAttribute(blend_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
         CUC(cudaFuncSetAttribute(dependency_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (228 * 1024) / 2 - ctx->kb_static_smem - 1024));
@@ -603,7 +605,8 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
             while (m.rb_rows > 1 && m.rb_rows * row_bytes > memb_kb * 1024) m.rb_rows = (m.rb_rows + 1) / 2;
             const unsigned tiles = static_cast<unsigned>(m.tiles_x) * static_cast<unsigned>((p.nrows + m.ty - 1) / m.ty);
             prof_begin(ctx, RPF_K_MEMBERSHIP);
-            membership_kernel<<<tiles, m.tx * m.ty, m.rb_rows * row_bytes, ctx->stream>>>(m);
+            if (m.sub.keep_q24 < RPF_SUBSAMPLE_ALL) membership_kernel<true><<<tiles, m.tx * m.ty, m.rb_rows * row_bytes, ctx->stream>>>(m);
+            else membership_kernel<false><<<tiles, m.tx * m.ty, m.rb_rows * row_bytes, ctx->stream>>>(m);
             prof_end(ctx);
         }
         prof_begin(ctx, RPF_K_ORDERED_STATS);
@@ -670,7 +673,8 @@ static int launch_rows(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
     p.sub = ctx->sub;
     const unsigned grid = static_cast<unsigned>((y1 - y0) * ctx->cfg.width);
     prof_begin(ctx, RPF_K_FUSED);
-    rpf_pixel_kernel<<<grid, THREADS, p.sm.total, ctx->stream>>>(p);
+    if (p.sub.keep_q24 < RPF_SUBSAMPLE_ALL) rpf_pixel_kernel<true><<<grid, THREADS, p.sm.total, ctx->stream>>>(p);
+    else rpf_pixel_kernel<false><<<grid, THREADS, p.sm.total, ctx->stream>>>(p);
     prof_end(ctx);
     ctx->launches++;
     CU(ctx, cudaGetLastError());

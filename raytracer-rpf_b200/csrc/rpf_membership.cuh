@@ -36,6 +36,7 @@ struct MembershipParams {
     SubsampleParams sub;
 };
 
+template <bool SUBSAMPLED>  // neighbour subsampling (include/rpf_subsample.h) compiled out of the default path
 __global__ void __launch_bounds__(KM_MAX_THREADS) membership_kernel(const MembershipParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     // [col_rows][P][12] features of one column of neighbour pixels; rows padded by two doubles so that the 2-4 rows a
@@ -60,8 +61,7 @@ __global__ void __launch_bounds__(KM_MAX_THREADS) membership_kernel(const Member
 #pragma unroll
         for (int k = 0; k < NF; ++k) { mu[k] = 0.0; sd3[k] = 0.0; }
     }
-    const bool subsampled = p.sub.keep_q24 < RPF_SUBSAMPLE_ALL;
-    const uint64_t ckey = subsampled ? rpf_subsample_centre_key(p.sub.seed, B, px, py + p.sub.row_g0) : 0ull;
+    const uint64_t ckey = SUBSAMPLED ? rpf_subsample_centre_key(p.sub.seed, B, px, py + p.sub.row_g0) : 0ull;
     uint32_t *mrow = p.mask + (static_cast<size_t>(py - p.row0) * W + px) * p.mw;
     unsigned long long buf = 0ull;
     int nbits = 0, wi = 0;
@@ -114,7 +114,7 @@ __global__ void __launch_bounds__(KM_MAX_THREADS) membership_kernel(const Member
                                     for (int k = 4; k < NF; ++k)
                                         if (fabs(__dsub_rn(cp[k], mu[k])) >= sd3[k]) acc = false;
                                 }
-                                if (subsampled && acc) acc = rpf_subsample_keep(ckey, p.sub.keep_q24, xn, yn + p.sub.row_g0, s0 + s);
+                                if (SUBSAMPLED && acc) acc = rpf_subsample_keep(ckey, p.sub.keep_q24, xn, yn + p.sub.row_g0, s0 + s);
                             }
                             bits |= static_cast<uint32_t>(acc) << s;
                         }

@@ -66,6 +66,7 @@ __device__ __forceinline__ double accumulate_task(unsigned char *colbase, const 
     return acc;
 }
 
+template <bool SUBSAMPLED>  // neighbour subsampling (include/rpf_subsample.h) compiled out of the default path
 __global__ void __launch_bounds__(THREADS, 4) rpf_pixel_kernel(const FilterParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ PixelSmall ps;
@@ -115,7 +116,7 @@ __global__ void __launch_bounds__(THREADS, 4) rpf_pixel_kernel(const FilterParam
                     const double d = fabs(__dsub_rn(static_cast<double>(fv[k]), ps.mu[k]));
                     if (d >= ps.sd3[k]) acc = false;
                 }
-                if (acc && p.sub.keep_q24 < RPF_SUBSAMPLE_ALL)
+                if (SUBSAMPLED && acc)
                     acc = rpf_subsample_keep(rpf_subsample_centre_key(p.sub.seed, B, px, py + p.sub.row_g0), p.sub.keep_q24, xn,
                                              yn + p.sub.row_g0, s);
             }
