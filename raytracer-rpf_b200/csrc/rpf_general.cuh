@@ -23,7 +23,7 @@ namespace rpf {
 constexpr int REC_M = 0, REC_SD = 19, REC_RLO = 38, REC_RHI = 57, REC_N = 76, REC_ALPHA = 77, REC_BETA = 80, REC_WRC = 92;
 constexpr int REC_DOUBLES = 96;  // per-pixel record in HBM scratch
 constexpr int KB_MAX_WARPS = 32, KB_GSM = 512;
-constexpr int KC_THREADS = 128, KC_SEG_WORDS = 128, KC_IC = 8;
+constexpr int KC_THREADS = 128, KC_WPT = 2, KC_SEG_WORDS = KC_WPT * KC_THREADS, KC_IC = 8;  // KC_WPT mask words per thread and segment
 
 struct GeneralPlan {
     int ncap;        // box*box*spp candidates
@@ -659,14 +659,24 @@ __global__ void __launch_bounds__(KC_THREADS, 4) blend_kernel(const GeneralParam
 #pragma unroll
         for (int ii = 0; ii < KC_IC; ++ii) { sw[ii] = 0.0; swc[ii][0] = swc[ii][1] = swc[ii][2] = 0.0; }
         for (int seg = 0; seg < nseg; ++seg) {
-            const int w = seg * KC_SEG_WORDS + tid;
-            unsigned bits = w < p.pl.mw ? mask[w] : 0u;
+            unsigned wbits[KC_WPT];
+            int cnt = 0;
+#pragma unroll
+            for (int k = 0; k < KC_WPT; ++k) {
+                const int w = seg * KC_SEG_WORDS + tid * KC_WPT + k;
+                wbits[k] = w < p.pl.mw ? mask[w] : 0u;
+                cnt += __popc(wbits[k]);
+            }
             int total;
-            int off = block_exclusive_scan<KC_THREADS>(__popc(bits), ks.wsum, &total);
-            while (bits) {
-                const int b = __ffs(bits) - 1;
-                bits &= bits - 1;
-                segidx[off++] = static_cast<unsigned short>(tid * 32 + b);
+            int off = block_exclusive_scan<KC_THREADS>(cnt, ks.wsum, &total);
+#pragma unroll
+            for (int k = 0; k < KC_WPT; ++k) {
+                unsigned bits = wbits[k];
+                while (bits) {
+                    const int b = __ffs(bits) - 1;
+                    bits &= bits - 1;
+                    segidx[off++] = static_cast<unsigned short>((tid * KC_WPT + k) * 32 + b);
+                }
             }
             __syncthreads();
             for (int n = tid; n < total; n += KC_THREADS) {

@@ -11,7 +11,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "librpf_b200.so")
+LIB_PATH = os.environ.get("RPF_B200_LIB", os.path.join(HERE, "lib", "librpf_b200.so"))
 NCH = 19
 FLAGS_DEFINED = 7
 FLAGS_VERBATIM = 0x100
