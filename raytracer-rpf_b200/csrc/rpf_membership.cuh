@@ -138,7 +138,7 @@ __global__ void __launch_bounds__(KM_MAX_THREADS) membership_kernel(const Member
 
 // =====================================================================================================
 constexpr int KO_WARPS = 4;  // pixels per CTA of the ordered statistics kernel
-constexpr int KO_GROUP = 8;  // mask words decoded per round
+constexpr int KO_GROUP = 16;  // mask words decoded per round
 
 __global__ void __launch_bounds__(KO_WARPS * 32) ordered_stats_kernel(const GeneralParams p) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
