@@ -531,7 +531,7 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
             const int hwn = (((nb * nb + 1) >> 1) + 3) & ~3;
             const int slots = L.region_words / hwn;
             int Gp, sets = 1, teams = 1;
-            if (slots >= 8) {
+            if (slots >= 4) {
                 Gp = 4;
                 // One set of tables per team; as many teams as fit (more independent teams hide more latency: 8 teams
                 // of 2 warps beat 4 of 4 by 10-20 %), then as many tables per team as still fit. Multi-warp teams
