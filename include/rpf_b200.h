@@ -98,6 +98,29 @@ int rpf_swap_colors(rpf_ctx *ctx);
  * neighbour pixel, sample number) in GLOBAL coordinates -- the CPU oracle and every row band draw the same stream.
  * global_row0 = global row of this context's row 0. keep_probability >= 1 switches it off (the default). */
 int rpf_set_subsampling(rpf_ctx *ctx, double keep_probability, unsigned long long rng_seed, int global_row0);
+/* Paper mode (Sen & Darabi 2012). None of it is in the reference (contrast rpf.cpp:531-533,575-583,
+ * 464-470,767): every field 0 -- the state after rpf_create, and what a NULL pointer restores -- is the reference's
+ * arithmetic bit for bit. The CPU restatement of each option is in oracle/rpf_oracle.cpp.
+ *   w_epsilon         added to the denominators of W_c_fk, W_r_fk and W_r_ck (rpf.cpp:464,465,470): no 0/0, and
+ *                     dependencies too small to measure give weights near 0 instead of noise ratios
+ *   min_sigma         low-variance guard of the 3-sigma test: the threshold is max(factor * sigma, min_sigma), so a
+ *                     pixel whose samples agree exactly (sigma = 0) still accepts neighbours that differ by rounding
+ *   world_pos_sigmas  factor for the world-position features p0, p1 (30 in the paper); 0 = 3 like every feature
+ * Takes effect from the next pass; the per-pixel thresholds are rebuilt when min_sigma / world_pos_sigmas change. */
+typedef struct rpf_paper_opts {
+    double w_epsilon;
+    double min_sigma;
+    double world_pos_sigmas;
+} rpf_paper_opts;
+int rpf_set_paper_mode(rpf_ctx *ctx, const rpf_paper_opts *opts);
+/* rpf_filter with one sigma_fc_seed per iteration (the paper lowers the variance from pass to pass; the reference
+ * uses the literal 0.002 of rpf.cpp:533 for every box size). Same as n_iter calls of rpf_filter with one box each. */
+int rpf_filter_sigmas(rpf_ctx *ctx, const int *box_sizes, const double *sigma_seeds, int n_iter);
+/* Paper-mode spike removal on the CURRENT colours, rows [y0,y1) (y1 <= 0: height), in place and stream ordered: per
+ * pixel and channel the sequential mean and population sigma of the spp samples; a sample with |c - mean| >
+ * k_sigmas * sigma in any channel takes the pixel mean in all three (the paper uses k = 1 after the last pass).
+ * Local to a pixel: row bands call it on their own rows, no exchange. */
+int rpf_hdr_clamp(rpf_ctx *ctx, double k_sigmas, int y0, int y1);
 /* Device pointers to the colour planes, [3][width*height*spp] doubles: which = 0 current, 1 next.
  * For halo exchange by the host (NCCL send/recv or peer copies between row bands). */
 int rpf_color_device_ptr(rpf_ctx *ctx, int which, double **out);

@@ -91,7 +91,7 @@ void bin_channels(const double *z /*[n][19]*/, int n, int bins, ChannelBins &cb)
 
 // rpf.cpp:356-488
 void cf_weights(const double *z, int n, int flags, double alpha[NC], double beta[NF], double &wrc,
-                ChannelBins &cb, std::vector<int> &joint) {
+                ChannelBins &cb, std::vector<int> &joint, double eps = 0.0) {
     const int bins = bins_for(n);
     bin_channels(z, n, bins, cb);
     auto MI = [&](int ca, int cbn) {
@@ -126,7 +126,10 @@ void cf_weights(const double *z, int n, int flags, double alpha[NC], double beta
         Dpc += D_p_c[i];
     }
     const bool p1 = flags & RPF_ORACLE_P1, p2 = flags & RPF_ORACLE_P2;
-    auto ratio = [&](double num, double den) { return (p2 && den == 0) ? 0.0 : num / den; };
+    auto ratio = [&](double num, double den) {
+        if (eps != 0) den = den + eps;  // paper mode: epsilon in the denominators
+        return (p2 && den == 0) ? 0.0 : num / den;
+    };
     // rpf.cpp:461-466
     double W_c_f[NF], W_r_f[NF], W_r_c[NC];
     for (int i = 0; i < NF; ++i) {
@@ -175,7 +178,12 @@ struct Subsample {
     int row0 = 0;
 };
 
-int filter_pixel(const Frame &f, int px, int py, int box, double seed, int flags, const Subsample &sub, double *col_out,
+// Paper mode (not in the reference): all zero = reference semantics
+struct Paper {
+    double w_eps = 0, min_sigma = 0, pos_sigmas = 0;
+};
+
+int filter_pixel(const Frame &f, int px, int py, int box, double seed, int flags, const Subsample &sub, const Paper &paper, double *col_out,
                  PixelScratch &s, int *n_out, double *alpha_out, double *beta_out, double *wrc_out) {
     const int P = f.P, W = f.W, H = f.H;
     const size_t base = (static_cast<size_t>(py) * W + px) * P;
@@ -191,6 +199,9 @@ int filter_pixel(const Frame &f, int px, int py, int box, double seed, int flags
         mu[k] = sum / static_cast<double>(P);
         const double sd = std::sqrt(sq / static_cast<double>(P) - mu[k] * mu[k]);
         sd3[k] = sd * 3;  // rpf.cpp:579 multiplyArray(stdDev, 3)
+        const bool world_pos = (k >= 3 && k < 6) || k >= 9;  // p0, p1 of sd.h:62-94
+        if (world_pos && paper.pos_sigmas > 0) sd3[k] = sd * paper.pos_sigmas;
+        if (paper.min_sigma > 0 && sd3[k] < paper.min_sigma) sd3[k] = paper.min_sigma;  // a NaN sigma stays NaN (accepts)
     }
     // rpf.cpp:558-586: own samples, then xn ascending, yn ascending, sample order
     s.nbh.clear();
@@ -240,7 +251,7 @@ int filter_pixel(const Frame &f, int px, int py, int box, double seed, int flags
             s.z[o] = SD[c] == 0 ? 0 : (s.raw[o] - M[c]) / SD[c];
         }
     double alpha[NC], beta[NF], wrc;
-    cf_weights(s.z.data(), n, flags, alpha, beta, wrc, s.cb, s.joint);
+    cf_weights(s.z.data(), n, flags, alpha, beta, wrc, s.cb, s.joint, paper.w_eps);
     if (n_out) *n_out = n;
     if (alpha_out) std::memcpy(alpha_out, alpha, sizeof alpha);
     if (beta_out) std::memcpy(beta_out, beta, sizeof beta);
@@ -301,8 +312,13 @@ extern "C" int rpf_oracle_filter(rpf_oracle_args *a) {
         sub.seed = a->subsample_seed;
         sub.row0 = a->global_row0;
     }
+    Paper paper;
+    paper.w_eps = a->w_epsilon;
+    paper.min_sigma = a->min_sigma;
+    paper.pos_sigmas = a->world_pos_sigmas;
     for (int it = 0; it < a->n_iter; ++it) {
         const int box = a->box_sizes[it];
+        const double seed = a->sigma_seeds ? a->sigma_seeds[it] : a->sigma_fc_seed;
         const bool last = it == a->n_iter - 1;
         nxt = cur;  // pixels outside the filtered window keep their colours
         Frame f{W, H, P, a->planes, S, cur.data()};
@@ -319,7 +335,7 @@ extern "C" int rpf_oracle_filter(rpf_oracle_args *a) {
                 for (int x = bx; x < bx + T && x < x1; ++x)
                     for (int y = by; y < by + T && y < y1; ++y) {
                         const size_t p = static_cast<size_t>(y) * W + x;
-                        nans += filter_pixel(f, x, y, box, a->sigma_fc_seed, a->flags, sub, nxt.data(), s,
+                        nans += filter_pixel(f, x, y, box, seed, a->flags, sub, paper, nxt.data(), s,
                                              last && a->nbh_size ? a->nbh_size + p : nullptr,
                                              last && a->alpha ? a->alpha + p * 3 : nullptr,
                                              last && a->beta ? a->beta + p * 12 : nullptr,
@@ -334,9 +350,37 @@ extern "C" int rpf_oracle_filter(rpf_oracle_args *a) {
         for (auto &t : th) t.join();
         cur.swap(nxt);  // rpf.cpp:732
     }
+    if (a->hdr_clamp_sigmas > 0 && a->n_iter > 0) rpf_oracle_hdr_clamp(cur.data(), W, H, P, y0, y1, a->hdr_clamp_sigmas);
     if (a->colors) std::memcpy(a->colors, cur.data(), 3 * S * sizeof(double));
     a->nan_count = nan_total.load();
     return 0;
+}
+
+extern "C" void rpf_oracle_hdr_clamp(double *colors, int width, int height, int spp, int y0, int y1, double k_sigmas) {
+    const size_t S = static_cast<size_t>(width) * height * spp;
+    for (int y = y0; y < y1; ++y)
+        for (int x = 0; x < width; ++x) {
+            const size_t base = (static_cast<size_t>(y) * width + x) * spp;
+            double mu[NC], lim[NC];
+            for (int k = 0; k < NC; ++k) {
+                const double *c = colors + k * S + base;
+                double sum = 0, sq = 0;
+                for (int i = 0; i < spp; ++i) {
+                    sum = sum + c[i];
+                    sq = sq + c[i] * c[i];
+                }
+                mu[k] = sum / static_cast<double>(spp);
+                const double var = sq / static_cast<double>(spp) - mu[k] * mu[k];
+                lim[k] = k_sigmas * std::sqrt(var > 0 ? var : 0.0);
+            }
+            for (int i = 0; i < spp; ++i) {
+                bool spike = false;
+                for (int k = 0; k < NC; ++k)
+                    if (std::fabs(colors[k * S + base + i] - mu[k]) > lim[k]) spike = true;
+                if (spike)
+                    for (int k = 0; k < NC; ++k) colors[k * S + base + i] = mu[k];
+            }
+        }
 }
 
 extern "C" double rpf_oracle_mi(const double *x, const double *y, int n) {

@@ -54,6 +54,16 @@ typedef struct rpf_oracle_args {
     unsigned int subsample_keep_q24;
     unsigned long long subsample_seed;
     int global_row0;         /* global row of local row 0 (row bands) */
+    /* Paper mode (Sen & Darabi 2012). None of it is in the reference; all zero = reference semantics.
+     *   w_epsilon         added to the denominators of W_c_fk, W_r_fk, W_r_ck (rpf.cpp:464,465,470)
+     *   min_sigma         low-variance guard of the 3-sigma test: threshold max(factor * sigma, min_sigma) (rpf.cpp:578-583)
+     *   world_pos_sigmas  factor for the world-position features p0, p1 (30 in the paper); 0 = 3 like every other feature
+     *   sigma_seeds       [n_iter] sigma_fc_seed of each iteration (NULL: sigma_fc_seed for all, rpf.cpp:533)
+     *   hdr_clamp_sigmas  after the last iteration a sample with a colour channel further than this many pixel sigmas from
+     *                     its pixel's mean is replaced by the mean (spike removal); 0 = off */
+    double w_epsilon, min_sigma, world_pos_sigmas;
+    const double *sigma_seeds;
+    double hdr_clamp_sigmas;
 } rpf_oracle_args;
 
 /* returns 0 on success, <0 on bad arguments */
@@ -67,6 +77,10 @@ void rpf_oracle_mean_std(const double *v, int n, double *mean, double *sd);
 
 /* rpf.cpp:356-488 restated: normalised neighbourhood z[n][19] -> alpha[3], beta[12], wrc */
 void rpf_oracle_cf_weights(const double *z, int n, int flags, double *alpha, double *beta, double *wrc);
+
+/* Paper-mode spike removal on colours [3][W*H*spp], rows [y0,y1): per pixel and channel the sequential mean and population
+ * sigma of the spp samples; a sample with |c - mean| > k_sigmas * sigma in any channel takes the mean in all three. */
+void rpf_oracle_hdr_clamp(double *colors, int width, int height, int spp, int y0, int y1, double k_sigmas);
 
 #ifdef __cplusplus
 }

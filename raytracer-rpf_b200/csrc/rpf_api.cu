@@ -35,6 +35,7 @@ struct rpf_ctx {
     size_t big_bytes = 0;
     bool force_large = false;
     SubsampleParams sub{0ull, RPF_SUBSAMPLE_ALL, 0};
+    double w_eps = 0.0, min_sigma = 0.0, pos_sigmas = 0.0;  // paper mode (rpf_set_paper_mode); all 0 = reference
     int blend_wide_min = 16;  // spp from which blend_wide_kernel replaces blend_kernel (RPF_BLEND_WIDE_MIN overrides)
     // general path (rpf_general.cuh): per-chunk scratch in HBM
     uint32_t *d_mask = nullptr;
@@ -478,7 +479,8 @@ static int ensure_pstat(rpf_ctx *ctx, const FrameView &f, int y0, int y1) {
     // features never change between iterations (rpf.cpp:715 writes colours only): computed once per upload
     const long long n = 1ll * (y1 - y0) * ctx->cfg.width * NF;
     prof_begin(ctx, RPF_K_PIXEL_STATS);
-    pixel_stats_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, ctx->stream>>>(f, y0, y1, ctx->d_pstat);
+    pixel_stats_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, ctx->stream>>>(f, y0, y1, ctx->d_pstat, ctx->min_sigma,
+                                                                                         ctx->pos_sigmas);
     prof_end(ctx);
     ctx->launches++;
     CU(ctx, cudaGetLastError());
@@ -572,6 +574,7 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
     p.cd = make_cand_decode(box, ctx->cfg.spp);
     p.flags = ctx->cfg.flags;
     p.seed = seed;
+    p.w_eps = ctx->w_eps;
     p.mask = ctx->d_mask;
     p.rec = ctx->d_rec;
     p.bins_scratch = ctx->d_bins;
@@ -665,6 +668,7 @@ static int launch_rows(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
     p.y1 = y1;
     p.flags = ctx->cfg.flags;
     p.seed = seed;
+    p.w_eps = ctx->w_eps;
     p.dbg_n = ctx->d_dbg_n;
     p.dbg_alpha = ctx->d_dbg_alpha;
     p.dbg_beta = ctx->d_dbg_beta;
@@ -714,6 +718,36 @@ extern "C" int rpf_set_subsampling(rpf_ctx *ctx, double keep_probability, unsign
     return RPF_OK;
 }
 
+extern "C" int rpf_set_paper_mode(rpf_ctx *ctx, const rpf_paper_opts *o) {
+    if (!ctx) return RPF_ERR_INVALID;
+    const rpf_paper_opts none{};
+    if (!o) o = &none;
+    if (!(o->w_epsilon >= 0.0) || !(o->min_sigma >= 0.0) || !(o->world_pos_sigmas >= 0.0))
+        return fail(ctx, RPF_ERR_INVALID, "rpf_set_paper_mode: options must be non-negative numbers");
+    ctx->w_eps = o->w_epsilon;
+    if (ctx->min_sigma != o->min_sigma || ctx->pos_sigmas != o->world_pos_sigmas) {
+        ctx->min_sigma = o->min_sigma;
+        ctx->pos_sigmas = o->world_pos_sigmas;
+        ctx->pstat_y0 = ctx->pstat_y1 = 0;  // the per-pixel thresholds are rebuilt by the next pass
+    }
+    return RPF_OK;
+}
+
+extern "C" int rpf_hdr_clamp(rpf_ctx *ctx, double k_sigmas, int y0, int y1) {
+    if (!ctx) return RPF_ERR_INVALID;
+    if (!ctx->uploaded) return fail(ctx, RPF_ERR_STATE, "rpf_hdr_clamp: no samples uploaded");
+    if (!(k_sigmas > 0.0)) return fail(ctx, RPF_ERR_INVALID, "rpf_hdr_clamp: k_sigmas must be positive");
+    if (y1 <= 0) y1 = ctx->cfg.height;
+    if (y0 < 0 || y1 > ctx->cfg.height || y0 >= y1) return fail(ctx, RPF_ERR_INVALID, "bad row range [%d,%d)", y0, y1);
+    CU(ctx, cudaSetDevice(ctx->cfg.device));
+    const long long n = 1ll * (y1 - y0) * ctx->cfg.width;
+    hdr_clamp_kernel<<<static_cast<unsigned>((n + 127) / 128), 128, 0, ctx->stream>>>(ctx->d_col[ctx->cur], ctx->S, ctx->cfg.width,
+                                                                                      ctx->cfg.spp, y0, y1, k_sigmas);
+    ctx->launches++;
+    CU(ctx, cudaGetLastError());
+    return RPF_OK;
+}
+
 extern "C" int rpf_swap_colors(rpf_ctx *ctx) {
     if (!ctx) return RPF_ERR_INVALID;
     ctx->cur ^= 1;
@@ -728,6 +762,22 @@ extern "C" int rpf_filter(rpf_ctx *ctx, const int *box_sizes, int n_iter, double
     CU(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
     for (int i = 0; i < n_iter; ++i) {
         rc = launch_rows(ctx, box_sizes[i], sigma_fc_seed, 0, ctx->cfg.height);
+        if (rc != RPF_OK) return rc;
+        ctx->cur ^= 1;  // rpf.cpp:732
+    }
+    CU(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    ctx->timing_pending = true;
+    return RPF_OK;
+}
+
+extern "C" int rpf_filter_sigmas(rpf_ctx *ctx, const int *box_sizes, const double *sigma_seeds, int n_iter) {
+    if (!ctx || (n_iter > 0 && (!box_sizes || !sigma_seeds)) || n_iter < 0) return fail(ctx, RPF_ERR_INVALID, "rpf_filter_sigmas: bad arguments");
+    CU(ctx, cudaSetDevice(ctx->cfg.device));
+    int rc = finish_timing(ctx);
+    if (rc != RPF_OK) return rc;
+    CU(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    for (int i = 0; i < n_iter; ++i) {
+        rc = launch_rows(ctx, box_sizes[i], sigma_seeds[i], 0, ctx->cfg.height);
         if (rc != RPF_OK) return rc;
         ctx->cur ^= 1;  // rpf.cpp:732
     }

@@ -58,6 +58,7 @@ struct FilterParams {
     double *dbg_alpha, *dbg_beta, *dbg_wrc;
     unsigned long long *counters;  // [0] sum N, [1] NaN channels, [2] min N, [3] max N
     SubsampleParams sub;
+    double w_eps;           // paper mode: epsilon added to the denominators of the W ratios (0 = reference)
 };
 
 // Non-colour channels are staged as floats in slots 0..15: slot -> channel.

@@ -78,6 +78,7 @@ struct GeneralParams {
     const unsigned long long *hq;
     int box, flags;
     double seed;
+    double w_eps;         // paper mode: epsilon of the W ratios (0 = reference)
     int row0, nrows;      // pixel rows of this chunk
     uint32_t *mask;       // [chunk pixels][mw]
     double *rec;          // [chunk pixels][REC_DOUBLES]
@@ -226,9 +227,12 @@ __device__ __forceinline__ void kb_prepare_pixel(KBSmall &ks, const double *rec,
 }
 
 // rpf.cpp:416-487 from the 96 mutual informations (same code path as phase 6 of the fused kernel)
-__device__ __forceinline__ void cf_weights_from_mi(KBSmall &ks, int flags, int tid) {
+__device__ __forceinline__ void cf_weights_from_mi(KBSmall &ks, int flags, double eps, int tid) {
     const bool p2 = flags & FLAG_P2;
-    auto ratio = [&](double num, double den) { return (p2 && den == 0.0) ? 0.0 : num / den; };
+    auto ratio = [&](double num, double den) {
+        if (eps != 0.0) den = den + eps;  // paper mode (rpf_set_paper_mode); 0 = the reference's ratios
+        return (p2 && den == 0.0) ? 0.0 : num / den;
+    };
     if (tid < NF) {
         const int i = tid;
         const double drf = (0.0 + ks.mi[4 * i]) + ks.mi[4 * i + 1];          // rpf.cpp:421
@@ -577,7 +581,7 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
         }
 
         // ---- dependencies -> alpha, beta, W_r_c (rpf.cpp:416-487) ------------------------------------------
-        cf_weights_from_mi(ks, p.flags, tid);
+        cf_weights_from_mi(ks, p.flags, p.w_eps, tid);
         if (tid < NC) rec[REC_ALPHA + tid] = ks.alpha[tid];
         if (tid < NF) rec[REC_BETA + tid] = ks.beta[tid];
         if (tid == 0) rec[REC_WRC] = ks.wrc;

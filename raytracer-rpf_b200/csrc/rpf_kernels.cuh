@@ -26,7 +26,9 @@ __global__ void colors_to_f64_kernel(const float *__restrict__ planes, size_t S,
 // ---------------------------------------------------------------------------------------------------
 // K1: per-pixel feature mean and 3*sigma (FillMeanAndStddev, rpf.cpp:302-353; getMean/getStdDev ops.h:111-144).
 // One thread per (pixel, feature); sums run sequentially in sample order like the reference.
-__global__ void pixel_stats_kernel(FrameView f, int y0, int y1, double *__restrict__ pstat) {
+// Paper mode (rpf_set_paper_mode; not in the reference, both 0 by default): world-position features take pos_sigmas
+// instead of 3, and the threshold never drops below min_sigma (low-variance guard). A NaN sigma stays NaN (accepts).
+__global__ void pixel_stats_kernel(FrameView f, int y0, int y1, double *__restrict__ pstat, double min_sigma, double pos_sigmas) {
     const long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
     const int k = static_cast<int>(t % NF);
     const long long pix = t / NF + static_cast<long long>(y0) * f.W;
@@ -42,7 +44,44 @@ __global__ void pixel_stats_kernel(FrameView f, int y0, int y1, double *__restri
     const double mu = __ddiv_rn(sum, n);
     const double sd = __dsqrt_rn(__dsub_rn(__ddiv_rn(sq, n), __dmul_rn(mu, mu)));  // no clamp: NaN is meaningful
     pstat[pix * 24 + k] = mu;
-    pstat[pix * 24 + NF + k] = __dmul_rn(sd, 3.0);  // rpf.cpp:579 multiplyArray(stdDev, 3)
+    double sd3 = __dmul_rn(sd, 3.0);  // rpf.cpp:579 multiplyArray(stdDev, 3)
+    const bool world_pos = (k >= 3 && k < 6) || k >= 9;  // p0, p1 of sd.h:62-94
+    if (world_pos && pos_sigmas > 0.0) sd3 = __dmul_rn(sd, pos_sigmas);
+    if (min_sigma > 0.0 && sd3 < min_sigma) sd3 = min_sigma;
+    pstat[pix * 24 + NF + k] = sd3;
+}
+
+// Paper-mode spike removal (rpf_hdr_clamp; not in the reference): one thread per pixel of rows [y0,y1). Per channel the
+// sequential mean and population sigma of the pixel's samples; a sample with |c - mean| > k * sigma in any channel
+// takes the mean in all three channels. In place on colours [3][S].
+__global__ void hdr_clamp_kernel(double *__restrict__ col, size_t S, int W, int P, int y0, int y1, double k_sigmas) {
+    const long long pix = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x + static_cast<long long>(y0) * W;
+    if (pix >= static_cast<long long>(y1) * W) return;
+    const size_t base = static_cast<size_t>(pix) * P;
+    double mu[NC], lim[NC];
+#pragma unroll
+    for (int k = 0; k < NC; ++k) {
+        const double *c = col + k * S + base;
+        double sum = 0.0, sq = 0.0;
+        for (int i = 0; i < P; ++i) {
+            sum = __dadd_rn(sum, c[i]);
+            sq = __dadd_rn(sq, __dmul_rn(c[i], c[i]));
+        }
+        const double n = static_cast<double>(P);
+        mu[k] = __ddiv_rn(sum, n);
+        const double var = __dsub_rn(__ddiv_rn(sq, n), __dmul_rn(mu[k], mu[k]));
+        lim[k] = __dmul_rn(k_sigmas, __dsqrt_rn(var > 0.0 ? var : 0.0));
+    }
+    for (int i = 0; i < P; ++i) {
+        bool spike = false;
+#pragma unroll
+        for (int k = 0; k < NC; ++k)
+            if (fabs(__dsub_rn(col[k * S + base + i], mu[k])) > lim[k]) spike = true;
+        if (spike) {
+#pragma unroll
+            for (int k = 0; k < NC; ++k) col[k * S + base + i] = mu[k];
+        }
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------

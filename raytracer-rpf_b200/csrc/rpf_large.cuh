@@ -238,7 +238,7 @@ __global__ void __launch_bounds__(KL_THREADS, 1) dependency_large_kernel(const G
                 if (ks.susp[t]) large_exact_pair(p, ks, sc, region, marg, t, N, nb, slab_rows);
         }
 
-        cf_weights_from_mi(ks, p.flags, tid);
+        cf_weights_from_mi(ks, p.flags, p.w_eps, tid);
         if (tid < NC) rec[REC_ALPHA + tid] = ks.alpha[tid];
         if (tid < NF) rec[REC_BETA + tid] = ks.beta[tid];
         if (tid == 0) rec[REC_WRC] = ks.wrc;

@@ -347,7 +347,11 @@ __global__ void __launch_bounds__(THREADS, 4) rpf_pixel_kernel(const FilterParam
     // mi[] order: 4*i + {r0,r1,p0,p1} for feature i; 48 + 16*i + {r0,r1,p0,p1,f0..f11} for colour i.
     {
         const bool p2 = p.flags & FLAG_P2;
-        auto ratio = [&](double num, double den) { return (p2 && den == 0.0) ? 0.0 : num / den; };
+        const double eps = p.w_eps;
+        auto ratio = [&](double num, double den) {
+            if (eps != 0.0) den = den + eps;  // paper mode (rpf_set_paper_mode); 0 = the reference's ratios
+            return (p2 && den == 0.0) ? 0.0 : num / den;
+        };
         if (tid < NF) {
             const int i = tid;
             const double drf = (0.0 + ps.mi[4 * i]) + ps.mi[4 * i + 1];          // rpf.cpp:421

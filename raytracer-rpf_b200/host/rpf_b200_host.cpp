@@ -66,8 +66,20 @@ static bool run(SamplingFilm &film, const RPFB200Options &opt, const rpf_film_de
     if (rpf_upload(ctx.get(), ptrs) != RPF_OK) return failed(error, "rpf_upload", ctx.get());
     // colours re-entering the filter after an earlier pass are doubles (sd.h:205-207): keep every bit
     if (rpf_upload_colors_f64(ctx.get(), colours.data()) != RPF_OK) return failed(error, "rpf_upload_colors_f64", ctx.get());
-    if (rpf_filter(ctx.get(), opt.boxSizes.data(), static_cast<int>(opt.boxSizes.size()), opt.sigmaSeed) != RPF_OK)
+    if ((opt.paper.w_epsilon != 0.0 || opt.paper.min_sigma != 0.0 || opt.paper.world_pos_sigmas != 0.0) &&
+        rpf_set_paper_mode(ctx.get(), &opt.paper) != RPF_OK)
+        return failed(error, "rpf_set_paper_mode", ctx.get());
+    if (!opt.sigmaSeeds.empty()) {
+        if (opt.sigmaSeeds.size() != opt.boxSizes.size()) {
+            if (error) *error = "RPFB200Options: sigmaSeeds must hold one value per box size";
+            return false;
+        }
+        if (rpf_filter_sigmas(ctx.get(), opt.boxSizes.data(), opt.sigmaSeeds.data(), static_cast<int>(opt.boxSizes.size())) != RPF_OK)
+            return failed(error, "rpf_filter_sigmas", ctx.get());
+    } else if (rpf_filter(ctx.get(), opt.boxSizes.data(), static_cast<int>(opt.boxSizes.size()), opt.sigmaSeed) != RPF_OK)
         return failed(error, "rpf_filter", ctx.get());
+    if (opt.hdrClampSigmas > 0.0 && rpf_hdr_clamp(ctx.get(), opt.hdrClampSigmas, 0, 0) != RPF_OK)
+        return failed(error, "rpf_hdr_clamp", ctx.get());
     if (rpf_download_colors_f64(ctx.get(), colours.data()) != RPF_OK) return failed(error, "rpf_download_colors_f64", ctx.get());
     rpf_stats_t st{};
     if (rpf_get_stats(ctx.get(), &st) != RPF_OK) return failed(error, "rpf_get_stats", ctx.get());

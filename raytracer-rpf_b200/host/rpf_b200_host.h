@@ -23,6 +23,10 @@ struct RPFB200Options {
     int flags = 0;                 // RPF_FLAG_* of include/rpf_b200.h; 0 = REF_DEFINED
     double keepProbability = 1.0;  // < 1: random neighbour subsampling (rpf_set_subsampling; not the reference's semantics)
     unsigned long long rngSeed = 0;
+    // Paper mode (rpf_set_paper_mode / rpf_filter_sigmas / rpf_hdr_clamp; none of it is the reference's semantics):
+    rpf_paper_opts paper{0.0, 0.0, 0.0};  // epsilon of the W ratios, low-variance guard, sigma factor of p0 / p1
+    std::vector<double> sigmaSeeds;       // one per box size when not empty, instead of sigmaSeed for all
+    double hdrClampSigmas = 0.0;          // > 0: spike removal after the last pass
 };
 
 struct RPFB200Report {

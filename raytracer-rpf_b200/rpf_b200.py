@@ -26,6 +26,7 @@ ABI_SYMBOLS = [
     "rpf_get_stats", "rpf_reset_stats", "rpf_set_profiling", "rpf_get_kernel_times", "rpf_max_neighbourhood",
     "rpf_synth_planes", "rpf_reconstruct_film", "rpf_film_filter_table",
     "rpf_buffer_write", "rpf_buffer_info_read", "rpf_buffer_read", "rpf_set_subsampling",
+    "rpf_set_paper_mode", "rpf_filter_sigmas", "rpf_hdr_clamp",
 ]
 
 
@@ -42,6 +43,11 @@ class Stats(C.Structure):
     _fields_ = [("pixels_filtered", C.c_longlong), ("nbh_sum", C.c_longlong), ("nbh_min", C.c_int),
                 ("nbh_max", C.c_int), ("nan_channels", C.c_longlong), ("kernel_launches", C.c_longlong),
                 ("last_filter_ms", C.c_double)]
+
+
+class PaperOpts(C.Structure):
+    """rpf_paper_opts: Sen & Darabi's additions, none of them in the reference; all 0 = reference arithmetic."""
+    _fields_ = [("w_epsilon", C.c_double), ("min_sigma", C.c_double), ("world_pos_sigmas", C.c_double)]
 
 
 class FilmDesc(C.Structure):
@@ -119,6 +125,9 @@ def lib():
         L.rpf_upload_colors_f64.argtypes = [vp, vp]
         L.rpf_filter.argtypes = [vp, vp, i, d]
         L.rpf_filter_rows.argtypes = [vp, i, d, i, i]
+        L.rpf_set_paper_mode.argtypes = [vp, vp]
+        L.rpf_filter_sigmas.argtypes = [vp, vp, vp, i]
+        L.rpf_hdr_clamp.argtypes = [vp, d, i, i]
         L.rpf_swap_colors.argtypes = [vp]
         L.rpf_color_device_ptr.argtypes = [vp, i, C.POINTER(vp)]
         L.rpf_stream.argtypes = [vp, C.POINTER(vp)]
@@ -236,6 +245,22 @@ class RPFFilter:
     def apply(self, box_sizes=(7,), sigma_fc_seed=0.002):
         bx = np.asarray(box_sizes, np.int32)
         self._check(lib().rpf_filter(self._h, _p(bx), len(bx), sigma_fc_seed))
+
+    def apply_sigmas(self, box_sizes, sigma_seeds):
+        """One sigma_fc_seed per iteration (paper mode; the reference uses 0.002 throughout, rpf.cpp:533)."""
+        bx = np.asarray(box_sizes, np.int32)
+        sg = np.asarray(sigma_seeds, np.float64)
+        assert len(bx) == len(sg)
+        self._check(lib().rpf_filter_sigmas(self._h, _p(bx), _p(sg), len(bx)))
+
+    def set_paper_mode(self, w_epsilon=0.0, min_sigma=0.0, world_pos_sigmas=0.0):
+        """Paper-mode options (include/rpf_b200.h rpf_paper_opts); no arguments restores the reference's arithmetic."""
+        o = PaperOpts(w_epsilon, min_sigma, world_pos_sigmas)
+        self._check(lib().rpf_set_paper_mode(self._h, C.byref(o)))
+
+    def hdr_clamp(self, k_sigmas=1.0, y0=0, y1=0):
+        """Spike removal on the current colours of rows [y0,y1) (y1 <= 0: all rows)."""
+        self._check(lib().rpf_hdr_clamp(self._h, C.c_double(k_sigmas), y0, y1))
 
     def filter_rows(self, box, y0, y1, sigma_fc_seed=0.002):
         self._check(lib().rpf_filter_rows(self._h, box, sigma_fc_seed, y0, y1))

@@ -21,6 +21,8 @@ class OracleArgs(C.Structure):
         ("nbh_size", C.c_void_p), ("alpha", C.c_void_p), ("beta", C.c_void_p), ("wrc", C.c_void_p),
         ("nan_count", C.c_longlong),
         ("subsample_keep_q24", C.c_uint), ("subsample_seed", C.c_ulonglong), ("global_row0", C.c_int),
+        ("w_epsilon", C.c_double), ("min_sigma", C.c_double), ("world_pos_sigmas", C.c_double),
+        ("sigma_seeds", C.c_void_p), ("hdr_clamp_sigmas", C.c_double),
     ]
 
 
@@ -45,6 +47,8 @@ def oracle():
         lib.rpf_oracle_mi.restype = C.c_double
         lib.rpf_oracle_mean_std.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         lib.rpf_oracle_cf_weights.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.rpf_oracle_hdr_clamp.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double]
+        lib.rpf_oracle_hdr_clamp.restype = None
         _oracle = lib
     return _oracle
 
@@ -76,7 +80,8 @@ def _p(a):
 
 
 def oracle_filter(planes, W, H, P, boxes, seed=0.002, flags=DEFINED, colors=None, threads=0,
-                  rows=None, cols=None, debug=False, subsample=None):
+                  rows=None, cols=None, debug=False, subsample=None, paper=None):
+    # paper = dict(w_epsilon=, min_sigma=, world_pos_sigmas=, sigma_seeds=[per iteration], hdr_clamp_sigmas=) or None
     # subsample = (keep probability, rng seed, global row of local row 0) or None
     """planes: float32 [19, W*H*P]. Returns dict(colors=[3,S] float64, N, alpha, beta, wrc, nan_count)."""
     planes = np.ascontiguousarray(planes, dtype=np.float32)
@@ -94,6 +99,15 @@ def oracle_filter(planes, W, H, P, boxes, seed=0.002, flags=DEFINED, colors=None
         a.subsample_keep_q24 = int(subsample[0] * (1 << 24))
         a.subsample_seed = subsample[1]
         a.global_row0 = subsample[2] if len(subsample) > 2 else 0
+    if paper:
+        a.w_epsilon = paper.get("w_epsilon", 0.0)
+        a.min_sigma = paper.get("min_sigma", 0.0)
+        a.world_pos_sigmas = paper.get("world_pos_sigmas", 0.0)
+        a.hdr_clamp_sigmas = paper.get("hdr_clamp_sigmas", 0.0)
+        if paper.get("sigma_seeds") is not None:
+            sg = np.asarray(paper["sigma_seeds"], np.float64)
+            assert len(sg) == len(bx)
+            a.sigma_seeds = _p(sg)
     out = {}
     if debug:
         out["N"] = np.zeros(W * H, np.int32)
