@@ -96,18 +96,25 @@ class DeviceColors:
         self.__cuda_array_interface__ = {"shape": (3, n), "typestr": "<f8", "data": (ptr, False), "version": 2}
 
 
-def run_passes(ctx, band, boxes, seed, dist=None, device=0):
+def run_passes(ctx, band, boxes, seed, dist=None, device=0, hdr_clamp_sigmas=0.0):
     """The loop of rpf.cpp:767-775 over one row band on one GPU: each pass filters the owned rows, then the freshly
     written colour rows within b_delta(next box) of a band edge go to the neighbouring ranks (NCCL send/recv over
-    NVLink) before the buffers swap. ctx: rpf_b200.RPFFilter holding the band plus its halo rows."""
+    NVLink) before the buffers swap. ctx: rpf_b200.RPFFilter holding the band plus its halo rows.
+    Paper mode: seed may be a sequence (one sigma per pass, rpf_filter_sigmas); hdr_clamp_sigmas > 0 runs the spike
+    removal on the owned rows after the last pass (local to a pixel: no exchange)."""
     import torch
     o0, o1 = band.local_own
     row = ctx.W * ctx.P
+    seeds = list(seed) if hasattr(seed, "__len__") else [seed] * len(boxes)
+    if len(seeds) != len(boxes):
+        raise ValueError("one sigma per box size")
     for i, b in enumerate(boxes):
-        ctx.filter_rows(b, o0, o1, seed)
+        ctx.filter_rows(b, o0, o1, seeds[i])
         if dist is not None and band.world > 1 and i + 1 < len(boxes):
             ctx.synchronize()
             nxt = torch.as_tensor(DeviceColors(ctx.color_ptr(1), ctx.S), device=f"cuda:{device}")
             exchange_halos(dist, band, boxes[i + 1], nxt, row)
             torch.cuda.synchronize(device)
         ctx.swap_colors()
+    if hdr_clamp_sigmas > 0 and len(boxes):
+        ctx.hdr_clamp(hdr_clamp_sigmas, o0, o1)

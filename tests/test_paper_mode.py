@@ -186,3 +186,22 @@ def test_paper_mode_off_again_is_the_reference_arithmetic():
     off = f.download_colors_f64()
     f.close()
     assert np.array_equal(ref, off) and not np.array_equal(ref, on)
+
+
+@pytest.mark.gpu
+def test_row_band_driver_takes_the_schedule_and_the_clamp():
+    """bands.run_passes with one sigma per pass and spike removal on the owned rows = rpf_filter_sigmas + rpf_hdr_clamp."""
+    import bands
+    import rpf_b200
+    W, H, P, boxes, sigmas = 28, 22, 8, [9, 7], [0.5, 0.25]
+    planes = _frame(W, H, P, seed=5)
+    o = ob.oracle_filter(planes, W, H, P, boxes, paper=dict(PAPER, sigma_seeds=sigmas, hdr_clamp_sigmas=1.0))["colors"]
+    f = rpf_b200.RPFFilter(W, H, P)
+    f.set_paper_mode(**PAPER)
+    f.upload(planes)
+    bands.run_passes(f, bands.make_band(0, 1, H, boxes), boxes, sigmas, hdr_clamp_sigmas=1.0)
+    g = f.download_colors_f64()
+    f.close()
+    m = ~np.isnan(o)
+    assert np.array_equal(np.isnan(g), np.isnan(o))
+    assert np.abs(g[m] - o[m]).max() <= 1e-9 * max(1.0, np.abs(o[m]).max())
