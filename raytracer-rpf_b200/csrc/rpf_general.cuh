@@ -93,6 +93,26 @@ struct GeneralParams {
     unsigned long long *counters;
 };
 
+// 256-bit gathers (LDG.E.256 on sm_100): a sample's 64-byte feature record in two requests instead of four, its
+// {r, g, b, 0} double4 in one instead of two. Addresses are 32-byte aligned (cudaMalloc base + multiples of 32).
+struct Rec16 { float4 q[4]; };
+__device__ __forceinline__ void ldg256(const float4 *p, float4 &a, float4 &b) {
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(p));
+}
+__device__ __forceinline__ Rec16 load_rec16(const float4 *rec16, uint32_t g) {
+    const float4 *p = rec16 + static_cast<size_t>(g) * 4;
+    Rec16 r;
+    ldg256(p, r.q[0], r.q[1]);
+    ldg256(p + 2, r.q[2], r.q[3]);
+    return r;
+}
+__device__ __forceinline__ double4 load_col4(const double4 *col4, uint32_t g) {
+    double4 c;
+    asm("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(c.x), "=d"(c.y), "=d"(c.z), "=d"(c.w) : "l"(col4 + g));  // constant per launch
+    return c;
+}
+
 __device__ __forceinline__ float warp_min_f(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
@@ -500,8 +520,8 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
                 uint32_t g;
                 bool centre;
                 candidate_sample(p.cd, t, px, py, B, P, W, H, g, centre);
-                const float4 *r16 = p.rec16 + static_cast<size_t>(g) * 4;
-                const double4 cc = p.col4[g];
+                const Rec16 r16 = load_rec16(p.rec16, g);
+                const double4 cc = load_col4(p.col4, g);
                 auto put = [&](int c, double x) {
                     const int b = bin_value(x, c, ks, nb, dnb);
                     bin8[c * cstride + m] = static_cast<uint8_t>(b);
@@ -512,7 +532,7 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
                 put(CH_COL + 2, cc.z);
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
-                    const float4 f = __ldg(r16 + q);
+                    const float4 f = r16.q[q];
                     put(slot_channel(4 * q + 0), f.x);
                     put(slot_channel(4 * q + 1), f.y);
                     put(slot_channel(4 * q + 2), f.z);

@@ -148,8 +148,8 @@ __global__ void __launch_bounds__(KL_THREADS, 1) dependency_large_kernel(const G
                 uint32_t g;
                 bool centre;
                 candidate_sample(p.cd, t, px, py, B, P, W, H, g, centre);
-                const float4 *r16 = p.rec16 + static_cast<size_t>(g) * 4;
-                const double4 cc = p.col4[g];
+                const Rec16 r16 = load_rec16(p.rec16, g);
+                const double4 cc = load_col4(p.col4, g);
                 auto put = [&](int c, double x) {
                     const int b = bin_value(x, c, ks, nb, dnb);
                     sc.bins[c * cs + m] = static_cast<uint16_t>(b);
@@ -160,7 +160,7 @@ __global__ void __launch_bounds__(KL_THREADS, 1) dependency_large_kernel(const G
                 put(CH_COL + 2, cc.z);
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
-                    const float4 f = __ldg(r16 + q);
+                    const float4 f = r16.q[q];
                     put(slot_channel(4 * q + 0), f.x);
                     put(slot_channel(4 * q + 1), f.y);
                     put(slot_channel(4 * q + 2), f.z);
