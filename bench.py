@@ -266,7 +266,7 @@ def main():
     roof = None
     if dom:
         general = dom != "rpf_pixel_kernel"
-        passes = [b for b in boxes if (b * b * P > 1279) == general] if dom != "pixel_stats_kernel" else boxes[:1]
+        passes = [b for b in boxes if (b * b * P > rpf_b200.lib().rpf_fused_max_candidates()) == general] if dom != "pixel_stats_kernel" else boxes[:1]
         alg_bytes = ALG_BYTES_PER_SAMPLE_ITER * own_samples * len(passes) * args.steps
         k_ms, k_n = kern[dom]["ms_total"], kern[dom]["launches"]
         achieved = alg_bytes / (k_ms * 1e-3) / 1e9

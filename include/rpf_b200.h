@@ -177,6 +177,10 @@ int rpf_get_kernel_times(rpf_ctx *ctx, rpf_kernel_times_t *out);
 
 /* Largest neighbourhood (box*box*spp candidate samples) this build can filter, for error messages and tests. */
 int rpf_max_neighbourhood(void);
+/* Largest box*box*spp served by the fused shared-memory kernel (one CTA per pixel); larger neighbourhoods take the
+ * general path. Default 512 (measured crossover on B200), at most 1279; the environment variable RPF_FUSED_MAX
+ * overrides. Both paths implement rpf.cpp:556-723 with the same results. */
+int rpf_fused_max_candidates(void);
 
 /* Deterministic synthetic feature buffer, host side, float32 values.
  * kind 0: all-noisy; kind 1: degenerate (flat normals, black background, duplicated samples).

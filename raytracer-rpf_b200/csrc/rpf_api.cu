@@ -96,8 +96,19 @@ static int bins_for(int n) {
 static int align16(int v) { return (v + 15) & ~15; }
 
 // Shared-memory plan for one pixel CTA. Returns false if the neighbourhood cannot fit.
+// Largest box*box*spp the fused kernel takes. It CAN run up to 1,279 candidates (u8 histogram cells with at most 4
+// remembered wraps, N >> 8 <= 4), but one CTA of 128 threads per pixel stops paying well before that: measured at 8 spp on
+// B200, fused / general = 90 / 101 ms at box 7 (392 candidates), 188 / 121 ms at box 9 (648), 433 / 145 ms at box 11
+// (968). RPF_FUSED_MAX overrides (tests keep the fused kernel covered up to its limit with it).
+static constexpr int kFusedHardMax = 1279, kFusedDefaultMax = 512;
+extern "C" int rpf_fused_max_candidates(void) {
+    int v = kFusedDefaultMax;
+    if (const char *e = getenv("RPF_FUSED_MAX")) v = atoi(e);
+    return v < 0 ? 0 : (v > kFusedHardMax ? kFusedHardMax : v);
+}
+
 static bool plan_smem(long long ncap, int spp, int limit, SmemLayout &L) {
-    if (ncap > 1279) return false;  // u8 histogram cells with at most 4 remembered wraps (N >> 8 <= 4)
+    if (ncap > rpf_fused_max_candidates()) return false;
     L.ncap = static_cast<int>(ncap);
     L.nstride = L.ncap | 1;
     const int nb = bins_for(L.ncap);

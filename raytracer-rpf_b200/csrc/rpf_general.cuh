@@ -658,7 +658,7 @@ __global__ void __launch_bounds__(KC_THREADS, 4) blend_kernel(const GeneralParam
     auto load_z = [&](uint32_t g, double *z, double *col) {
         const float4 *r16 = p.rec16 + static_cast<size_t>(g) * 4;
         const float4 f0 = __ldg(r16), f1 = __ldg(r16 + 1), f2 = __ldg(r16 + 2), f3 = __ldg(r16 + 3);
-        const double4 cc = p.col4[g];
+        const double4 cc = load_col4(p.col4, g);
         const float fs[16] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w, f2.x, f2.y, f2.z, f2.w, f3.x, f3.y, f3.z, f3.w};
         col[0] = cc.x; col[1] = cc.y; col[2] = cc.z;
 #pragma unroll
@@ -712,7 +712,7 @@ __global__ void __launch_bounds__(KC_THREADS, 4) blend_kernel(const GeneralParam
                 // by every own sample, and then the other 14 channels are never scaled (they are two thirds of the work)
                 const float4 *r16 = p.rec16 + static_cast<size_t>(g) * 4;
                 const float4 f0 = __ldg(r16), f1 = __ldg(r16 + 1), f2 = __ldg(r16 + 2), f3 = __ldg(r16 + 3);
-                const double4 cc = p.col4[g];
+                const double4 cc = load_col4(p.col4, g);
                 const double cj[NC] = {cc.x, cc.y, cc.z};
                 double zj[NWZ];
 #pragma unroll

@@ -26,7 +26,7 @@ ABI_SYMBOLS = [
     "rpf_get_stats", "rpf_reset_stats", "rpf_set_profiling", "rpf_get_kernel_times", "rpf_max_neighbourhood",
     "rpf_synth_planes", "rpf_reconstruct_film", "rpf_film_filter_table",
     "rpf_buffer_write", "rpf_buffer_info_read", "rpf_buffer_read", "rpf_set_subsampling",
-    "rpf_set_paper_mode", "rpf_filter_sigmas", "rpf_hdr_clamp",
+    "rpf_set_paper_mode", "rpf_filter_sigmas", "rpf_hdr_clamp", "rpf_fused_max_candidates",
 ]
 
 

@@ -52,6 +52,47 @@ def _compare(g, o, W, H, P):
 PATHS = pytest.mark.parametrize("general", [False, True], ids=["fused", "general"])
 
 
+@pytest.fixture(autouse=True)
+def _fused_kernel_up_to_its_limit(request, monkeypatch):
+    """By default neighbourhoods above 512 candidates go to the general path (rpf_fused_max_candidates: it is faster there);
+    the cases labelled 'fused' keep the fused kernel covered up to its hard limit of 1,279 candidates."""
+    if "fused" in request.node.name:
+        monkeypatch.setenv("RPF_FUSED_MAX", "1279")
+
+
+def test_default_crossover_between_the_fused_and_the_general_path(monkeypatch):
+    """box 7 x 8 spp (392 candidates) runs fused, box 9 x 8 spp (648) general; RPF_FUSED_MAX moves the line; same colours."""
+    import rpf_b200
+    monkeypatch.delenv("RPF_FUSED_MAX", raising=False)
+    assert rpf_b200.lib().rpf_fused_max_candidates() == 512
+    W, H, P = 24, 20, 8
+    planes = rpf_b200.synth_planes(W, H, P, seed=3, kind=0)
+
+    def run(box):
+        f = rpf_b200.RPFFilter(W, H, P)
+        f.set_profiling(True)
+        f.upload(planes)
+        f.apply([box], 0.3)
+        f.synchronize()
+        kt = f.kernel_times()
+        col = f.download_colors_f64()
+        f.close()
+        return kt, col
+
+    kt7, _ = run(7)
+    kt9, c9 = run(9)
+    assert kt7["rpf_pixel_kernel"][1] == 1 and kt7["dependency_kernel"][1] == 0
+    assert kt9["rpf_pixel_kernel"][1] == 0 and kt9["dependency_kernel"][1] >= 1
+    monkeypatch.setenv("RPF_FUSED_MAX", "1279")
+    kt9f, c9f = run(9)
+    assert kt9f["rpf_pixel_kernel"][1] == 1 and kt9f["dependency_kernel"][1] == 0
+    m = ~np.isnan(c9)
+    assert np.array_equal(np.isnan(c9), np.isnan(c9f)) and np.abs(c9[m] - c9f[m]).max() <= TOL_TIGHT * max(1.0, np.abs(c9[m]).max())
+    monkeypatch.setenv("RPF_FUSED_MAX", "0")
+    kt7g, _ = run(7)
+    assert kt7g["rpf_pixel_kernel"][1] == 0 and kt7g["dependency_kernel"][1] >= 1
+
+
 @PATHS
 @pytest.mark.parametrize("seed", [0.002, 0.2, 2.0])
 @pytest.mark.parametrize("kind", [0, 1])
