@@ -37,6 +37,12 @@ class Band:
 def make_band(rank, world, height, box_sizes):
     """Equal-height bands; halo = largest b_delta over all passes (feature rows are needed at that depth)."""
     halo = max(b_delta(b) for b in box_sizes)
+    # the exchange after a pass talks to the two adjacent ranks only: every band must own at least the rows the next
+    # pass reaches across its edge, or a pixel would need colours from a rank two bands away
+    reach = max([b_delta(b) for b in box_sizes[1:]], default=0)
+    if world > 1 and height // world < reach:
+        raise ValueError(f"{height} rows over {world} ranks leaves bands of {height // world} rows, thinner than the "
+                         f"{reach}-row halo of the later passes: use fewer ranks")
     own0 = rank * height // world
     own1 = (rank + 1) * height // world
     return Band(rank, world, height, own0, own1, max(0, own0 - halo), min(height, own1 + halo))

@@ -147,3 +147,53 @@ def test_host_cpp_dump_hook_round_trip(tmp_path):
     assert lib.host_dump_sampling_film(W, H, P, planes.ctypes.data, rw.ctypes.data, out.encode()) == 0
     got, grw, info = rpf_b200.read_buffer(out)
     assert np.array_equal(got, planes) and np.array_equal(grw, rw) and info["spp"] == P
+
+
+def test_fused_limit_and_its_override(monkeypatch):
+    """rpf_fused_max_candidates: 512 by default, RPF_FUSED_MAX moves it within [0, 1279] (no compute, no GPU)."""
+    rpf_b200 = _lib_or_skip()
+    f = rpf_b200.lib().rpf_fused_max_candidates
+    monkeypatch.delenv("RPF_FUSED_MAX", raising=False)
+    assert f() == 512
+    assert 7 * 7 * 8 <= f() < 9 * 9 * 8      # the shipped box 7 at 8 spp stays fused, box 9 does not
+    for env, want in (("0", 0), ("1279", 1279), ("100000", 1279), ("-5", 0), ("700", 700)):
+        monkeypatch.setenv("RPF_FUSED_MAX", env)
+        assert f() == want
+
+
+def test_new_entry_points_reject_a_null_context():
+    """Paper-mode entry points follow the error convention (negative status, nothing thrown) without a context."""
+    import ctypes as C
+    rpf_b200 = _lib_or_skip()
+    L = rpf_b200.lib()
+    o = rpf_b200.PaperOpts(1e-7, 0.1, 30.0)
+    bx = (C.c_int * 1)(7)
+    sg = (C.c_double * 1)(0.3)
+    assert L.rpf_set_paper_mode(None, C.byref(o)) < 0
+    assert L.rpf_filter_sigmas(None, bx, sg, 1) < 0
+    assert L.rpf_hdr_clamp(None, C.c_double(1.0), 0, 0) < 0
+
+
+def test_band_planning_small_frames_and_many_ranks():
+    """Bands tile the frame exactly for every world size, also when there are barely more rows than ranks; the buffered
+    rows cover the largest box's halo, clipped at the frame."""
+    import bands
+    for H, world, boxes in ((720, 8, [55, 35, 17, 7]), (9, 8, [7]), (64, 4, [17, 7]), (10, 3, [55])):
+        bs = [bands.make_band(r, world, H, boxes) for r in range(world)]
+        assert bs[0].own0 == 0 and bs[-1].own1 == H
+        assert all(a.own1 == b.own0 for a, b in zip(bs, bs[1:]))
+        assert all(b.own1 > b.own0 for b in bs)
+        d = bands.b_delta(max(boxes))
+        for b in bs:
+            assert b.buf0 == max(0, b.own0 - d) and b.buf1 == min(H, b.own1 + d)
+            assert b.local_own == (b.own0 - b.buf0, b.own1 - b.buf0) and b.local_height == b.buf1 - b.buf0
+
+
+def test_bands_thinner_than_the_halo_are_refused():
+    """Halo exchange is between adjacent ranks only; a plan that would need colours from two bands away fails loudly."""
+    import bands
+    import pytest
+    with pytest.raises(ValueError, match="thinner"):
+        bands.make_band(0, 8, 64, [55, 35, 17, 7])     # 8 rows per band, the box-35 pass reaches 17 rows
+    bands.make_band(0, 8, 64, [55])                    # one pass: nothing is exchanged
+    bands.make_band(0, 2, 64, [55, 35, 17, 7])         # 32 rows per band
