@@ -19,7 +19,28 @@ namespace pbrt {
 int ref_stub_threads = 1;
 static std::atomic<int> ref_nan_exit_flag{0};
 double ref_sigma_fc_seed = 0.002;  // rpf.cpp:533 literal; only the REF_DEFINED build reads this variable
+#ifndef REF_PAPER
 #define REF_RATIO(num, den) ((den) == 0 ? 0 : (num) / (den))
+#else
+// libref_rpf_paper.so: the REF_DEFINED build plus ref_paper.sed = the reference's own code carrying the two in-filter
+// options of paper mode, so that the oracle's restatement of them is pinned against the reference's
+// control flow and arithmetic rather than against itself. Both hooks are no-ops while the three globals are 0.
+double ref_w_eps = 0, ref_min_sigma = 0, ref_pos_sigmas = 0;
+#define REF_RATIO(num, den) \
+    (((::pbrt::ref_w_eps != 0 ? (den) + ::pbrt::ref_w_eps : (den))) == 0 \
+         ? 0                                                             \
+         : (num) / ((::pbrt::ref_w_eps != 0 ? (den) + ::pbrt::ref_w_eps : (den))))
+// stands in for multiplyArray(stdDev, 3) at rpf.cpp:579
+static SampleF ref_paper_thresholds(const SampleF &sd) {
+    SampleF t = multiplyArray(sd, 3);
+    for (int k = 0; k < SD_N_FEATURES; ++k) {
+        const bool world_pos = (k >= 3 && k < 6) || k >= 9;  // p0, p1 (sd.h:62-94)
+        if (world_pos && ref_pos_sigmas > 0) t[k] = sd[k] * ref_pos_sigmas;
+        if (ref_min_sigma > 0 && t[k] < ref_min_sigma) t[k] = ref_min_sigma;
+    }
+    return t;
+}
+#endif
 
 // Declaration mirror of rpf.h:28-96 restricted to what rpf.cpp:302-733 defines and uses.
 class RPFIntegrator {
@@ -47,6 +68,14 @@ double ref_mi(const double *x, const double *y, int n) {
     std::vector<double> a(x, x + n), b(y, y + n);
     return MutualInformation(a, b);
 }
+
+#ifdef REF_PAPER
+void ref_set_paper(double w_eps, double min_sigma, double pos_sigmas) {
+    ref_w_eps = w_eps;
+    ref_min_sigma = min_sigma;
+    ref_pos_sigmas = pos_sigmas;
+}
+#endif
 
 // ops.h:111-144 on one channel
 void ref_mean_std(const double *v, int n, double *mean, double *sd) {

@@ -94,6 +94,46 @@ def main():
     print("golden fixtures written to", GOLD)
 
 
+# Paper mode: the reference's own rpf.cpp:302-733 with the REF_DEFINED patches plus the two hooks of
+# oracle/ref_paper.sed (oracle/_ref/libref_rpf_paper.so), chained over the box sizes with one sigma per pass.
+# (W, H, P, boxes, sigmas, epsilon, min sigma, world-position factor, synth kind)
+PAPER_CASES = [
+    (20, 16, 8, [7], [0.3], 1e-7, 0.0, 0.0, 0),                    # epsilon alone
+    (20, 16, 8, [7], [0.3], 0.0, 0.1, 0.0, 1),                     # low-variance guard alone
+    (18, 14, 8, [9, 7, 5], [0.5, 0.25, 0.125], 1e-7, 0.1, 30.0, 1),  # everything, sigma per pass
+    (14, 12, 4, [5], [1.0], 1e-3, 0.05, 30.0, 0),
+]
+
+
+def paper_lib():
+    lib = C.CDLL(os.path.join(ob.ORACLE_DIR, "_ref", "libref_rpf_paper.so"))
+    lib.ref_apply_rpf_filter.argtypes = [C.c_int] * 3 + [C.c_void_p] * 2 + [C.c_int] * 2 + [C.c_double]
+    lib.ref_set_paper.argtypes = [C.c_double] * 3
+    lib.ref_set_paper.restype = None
+    return lib
+
+
+def paper_reference(lib, planes, W, H, P, boxes, sigmas, eps, min_sigma, pos):
+    """Colours after the passes and whether the reference would have exited on a NaN in any of them."""
+    col = planes[2:5].astype(np.float64).copy()
+    lib.ref_set_paper(eps, min_sigma, pos)
+    flag = 0
+    for box, sg in zip(boxes, sigmas):
+        flag |= lib.ref_apply_rpf_filter(W, H, P, planes.ctypes.data, col.ctypes.data, box, 8, sg)
+    lib.ref_set_paper(0.0, 0.0, 0.0)
+    return col, flag
+
+
+def paper_main():
+    lib = paper_lib()
+    for i, (W, H, P, boxes, sigmas, eps, ms, pos, kind) in enumerate(PAPER_CASES):
+        planes = synth(W, H, P, 3000 + i, kind)
+        col, flag = paper_reference(lib, planes, W, H, P, boxes, sigmas, eps, ms, pos)
+        np.savez_compressed(os.path.join(GOLD, f"paper_case{i}.npz"), planes=planes, colors=col, meta=np.array([W, H, P, kind]),
+                            boxes=np.array(boxes), sigmas=np.array(sigmas), opts=np.array([eps, ms, pos]), nan_exit=flag)
+    print("paper-mode fixtures written to", GOLD)
+
+
 # Film reconstruction cases (SURVEY.md 8(f) N1), from oracle/_ref/libref_film.so = the reference's own film.h / film.cpp /
 # filters lines. (W, H, P, filter kind, rx, ry, alpha, pixel bounds, scale, max luminance, ray weights?, synth kind)
 FILM_CASES = [
@@ -126,7 +166,9 @@ def film_main():
 
 if __name__ == "__main__":
     import sys
-    if len(sys.argv) > 1 and sys.argv[1] == "film":
+    if len(sys.argv) > 1 and sys.argv[1] == "paper":
+        paper_main()
+    elif len(sys.argv) > 1 and sys.argv[1] == "film":
         film_main()
     else:
         main()

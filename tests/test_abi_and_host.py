@@ -197,3 +197,38 @@ def test_bands_thinner_than_the_halo_are_refused():
         bands.make_band(0, 8, 64, [55, 35, 17, 7])     # 8 rows per band, the box-35 pass reaches 17 rows
     bands.make_band(0, 8, 64, [55])                    # one pass: nothing is exchanged
     bands.make_band(0, 2, 64, [55, 35, 17, 7])         # 32 rows per band
+
+
+def test_headers_are_plain_c_and_link_against_the_library(tmp_path):
+    """The boundary is a C ABI: include/*.h compile as pedantic C99, and a C program links against librpf_b200.so and calls
+    an entry point that needs no device (the cgo / JNI / ctypes binding of INTEGRATION.md sees exactly this)."""
+    import shutil
+    import subprocess
+    rpf_b200 = _lib_or_skip()
+    cc = shutil.which("gcc") or shutil.which("cc")
+    if cc is None:
+        import pytest
+        pytest.skip("no C compiler")
+    src = tmp_path / "abi.c"
+    src.write_text('#include "rpf_b200.h"\n#include "rpf_subsample.h"\n#include <stdio.h>\n'
+                   'int main(void) {\n'
+                   '    rpf_paper_opts o = {0, 0, 0};\n'
+                   '    rpf_ctx *ctx = 0;\n'
+                   '    rpf_config cfg = {0};\n'
+                   '    float table[256];\n'
+                   '    (void)o; (void)ctx; (void)cfg;\n'
+                   '    if (rpf_film_filter_table(0, 0.5f, 0.5f, 0.f, table) != RPF_OK) return 2;\n'
+                   '    if (rpf_subsample_keep(rpf_subsample_centre_key(1, 7, 3, 4), RPF_SUBSAMPLE_ALL, 1, 2, 0) != 1) return 3;\n'
+                   '    printf("%d %d\\n", rpf_fused_max_candidates(), rpf_max_neighbourhood());\n'
+                   '    return 0;\n}\n')
+    exe = tmp_path / "abi"
+    libdir = os.path.dirname(rpf_b200.LIB_PATH)
+    inc = os.path.join(ROOT, "include")
+    r = subprocess.run([cc, "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", f"-I{inc}", str(src), "-o", str(exe),
+                        f"-L{libdir}", "-lrpf_b200", f"-Wl,-rpath,{libdir}"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    env = dict(os.environ)
+    env.pop("RPF_FUSED_MAX", None)
+    r = subprocess.run([str(exe)], capture_output=True, text=True, env=env)
+    assert r.returncode == 0, (r.returncode, r.stderr)
+    assert r.stdout.split() == ["512", str(1 << 20)]

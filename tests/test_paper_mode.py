@@ -1,7 +1,10 @@
 """Paper mode: epsilon in the W denominators, the low-variance guard and the world-position factor of
 the 3-sigma test, one sigma per iteration, spike removal. None of it is in the reference, so there is no reference output
-to match: the CPU tests pin the oracle's restatement through properties (all-zero options = the golden fixtures bit for
-bit, limits, monotonicity, chaining), the GPU tests hold the kernels to the oracle as tightly as everywhere else."""
+to match as shipped. The in-filter options (epsilon, guard, factor, sigma per pass) are pinned against the reference's
+own rpf.cpp:302-733 compiled with two one-line hooks (oracle/ref_paper.sed -> oracle/_ref/libref_rpf_paper.so; fixtures
+tests/golden/paper_case*.npz), bit for bit; spike removal, which has no counterpart at all, against a numpy twin; plus
+properties (all-zero options = the reference arithmetic, limits, monotonicity, chaining). The GPU tests hold the kernels
+to the oracle as tightly as everywhere else."""
 import numpy as np
 import pytest
 
@@ -107,6 +110,60 @@ def test_hdr_clamp_restatement():
     a = ob.oracle_filter(planes, W, H, P, [5], seed=0.3)["colors"]
     b = ob.oracle_filter(planes, W, H, P, [5], seed=0.3, paper=dict(hdr_clamp_sigmas=1.0))["colors"]
     assert np.array_equal(b, _clamp_numpy(a, W, H, P, 1.0)[0])
+
+
+# ---- pinned against the reference's own code carrying the hooks (oracle/_ref/libref_rpf_paper.so, ref_paper.sed) --------
+import glob
+import os
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _oracle_for_fixture(g):
+    W, H, P, _ = (int(v) for v in g["meta"])
+    eps, ms, pos = (float(v) for v in g["opts"])
+    return ob.oracle_filter(g["planes"], W, H, P, [int(b) for b in g["boxes"]],
+                            paper=dict(w_epsilon=eps, min_sigma=ms, world_pos_sigmas=pos, sigma_seeds=list(g["sigmas"])))
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLD, "paper_case*.npz"))))
+def test_oracle_reproduces_the_patched_reference_bit_for_bit(path):
+    """Fixtures come from rpf.cpp:302-733 itself with REF_DEFINED + the two paper hooks (tests/make_golden.py paper)."""
+    g = np.load(path)
+    o = _oracle_for_fixture(g)
+    assert np.array_equal(o["colors"], g["colors"], equal_nan=True)
+    assert (o["nan_count"] > 0) == bool(g["nan_exit"])
+    assert np.isfinite(g["colors"]).mean() > 0.99 and not np.array_equal(g["colors"], g["planes"][2:5].astype(np.float64))
+
+
+def test_fixture_set_is_complete():
+    assert len(glob.glob(os.path.join(GOLD, "paper_case*.npz"))) == 4
+
+
+def test_live_patched_reference_on_fresh_cases():
+    """Where oracle/_ref exists (this container, and the GPU box through the snapshot): fresh random cases, and the
+    hooks are no-ops at 0 (the paper build then IS the REF_DEFINED build)."""
+    import make_golden as mg
+    if not os.path.exists(os.path.join(ob.ORACLE_DIR, "_ref", "libref_rpf_paper.so")):
+        pytest.skip("oracle/_ref/libref_rpf_paper.so not built")
+    lib = mg.paper_lib()
+    rng = np.random.default_rng(17)
+    for i in range(3):
+        W, H, P = int(rng.integers(10, 18)), int(rng.integers(8, 14)), int(rng.choice([2, 4, 8]))
+        boxes = [int(b) for b in rng.choice([5, 7, 9], size=2)]
+        sigmas = [float(v) for v in rng.uniform(0.1, 1.0, size=2)]
+        eps, ms, pos = float(10.0 ** rng.uniform(-9, -2)), float(rng.uniform(0.01, 0.3)), float(rng.choice([0.0, 10.0, 30.0]))
+        planes = _frame(W, H, P, seed=500 + i, kind=i % 2)
+        want, _ = mg.paper_reference(lib, planes, W, H, P, boxes, sigmas, eps, ms, pos)
+        got = ob.oracle_filter(planes, W, H, P, boxes,
+                               paper=dict(w_epsilon=eps, min_sigma=ms, world_pos_sigmas=pos, sigma_seeds=sigmas))["colors"]
+        assert np.array_equal(got, want, equal_nan=True), (W, H, P, boxes, sigmas, eps, ms, pos)
+    planes = _frame(14, 10, 8, seed=9)
+    off, _ = mg.paper_reference(lib, planes, 14, 10, 8, [7], [0.4], 0.0, 0.0, 0.0)
+    dlib = mg.defined_lib()
+    col = planes[2:5].astype(np.float64).copy()
+    dlib.ref_apply_rpf_filter(14, 10, 8, planes.ctypes.data, col.ctypes.data, 7, 8, 0.4)
+    assert np.array_equal(off, col, equal_nan=True)
 
 
 # ---------------------------------------------------------------- kernels (GPU) ---------------------------------------
