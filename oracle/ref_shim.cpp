@@ -14,6 +14,9 @@
 #include "custom/ops.h"
 #include "custom/sd.h"
 #include "custom/sample_film.h"
+#ifdef REF_PAPER
+#include "../include/rpf_subsample.h"
+#endif
 
 namespace pbrt {
 int ref_stub_threads = 1;
@@ -30,6 +33,13 @@ double ref_w_eps = 0, ref_min_sigma = 0, ref_pos_sigmas = 0;
     (((::pbrt::ref_w_eps != 0 ? (den) + ::pbrt::ref_w_eps : (den))) == 0 \
          ? 0                                                             \
          : (num) / ((::pbrt::ref_w_eps != 0 ? (den) + ::pbrt::ref_w_eps : (den))))
+unsigned ref_keep_q24 = RPF_SUBSAMPLE_ALL;
+unsigned long long ref_sub_seed = 0;
+// joined to the 3-sigma test at rpf.cpp:581: the counter-based keep decision every implementation shares
+static bool ref_paper_keep(int box, int cx, int cy, int nx, int ny, int s) {
+    if (ref_keep_q24 >= RPF_SUBSAMPLE_ALL) return true;
+    return rpf_subsample_keep(rpf_subsample_centre_key(ref_sub_seed, box, cx, cy), ref_keep_q24, nx, ny, s) != 0;
+}
 // stands in for multiplyArray(stdDev, 3) at rpf.cpp:579
 static SampleF ref_paper_thresholds(const SampleF &sd) {
     SampleF t = multiplyArray(sd, 3);
@@ -74,6 +84,10 @@ void ref_set_paper(double w_eps, double min_sigma, double pos_sigmas) {
     ref_w_eps = w_eps;
     ref_min_sigma = min_sigma;
     ref_pos_sigmas = pos_sigmas;
+}
+void ref_set_subsampling(unsigned keep_q24, unsigned long long seed) {
+    ref_keep_q24 = keep_q24 == 0 ? RPF_SUBSAMPLE_ALL : keep_q24;
+    ref_sub_seed = seed;
 }
 #endif
 

@@ -103,6 +103,11 @@ PAPER_CASES = [
     (18, 14, 8, [9, 7, 5], [0.5, 0.25, 0.125], 1e-7, 0.1, 30.0, 1),  # everything, sigma per pass
     (14, 12, 4, [5], [1.0], 1e-3, 0.05, 30.0, 0),
 ]
+# the same plus random neighbour subsampling: (..., keep probability, rng seed)
+PAPER_SUB_CASES = [
+    (20, 16, 8, [7], [0.3], 0.0, 0.0, 0.0, 0, 0.5, 99),             # subsampling alone
+    (18, 14, 8, [9, 7], [0.5, 0.25], 1e-7, 0.1, 30.0, 1, 0.25, 7),  # with everything else
+]
 
 
 def paper_lib():
@@ -110,17 +115,21 @@ def paper_lib():
     lib.ref_apply_rpf_filter.argtypes = [C.c_int] * 3 + [C.c_void_p] * 2 + [C.c_int] * 2 + [C.c_double]
     lib.ref_set_paper.argtypes = [C.c_double] * 3
     lib.ref_set_paper.restype = None
+    lib.ref_set_subsampling.argtypes = [C.c_uint, C.c_ulonglong]
+    lib.ref_set_subsampling.restype = None
     return lib
 
 
-def paper_reference(lib, planes, W, H, P, boxes, sigmas, eps, min_sigma, pos):
+def paper_reference(lib, planes, W, H, P, boxes, sigmas, eps, min_sigma, pos, keep=1.0, rng_seed=0):
     """Colours after the passes and whether the reference would have exited on a NaN in any of them."""
     col = planes[2:5].astype(np.float64).copy()
     lib.ref_set_paper(eps, min_sigma, pos)
+    lib.ref_set_subsampling(int(keep * (1 << 24)) if keep < 1.0 else 0, rng_seed)
     flag = 0
     for box, sg in zip(boxes, sigmas):
         flag |= lib.ref_apply_rpf_filter(W, H, P, planes.ctypes.data, col.ctypes.data, box, 8, sg)
     lib.ref_set_paper(0.0, 0.0, 0.0)
+    lib.ref_set_subsampling(0, 0)
     return col, flag
 
 
@@ -131,6 +140,12 @@ def paper_main():
         col, flag = paper_reference(lib, planes, W, H, P, boxes, sigmas, eps, ms, pos)
         np.savez_compressed(os.path.join(GOLD, f"paper_case{i}.npz"), planes=planes, colors=col, meta=np.array([W, H, P, kind]),
                             boxes=np.array(boxes), sigmas=np.array(sigmas), opts=np.array([eps, ms, pos]), nan_exit=flag)
+    for i, (W, H, P, boxes, sigmas, eps, ms, pos, kind, keep, rs) in enumerate(PAPER_SUB_CASES):
+        planes = synth(W, H, P, 3100 + i, kind)
+        col, flag = paper_reference(lib, planes, W, H, P, boxes, sigmas, eps, ms, pos, keep, rs)
+        np.savez_compressed(os.path.join(GOLD, f"paper_sub_case{i}.npz"), planes=planes, colors=col, meta=np.array([W, H, P, kind]),
+                            boxes=np.array(boxes), sigmas=np.array(sigmas), opts=np.array([eps, ms, pos]), nan_exit=flag,
+                            keep=keep, rng_seed=rs)
     print("paper-mode fixtures written to", GOLD)
 
 

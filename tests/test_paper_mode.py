@@ -122,11 +122,12 @@ GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 def _oracle_for_fixture(g):
     W, H, P, _ = (int(v) for v in g["meta"])
     eps, ms, pos = (float(v) for v in g["opts"])
-    return ob.oracle_filter(g["planes"], W, H, P, [int(b) for b in g["boxes"]],
+    sub = (float(g["keep"]), int(g["rng_seed"])) if "keep" in g.files else None
+    return ob.oracle_filter(g["planes"], W, H, P, [int(b) for b in g["boxes"]], subsample=sub,
                             paper=dict(w_epsilon=eps, min_sigma=ms, world_pos_sigmas=pos, sigma_seeds=list(g["sigmas"])))
 
 
-@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLD, "paper_case*.npz"))))
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLD, "paper_*case*.npz"))), ids=os.path.basename)
 def test_oracle_reproduces_the_patched_reference_bit_for_bit(path):
     """Fixtures come from rpf.cpp:302-733 itself with REF_DEFINED + the two paper hooks (tests/make_golden.py paper)."""
     g = np.load(path)
@@ -138,6 +139,7 @@ def test_oracle_reproduces_the_patched_reference_bit_for_bit(path):
 
 def test_fixture_set_is_complete():
     assert len(glob.glob(os.path.join(GOLD, "paper_case*.npz"))) == 4
+    assert len(glob.glob(os.path.join(GOLD, "paper_sub_case*.npz"))) == 2
 
 
 def test_live_patched_reference_on_fresh_cases():
@@ -154,10 +156,11 @@ def test_live_patched_reference_on_fresh_cases():
         sigmas = [float(v) for v in rng.uniform(0.1, 1.0, size=2)]
         eps, ms, pos = float(10.0 ** rng.uniform(-9, -2)), float(rng.uniform(0.01, 0.3)), float(rng.choice([0.0, 10.0, 30.0]))
         planes = _frame(W, H, P, seed=500 + i, kind=i % 2)
-        want, _ = mg.paper_reference(lib, planes, W, H, P, boxes, sigmas, eps, ms, pos)
-        got = ob.oracle_filter(planes, W, H, P, boxes,
+        keep, rs = (1.0, 0) if i == 0 else (float(rng.uniform(0.2, 0.8)), int(rng.integers(1, 1 << 40)))
+        want, _ = mg.paper_reference(lib, planes, W, H, P, boxes, sigmas, eps, ms, pos, keep, rs)
+        got = ob.oracle_filter(planes, W, H, P, boxes, subsample=None if keep >= 1.0 else (keep, rs),
                                paper=dict(w_epsilon=eps, min_sigma=ms, world_pos_sigmas=pos, sigma_seeds=sigmas))["colors"]
-        assert np.array_equal(got, want, equal_nan=True), (W, H, P, boxes, sigmas, eps, ms, pos)
+        assert np.array_equal(got, want, equal_nan=True), (W, H, P, boxes, sigmas, eps, ms, pos, keep, rs)
     planes = _frame(14, 10, 8, seed=9)
     off, _ = mg.paper_reference(lib, planes, 14, 10, 8, [7], [0.4], 0.0, 0.0, 0.0)
     dlib = mg.defined_lib()
