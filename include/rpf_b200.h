@@ -8,8 +8,9 @@
  * into structure-of-arrays planes and calls the entry points below instead of ApplyRPFFilter.
  *
  * Conventions: plain pointers and sizes only; every call returns RPF_OK (0) or a negative rpf_status and
- * leaves a message retrievable with rpf_last_error(). A context is bound to one CUDA device and is not
- * re-entrant. There is no CPU fallback: without a usable sm_100 device rpf_create fails.
+ * leaves a message retrievable with rpf_last_error(). A context is bound to one CUDA device -- or, with
+ * rpf_config.n_gpus > 1, to one row band per device -- and is not re-entrant. There is no CPU
+ * fallback: without a usable sm_100 device rpf_create fails.
  *
  * Sample layout: channel c of sample s of pixel (x,y) lives at plane[c][(y*width + x)*spp + s].
  * Channel order is SampleData::data (src/custom/sd.h:62-94):
@@ -25,6 +26,7 @@ extern "C" {
 #endif
 
 #define RPF_NUM_CHANNELS 19
+#define RPF_MAX_GPUS 8
 
 typedef enum rpf_status {
     RPF_OK = 0,
@@ -58,6 +60,15 @@ typedef struct rpf_config {
     int device;  /* CUDA device ordinal */
     int flags;   /* RPF_FLAG_* bits; 0 selects RPF_FLAGS_DEFINED, RPF_FLAGS_VERBATIM selects none */
     int debug;   /* 1: keep per-pixel N, alpha, beta, W_r_c of the last iteration for rpf_download_debug */
+    /* Row-band sharding inside ONE process (the role of ParallelFor2D over tiles, rpf.cpp:542, parallel.cpp:247-299):
+     * n_gpus 0 or 1 = the single device `device`; 2..8 = the frame is split into n_gpus row bands of equal WORK
+     * (rpf_band_plan), band g on device_ids[g]. The context then owns one band buffer, one compute stream and one
+     * copy stream per device; rpf_filter exchanges the colour halo rows between passes with peer copies over NVLink
+     * that overlap the interior rows. Results are bit-identical to n_gpus = 1. */
+    int n_gpus;
+    int device_ids[RPF_MAX_GPUS];
+    int max_box;  /* n_gpus > 1 only: largest box size rpf_filter will be given; every band keeps b_delta(max_box) halo
+                     rows of all planes. 0 = 55 (north_star's schedule 55/35/17/7). */
 } rpf_config;
 
 typedef struct rpf_stats_t {
@@ -66,7 +77,8 @@ typedef struct rpf_stats_t {
     int nbh_min, nbh_max;
     long long nan_channels;      /* NaN colour channels written (rpf.cpp:702-705 would exit(1); here: counted) */
     long long kernel_launches;   /* device kernels launched by this context */
-    double last_filter_ms;       /* device time of the last rpf_filter / rpf_filter_rows call (CUDA events) */
+    double last_filter_ms;       /* device time of the last rpf_filter / rpf_filter_rows call (CUDA events; the slowest band when sharded) */
+    long long halo_bytes;        /* colour bytes sent to neighbouring row bands since create/reset (0 on an unsharded context) */
 } rpf_stats_t;
 
 /* Replaces the SamplingFilm container (sample_film.h:28-45): allocate device planes for width*height*spp samples. */
@@ -158,6 +170,40 @@ int rpf_reconstruct_film(rpf_ctx *ctx, const rpf_film_desc *film, const float *r
 /* Host helper: the Film constructor's filter table (core/film.cpp:69-77) for pbrt's box (kind 0, filters/box.cpp:41)
  * or gaussian (kind 1, filters/gaussian.h:52-66, gaussian.cpp:41-43) filter. Other filters: evaluate them yourself. */
 int rpf_film_filter_table(int kind, float radius_x, float radius_y, float alpha, float table[256]);
+
+/* ---- row bands: pixels are independent within a pass (Jacobi, rpf.cpp:527,732), so the frame splits
+ * along y; features never change (rpf.cpp:715 writes colours only), so a band holds its rows plus b_delta(largest box)
+ * halo rows of all 19 planes once, and between passes only the 3 colour planes of the b_delta(next box) rows next to a
+ * band edge move to the neighbouring band.
+ *
+ * rpf_band_plan (host only, no device): first owned row of each of n_bands bands, own0[0..n_bands] with own0[n_bands] =
+ * height, so that every band carries about the same WORK: a row's weight is sum over passes of box^2 * (rows of the
+ * box inside the frame) / box -- rows near the top and bottom edge see truncated boxes and are cheaper. Every band owns
+ * at least b_delta(largest later box) rows, so the exchange after a pass talks to adjacent bands only; RPF_ERR_INVALID
+ * if the frame is too short for that. */
+int rpf_band_plan(int height, int n_bands, const int *box_sizes, int n_iter, int *own0 /* [n_bands + 1] */);
+
+/* One band per PROCESS (torchrun-style launch, one process per GPU): this context holds global rows [buf0, buf0 +
+ * cfg.height) of a frame of global_height rows and owns rows [own0, own1). After rpf_band_attach, rpf_filter /
+ * rpf_filter_sigmas run the band schedule: per pass the rows next to a band edge are filtered first, their colours go
+ * to the neighbouring ranks with ncclSend / ncclRecv on the context's copy stream while the interior rows are filtered,
+ * and no host synchronisation happens inside the schedule. NCCL is resolved at run time (dlopen of libnccl.so.2: the
+ * one the process already loaded, e.g. torch's); nccl_unique_id = the 128 bytes of ncclUniqueId, created with
+ * rpf_band_unique_id on rank 0 and handed to every rank by the launcher. rpf_download_* return the whole local buffer;
+ * only the owned rows are meaningful. */
+typedef struct rpf_band {
+    int global_height;
+    int buf0;        /* global row of this context's row 0 */
+    int own0, own1;  /* owned global rows */
+    int rank, world;
+} rpf_band;
+int rpf_band_unique_id(void *out128);
+int rpf_band_attach(rpf_ctx *ctx, const rpf_band *band, const void *nccl_unique_id);
+
+/* Page-locked host memory for the planes handed to rpf_upload and the buffers rpf_download_* fill: uploads from it are
+ * asynchronous single DMA transfers (the reference's host container is nested std::vectors, sample_film.h:28-45). */
+int rpf_host_alloc(void **out, size_t bytes);
+void rpf_host_free(void *p);
 
 int rpf_get_stats(rpf_ctx *ctx, rpf_stats_t *out);
 int rpf_reset_stats(rpf_ctx *ctx);

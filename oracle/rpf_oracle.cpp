@@ -240,7 +240,7 @@ int filter_pixel(const Frame &f, int px, int py, int box, double seed, int flags
         }
         M[c] = sum / static_cast<double>(n);
         double var = sq / static_cast<double>(n) - M[c] * M[c];
-        if ((flags & RPF_ORACLE_P3) && !(var > 0)) var = (var != var) ? var : 0.0;
+        if ((flags & RPF_ORACLE_P3) && !(var > 0)) var = 0.0;  // sqrt(std::max(0.0, var)): a NaN variance gives 0 as well
         SD[c] = std::sqrt(var);
     }
     // rpf.cpp:603-612, sd.h:224-235, ops.h:44-51. The own samples are the first P entries.

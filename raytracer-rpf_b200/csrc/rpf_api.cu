@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include <string>
 #include <vector>
 
@@ -68,6 +69,17 @@ struct rpf_ctx {
     double last_ms = 0.0;
     int max_dyn_smem = 0;
     std::string err;
+    bool col4_valid = false;        // col4 / the colour slots of rec19 hold the CURRENT colours (general path, once per pass)
+    // ---- row bands (rpf_bands.inl) ----
+    std::vector<rpf_ctx *> shards;  // n_gpus > 1: this context is the parent of one child per device and owns no device memory
+    std::vector<int> shard_own0;    // [n+1] first owned global row of every band
+    std::vector<int> shard_buf0, shard_buf1;  // global rows a band's buffer holds
+    int halo_rows = 0;
+    rpf_band band{};                // one band per process (rpf_band_attach): world > 1
+    void *nccl_comm = nullptr;
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_edge = nullptr, ev_copy = nullptr, ev_start = nullptr;
+    unsigned long long halo_bytes = 0;  // colour bytes this context sent to neighbouring bands since reset_stats
 };
 
 static thread_local std::string g_create_err;
@@ -144,11 +156,19 @@ static const int kLargeMaxCandidates = 1 << 20;  // 2^-38 fixed-point entropy su
 
 extern "C" int rpf_max_neighbourhood(void) { return kLargeMaxCandidates; }
 
+static void band_release(rpf_ctx *ctx);  // rpf_bands.inl state: NCCL communicator, copy stream, events
+
 extern "C" const char *rpf_last_error(const rpf_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
 
 extern "C" void rpf_destroy(rpf_ctx *ctx) {
     if (!ctx) return;
+    if (!ctx->shards.empty()) {
+        for (rpf_ctx *c : ctx->shards) rpf_destroy(c);
+        delete ctx;
+        return;
+    }
     cudaSetDevice(ctx->cfg.device);
+    band_release(ctx);
     cudaFree(ctx->d_planes);
     cudaFree(ctx->d_col[0]);
     cudaFree(ctx->d_col[1]);
@@ -262,6 +282,8 @@ static int ensure_gtab(rpf_ctx *ctx, int n) {
     return RPF_OK;
 }
 
+static int create_sharded(rpf_ctx **out, const rpf_config *cfg, int ndev);
+
 extern "C" int rpf_create(rpf_ctx **out, const rpf_config *cfg) {
     if (!out || !cfg) return fail(nullptr, RPF_ERR_INVALID, "rpf_create: null argument");
     *out = nullptr;
@@ -272,6 +294,7 @@ extern "C" int rpf_create(rpf_ctx **out, const rpf_config *cfg) {
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
         return fail(nullptr, RPF_ERR_NO_DEVICE, "rpf_create: no CUDA device (this library has no CPU fallback)");
+    if (cfg->n_gpus > 1) return create_sharded(out, cfg, ndev);
     if (cfg->device < 0 || cfg->device >= ndev) return fail(nullptr, RPF_ERR_INVALID, "rpf_create: bad device ordinal");
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, cfg->device) != cudaSuccess || prop.major != 10)
@@ -351,12 +374,27 @@ static int after_upload(rpf_ctx *ctx) {
     CU(ctx, cudaGetLastError());
     ctx->pstat_y0 = ctx->pstat_y1 = 0;
     ctx->rec16_valid = false;
+    ctx->col4_valid = false;
     ctx->uploaded = true;
     return RPF_OK;
 }
 
 extern "C" int rpf_upload(rpf_ctx *ctx, const float *const planes[RPF_NUM_CHANNELS]) {
     if (!ctx || !planes) return fail(ctx, RPF_ERR_INVALID, "rpf_upload: null argument");
+    if (!ctx->shards.empty()) {  // every band takes its rows (own + halo) of every plane: y is the slow index, a band is contiguous
+        const size_t row = static_cast<size_t>(ctx->cfg.width) * ctx->cfg.spp;
+        for (size_t g = 0; g < ctx->shards.size(); ++g) {
+            const float *sub[RPF_NUM_CHANNELS];
+            for (int c = 0; c < NCH; ++c) {
+                if (!planes[c]) return fail(ctx, RPF_ERR_INVALID, "rpf_upload: plane %d is null", c);
+                sub[c] = planes[c] + ctx->shard_buf0[g] * row;
+            }
+            const int rc = rpf_upload(ctx->shards[g], sub);
+            if (rc != RPF_OK) { ctx->err = ctx->shards[g]->err; return rc; }
+        }
+        ctx->uploaded = true;
+        return RPF_OK;
+    }
     CU(ctx, cudaSetDevice(ctx->cfg.device));
     for (int c = 0; c < NCH; ++c) {
         if (!planes[c]) return fail(ctx, RPF_ERR_INVALID, "rpf_upload: plane %d is null", c);
@@ -368,6 +406,7 @@ extern "C" int rpf_upload(rpf_ctx *ctx, const float *const planes[RPF_NUM_CHANNE
 
 extern "C" int rpf_upload_device(rpf_ctx *ctx, const float *const d_planes[RPF_NUM_CHANNELS]) {
     if (!ctx || !d_planes) return fail(ctx, RPF_ERR_INVALID, "rpf_upload_device: null argument");
+    if (!ctx->shards.empty()) return fail(ctx, RPF_ERR_UNSUPPORTED, "rpf_upload_device: not available on a context sharded over several devices");
     CU(ctx, cudaSetDevice(ctx->cfg.device));
     for (int c = 0; c < NCH; ++c) {
         if (!d_planes[c]) return fail(ctx, RPF_ERR_INVALID, "rpf_upload_device: plane %d is null", c);
@@ -380,6 +419,19 @@ extern "C" int rpf_upload_device(rpf_ctx *ctx, const float *const d_planes[RPF_N
 extern "C" int rpf_upload_colors_f64(rpf_ctx *ctx, const double *rgb) {
     if (!ctx || !rgb) return fail(ctx, RPF_ERR_INVALID, "rpf_upload_colors_f64: null argument");
     if (!ctx->uploaded) return fail(ctx, RPF_ERR_STATE, "rpf_upload_colors_f64: call rpf_upload first");
+    if (!ctx->shards.empty()) {
+        const size_t row = static_cast<size_t>(ctx->cfg.width) * ctx->cfg.spp, S = row * ctx->cfg.height;
+        for (size_t g = 0; g < ctx->shards.size(); ++g) {
+            rpf_ctx *c = ctx->shards[g];
+            CU(ctx, cudaSetDevice(c->cfg.device));
+            for (int k = 0; k < 3; ++k)
+                CU(ctx, cudaMemcpyAsync(c->d_col[c->cur] + k * c->S, rgb + k * S + ctx->shard_buf0[g] * row, c->S * sizeof(double),
+                                        cudaMemcpyHostToDevice, c->stream));
+            c->col4_valid = false;
+        }
+        return RPF_OK;
+    }
+    ctx->col4_valid = false;
     CU(ctx, cudaSetDevice(ctx->cfg.device));
     CU(ctx, cudaMemcpyAsync(ctx->d_col[ctx->cur], rgb, 3 * ctx->S * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
     return RPF_OK;
@@ -486,17 +538,20 @@ static int ensure_buffer(rpf_ctx *ctx, T **ptr, size_t *have, size_t need) {
 }
 
 static int ensure_pstat(rpf_ctx *ctx, const FrameView &f, int y0, int y1) {
-    if (ctx->pstat_y0 <= y0 && y1 <= ctx->pstat_y1) return RPF_OK;
-    // features never change between iterations (rpf.cpp:715 writes colours only): computed once per upload
-    const long long n = 1ll * (y1 - y0) * ctx->cfg.width * NF;
+    (void)y0; (void)y1;
+    if (ctx->pstat_y1 > ctx->pstat_y0) return RPF_OK;
+    // Features never change between iterations (rpf.cpp:715 writes colours only): computed once per upload, for EVERY
+    // row of the context (0.16 ms at 720p) -- callers may filter any rows in any order (rpf_filter_rows), and a cached
+    // interval merged across a gap would leave rows in between uninitialised.
+    const long long n = 1ll * ctx->cfg.height * ctx->cfg.width * NF;
     prof_begin(ctx, RPF_K_PIXEL_STATS);
-    pixel_stats_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, ctx->stream>>>(f, y0, y1, ctx->d_pstat, ctx->min_sigma,
+    pixel_stats_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, ctx->stream>>>(f, 0, ctx->cfg.height, ctx->d_pstat, ctx->min_sigma,
                                                                                          ctx->pos_sigmas);
     prof_end(ctx);
     ctx->launches++;
     CU(ctx, cudaGetLastError());
-    if (ctx->pstat_y1 <= ctx->pstat_y0) { ctx->pstat_y0 = y0; ctx->pstat_y1 = y1; }
-    else { ctx->pstat_y0 = y0 < ctx->pstat_y0 ? y0 : ctx->pstat_y0; ctx->pstat_y1 = y1 > ctx->pstat_y1 ? y1 : ctx->pstat_y1; }
+    ctx->pstat_y0 = 0;
+    ctx->pstat_y1 = ctx->cfg.height;
     return RPF_OK;
 }
 
@@ -568,9 +623,12 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
         ctx->launches += 2;
         ctx->rec16_valid = true;
     }
-    pack_colors_kernel<<<static_cast<unsigned>((ctx->S + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_col[ctx->cur], ctx->S, ctx->d_col4, ctx->d_rec19);
-    ctx->launches++;
-    CU(ctx, cudaGetLastError());
+    if (!ctx->col4_valid) {  // once per pass, however many row ranges the pass is launched in (band edges first, then the interior)
+        pack_colors_kernel<<<static_cast<unsigned>((ctx->S + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_col[ctx->cur], ctx->S, ctx->d_col4, ctx->d_rec19);
+        ctx->launches++;
+        CU(ctx, cudaGetLastError());
+        ctx->col4_valid = true;
+    }
     p.rec16 = ctx->d_rec16;
     p.col4 = ctx->d_col4;
     p.rec19 = ctx->d_rec19;
@@ -708,8 +766,15 @@ static int finish_timing(rpf_ctx *ctx) {
     return RPF_OK;
 }
 
+#include "rpf_bands.inl"
+
+#define NOT_SHARDED(ctx, name)                                                                                         \
+    if (!(ctx)->shards.empty())                                                                                        \
+        return fail(ctx, RPF_ERR_UNSUPPORTED, name ": not available on a context sharded over several devices (n_gpus > 1)")
+
 extern "C" int rpf_filter_rows(rpf_ctx *ctx, int box_size, double sigma_fc_seed, int y0, int y1) {
     if (!ctx) return RPF_ERR_INVALID;
+    NOT_SHARDED(ctx, "rpf_filter_rows");
     CU(ctx, cudaSetDevice(ctx->cfg.device));
     int rc = finish_timing(ctx);
     if (rc != RPF_OK) return rc;
@@ -723,6 +788,8 @@ extern "C" int rpf_filter_rows(rpf_ctx *ctx, int box_size, double sigma_fc_seed,
 
 extern "C" int rpf_set_subsampling(rpf_ctx *ctx, double keep_probability, unsigned long long rng_seed, int global_row0) {
     if (!ctx || !(keep_probability > 0.0)) return fail(ctx, RPF_ERR_INVALID, "rpf_set_subsampling: keep probability must be in (0, 1]");
+    for (size_t g = 0; g < ctx->shards.size(); ++g)  // the RNG is keyed by GLOBAL coordinates: every band draws the same stream
+        rpf_set_subsampling(ctx->shards[g], keep_probability, rng_seed, global_row0 + ctx->shard_buf0[g]);
     ctx->sub.keep_q24 = keep_probability >= 1.0 ? RPF_SUBSAMPLE_ALL : static_cast<unsigned>(keep_probability * (1 << 24));
     ctx->sub.seed = rng_seed;
     ctx->sub.row_g0 = global_row0;
@@ -735,6 +802,7 @@ extern "C" int rpf_set_paper_mode(rpf_ctx *ctx, const rpf_paper_opts *o) {
     if (!o) o = &none;
     if (!(o->w_epsilon >= 0.0) || !(o->min_sigma >= 0.0) || !(o->world_pos_sigmas >= 0.0))
         return fail(ctx, RPF_ERR_INVALID, "rpf_set_paper_mode: options must be non-negative numbers");
+    for (rpf_ctx *c : ctx->shards) rpf_set_paper_mode(c, o);
     ctx->w_eps = o->w_epsilon;
     if (ctx->min_sigma != o->min_sigma || ctx->pos_sigmas != o->world_pos_sigmas) {
         ctx->min_sigma = o->min_sigma;
@@ -750,6 +818,16 @@ extern "C" int rpf_hdr_clamp(rpf_ctx *ctx, double k_sigmas, int y0, int y1) {
     if (!(k_sigmas > 0.0)) return fail(ctx, RPF_ERR_INVALID, "rpf_hdr_clamp: k_sigmas must be positive");
     if (y1 <= 0) y1 = ctx->cfg.height;
     if (y0 < 0 || y1 > ctx->cfg.height || y0 >= y1) return fail(ctx, RPF_ERR_INVALID, "bad row range [%d,%d)", y0, y1);
+    if (!ctx->shards.empty()) {  // local to a pixel: every band clamps the rows it owns
+        for (size_t g = 0; g < ctx->shards.size(); ++g) {
+            const int a = std::max(y0, ctx->shard_own0[g]), b = std::min(y1, ctx->shard_own0[g + 1]);
+            if (a >= b) continue;
+            const int rc = rpf_hdr_clamp(ctx->shards[g], k_sigmas, a - ctx->shard_buf0[g], b - ctx->shard_buf0[g]);
+            if (rc != RPF_OK) { ctx->err = ctx->shards[g]->err; return rc; }
+        }
+        return RPF_OK;
+    }
+    ctx->col4_valid = false;
     CU(ctx, cudaSetDevice(ctx->cfg.device));
     const long long n = 1ll * (y1 - y0) * ctx->cfg.width;
     hdr_clamp_kernel<<<static_cast<unsigned>((n + 127) / 128), 128, 0, ctx->stream>>>(ctx->d_col[ctx->cur], ctx->S, ctx->cfg.width,
@@ -761,58 +839,88 @@ extern "C" int rpf_hdr_clamp(rpf_ctx *ctx, double k_sigmas, int y0, int y1) {
 
 extern "C" int rpf_swap_colors(rpf_ctx *ctx) {
     if (!ctx) return RPF_ERR_INVALID;
+    NOT_SHARDED(ctx, "rpf_swap_colors");
     ctx->cur ^= 1;
+    ctx->col4_valid = false;
+    return RPF_OK;
+}
+
+// The loop of rpf.cpp:767-775. seeds == nullptr: seed_all for every pass.
+static int run_filter(rpf_ctx *ctx, const int *box_sizes, const double *seeds, double seed_all, int n_iter) {
+    if (!ctx->shards.empty()) {
+        if (!ctx->uploaded) return fail(ctx, RPF_ERR_STATE, "rpf_filter: no samples uploaded");
+        for (rpf_ctx *c : ctx->shards) {
+            CU(ctx, cudaSetDevice(c->cfg.device));
+            int rc = finish_timing(c);
+            if (rc != RPF_OK) { ctx->err = c->err; return rc; }
+            CU(ctx, cudaEventRecord(c->ev0, c->stream));
+        }
+        const int rc = sharded_filter(ctx, box_sizes, seeds, seed_all, n_iter);
+        if (rc != RPF_OK) return rc;
+        for (rpf_ctx *c : ctx->shards) {
+            CU(ctx, cudaSetDevice(c->cfg.device));
+            CU(ctx, cudaEventRecord(c->ev1, c->stream));
+            c->timing_pending = true;
+        }
+        return RPF_OK;
+    }
+    CU(ctx, cudaSetDevice(ctx->cfg.device));
+    int rc = finish_timing(ctx);
+    if (rc != RPF_OK) return rc;
+    CU(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    if (ctx->band.world > 1) {
+        if ((rc = attached_filter(ctx, box_sizes, seeds, seed_all, n_iter)) != RPF_OK) return rc;
+    } else {
+        for (int i = 0; i < n_iter; ++i) {
+            rc = launch_rows(ctx, box_sizes[i], seeds ? seeds[i] : seed_all, 0, ctx->cfg.height);
+            if (rc != RPF_OK) return rc;
+            ctx->cur ^= 1;  // rpf.cpp:732
+            ctx->col4_valid = false;
+        }
+    }
+    CU(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    ctx->timing_pending = true;
     return RPF_OK;
 }
 
 extern "C" int rpf_filter(rpf_ctx *ctx, const int *box_sizes, int n_iter, double sigma_fc_seed) {
     if (!ctx || (n_iter > 0 && !box_sizes) || n_iter < 0) return fail(ctx, RPF_ERR_INVALID, "rpf_filter: bad arguments");
-    CU(ctx, cudaSetDevice(ctx->cfg.device));
-    int rc = finish_timing(ctx);
-    if (rc != RPF_OK) return rc;
-    CU(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-    for (int i = 0; i < n_iter; ++i) {
-        rc = launch_rows(ctx, box_sizes[i], sigma_fc_seed, 0, ctx->cfg.height);
-        if (rc != RPF_OK) return rc;
-        ctx->cur ^= 1;  // rpf.cpp:732
-    }
-    CU(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
-    ctx->timing_pending = true;
-    return RPF_OK;
+    return run_filter(ctx, box_sizes, nullptr, sigma_fc_seed, n_iter);
 }
 
 extern "C" int rpf_filter_sigmas(rpf_ctx *ctx, const int *box_sizes, const double *sigma_seeds, int n_iter) {
     if (!ctx || (n_iter > 0 && (!box_sizes || !sigma_seeds)) || n_iter < 0) return fail(ctx, RPF_ERR_INVALID, "rpf_filter_sigmas: bad arguments");
-    CU(ctx, cudaSetDevice(ctx->cfg.device));
-    int rc = finish_timing(ctx);
-    if (rc != RPF_OK) return rc;
-    CU(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-    for (int i = 0; i < n_iter; ++i) {
-        rc = launch_rows(ctx, box_sizes[i], sigma_seeds[i], 0, ctx->cfg.height);
-        if (rc != RPF_OK) return rc;
-        ctx->cur ^= 1;  // rpf.cpp:732
-    }
-    CU(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
-    ctx->timing_pending = true;
-    return RPF_OK;
+    return run_filter(ctx, box_sizes, sigma_seeds, 0.0, n_iter);
 }
 
 extern "C" int rpf_color_device_ptr(rpf_ctx *ctx, int which, double **out) {
     if (!ctx || !out || which < 0 || which > 1) return fail(ctx, RPF_ERR_INVALID, "rpf_color_device_ptr: bad arguments");
+    NOT_SHARDED(ctx, "rpf_color_device_ptr");
     *out = ctx->d_col[ctx->cur ^ which];
     return RPF_OK;
 }
 
 extern "C" int rpf_stream(rpf_ctx *ctx, void **out) {
     if (!ctx || !out) return RPF_ERR_INVALID;
+    NOT_SHARDED(ctx, "rpf_stream");
     *out = ctx->stream;
     return RPF_OK;
 }
 
 extern "C" int rpf_synchronize(rpf_ctx *ctx) {
     if (!ctx) return RPF_ERR_INVALID;
+    if (!ctx->shards.empty()) {
+        ctx->last_ms = 0.0;
+        for (rpf_ctx *c : ctx->shards) {
+            const int rc = rpf_synchronize(c);
+            if (rc != RPF_OK) { ctx->err = c->err; return rc; }
+            ctx->last_ms = std::max(ctx->last_ms, c->last_ms);  // the bands run side by side: the slowest one is the step
+        }
+        return RPF_OK;
+    }
     CU(ctx, cudaSetDevice(ctx->cfg.device));
     CU(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ctx->copy_stream) CU(ctx, cudaStreamSynchronize(ctx->copy_stream));
     prof_collect(ctx);
     return finish_timing(ctx);
 }
@@ -821,6 +929,7 @@ extern "C" int rpf_set_profiling(rpf_ctx *ctx, int on) {
     if (!ctx) return RPF_ERR_INVALID;
     int rc = rpf_synchronize(ctx);
     ctx->profiling = on != 0;
+    for (rpf_ctx *c : ctx->shards) c->profiling = on != 0;
     return rc;
 }
 
@@ -829,11 +938,25 @@ extern "C" int rpf_get_kernel_times(rpf_ctx *ctx, rpf_kernel_times_t *out) {
     int rc = rpf_synchronize(ctx);
     if (rc != RPF_OK) return rc;
     for (int k = 0; k < RPF_NUM_KERNELS; ++k) { out->ms[k] = ctx->k_ms[k]; out->launches[k] = ctx->k_launches[k]; }
+    for (rpf_ctx *c : ctx->shards)  // summed over the bands (device-milliseconds, not elapsed time)
+        for (int k = 0; k < RPF_NUM_KERNELS; ++k) { out->ms[k] += c->k_ms[k]; out->launches[k] += c->k_launches[k]; }
     return RPF_OK;
 }
 
 extern "C" int rpf_download_colors_f64(rpf_ctx *ctx, double *rgb) {
     if (!ctx || !rgb) return fail(ctx, RPF_ERR_INVALID, "rpf_download_colors_f64: null argument");
+    if (!ctx->shards.empty()) {  // every band returns the rows it owns
+        const size_t row = static_cast<size_t>(ctx->cfg.width) * ctx->cfg.spp, S = row * ctx->cfg.height;
+        for (size_t g = 0; g < ctx->shards.size(); ++g) {
+            rpf_ctx *c = ctx->shards[g];
+            CU(ctx, cudaSetDevice(c->cfg.device));
+            const size_t lo = static_cast<size_t>(ctx->shard_own0[g] - ctx->shard_buf0[g]) * row, n = static_cast<size_t>(ctx->shard_own0[g + 1] - ctx->shard_own0[g]) * row;
+            for (int k = 0; k < 3; ++k)
+                CU(ctx, cudaMemcpyAsync(rgb + k * S + ctx->shard_own0[g] * row, c->d_col[c->cur] + k * c->S + lo, n * sizeof(double),
+                                        cudaMemcpyDeviceToHost, c->stream));
+        }
+        return rpf_synchronize(ctx);
+    }
     CU(ctx, cudaSetDevice(ctx->cfg.device));
     CU(ctx, cudaMemcpyAsync(rgb, ctx->d_col[ctx->cur], 3 * ctx->S * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     return rpf_synchronize(ctx);
@@ -841,6 +964,24 @@ extern "C" int rpf_download_colors_f64(rpf_ctx *ctx, double *rgb) {
 
 extern "C" int rpf_download_colors(rpf_ctx *ctx, float *r, float *g, float *b) {
     if (!ctx) return RPF_ERR_INVALID;
+    if (!ctx->shards.empty()) {
+        const size_t row = static_cast<size_t>(ctx->cfg.width) * ctx->cfg.spp;
+        float *dst[3] = {r, g, b};
+        for (size_t s = 0; s < ctx->shards.size(); ++s) {
+            rpf_ctx *c = ctx->shards[s];
+            CU(ctx, cudaSetDevice(c->cfg.device));
+            float *tmp = reinterpret_cast<float *>(c->d_col[c->cur ^ 1]);
+            const size_t n3 = 3 * c->S;
+            colors_to_f32_kernel<<<static_cast<unsigned>((n3 + 255) / 256), 256, 0, c->stream>>>(c->d_col[c->cur], n3, tmp);
+            c->launches++;
+            CU(ctx, cudaGetLastError());
+            const size_t lo = static_cast<size_t>(ctx->shard_own0[s] - ctx->shard_buf0[s]) * row, n = static_cast<size_t>(ctx->shard_own0[s + 1] - ctx->shard_own0[s]) * row;
+            for (int k = 0; k < 3; ++k)
+                if (dst[k])
+                    CU(ctx, cudaMemcpyAsync(dst[k] + ctx->shard_own0[s] * row, tmp + k * c->S + lo, n * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+        }
+        return rpf_synchronize(ctx);
+    }
     CU(ctx, cudaSetDevice(ctx->cfg.device));
     // the "next" colour buffer is dead between passes: use its first 3*S floats as conversion scratch
     float *tmp = reinterpret_cast<float *>(ctx->d_col[ctx->cur ^ 1]);
@@ -857,6 +998,21 @@ extern "C" int rpf_download_colors(rpf_ctx *ctx, float *r, float *g, float *b) {
 
 extern "C" int rpf_download_debug(rpf_ctx *ctx, int *nbh, double *alpha, double *beta, double *wrc) {
     if (!ctx) return RPF_ERR_INVALID;
+    if (!ctx->shards.empty()) {
+        const size_t W = ctx->cfg.width;
+        for (size_t g = 0; g < ctx->shards.size(); ++g) {
+            rpf_ctx *c = ctx->shards[g];
+            if (!c->d_dbg_n) return fail(ctx, RPF_ERR_STATE, "rpf_download_debug: context created without cfg.debug");
+            CU(ctx, cudaSetDevice(c->cfg.device));
+            const size_t lo = static_cast<size_t>(ctx->shard_own0[g] - ctx->shard_buf0[g]) * W, go = static_cast<size_t>(ctx->shard_own0[g]) * W,
+                         n = static_cast<size_t>(ctx->shard_own0[g + 1] - ctx->shard_own0[g]) * W;
+            if (nbh) CU(ctx, cudaMemcpyAsync(nbh + go, c->d_dbg_n + lo, n * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+            if (alpha) CU(ctx, cudaMemcpyAsync(alpha + 3 * go, c->d_dbg_alpha + 3 * lo, 3 * n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+            if (beta) CU(ctx, cudaMemcpyAsync(beta + 12 * go, c->d_dbg_beta + 12 * lo, 12 * n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+            if (wrc) CU(ctx, cudaMemcpyAsync(wrc + go, c->d_dbg_wrc + lo, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+        }
+        return rpf_synchronize(ctx);
+    }
     if (!ctx->d_dbg_n) return fail(ctx, RPF_ERR_STATE, "rpf_download_debug: context created without cfg.debug");
     CU(ctx, cudaSetDevice(ctx->cfg.device));
     const size_t n = ctx->npix;
@@ -869,6 +1025,7 @@ extern "C" int rpf_download_debug(rpf_ctx *ctx, int *nbh, double *alpha, double 
 
 extern "C" int rpf_reconstruct_box(rpf_ctx *ctx, float *rgb) {
     if (!ctx || !rgb) return fail(ctx, RPF_ERR_INVALID, "rpf_reconstruct_box: null argument");
+    NOT_SHARDED(ctx, "rpf_reconstruct_box");
     CU(ctx, cudaSetDevice(ctx->cfg.device));
     float *tmp = reinterpret_cast<float *>(ctx->d_col[ctx->cur ^ 1]);
     const int n = ctx->npix * 3;
@@ -881,6 +1038,7 @@ extern "C" int rpf_reconstruct_box(rpf_ctx *ctx, float *rgb) {
 
 extern "C" int rpf_reconstruct_film(rpf_ctx *ctx, const rpf_film_desc *film, const float *ray_weight, float *rgb) {
     if (!ctx || !film || !rgb) return fail(ctx, RPF_ERR_INVALID, "rpf_reconstruct_film: null argument");
+    NOT_SHARDED(ctx, "rpf_reconstruct_film");
     if (!ctx->uploaded) return fail(ctx, RPF_ERR_STATE, "rpf_reconstruct_film: no samples uploaded");
     const long long pw = 1ll * film->pixel_x1 - film->pixel_x0, ph = 1ll * film->pixel_y1 - film->pixel_y0;
     if (pw <= 0 || ph <= 0 || pw * ph > (1ll << 30) || !(film->radius_x > 0.f) || !(film->radius_y > 0.f))
@@ -926,6 +1084,22 @@ extern "C" int rpf_get_stats(rpf_ctx *ctx, rpf_stats_t *out) {
     if (!ctx || !out) return RPF_ERR_INVALID;
     int rc = rpf_synchronize(ctx);
     if (rc != RPF_OK) return rc;
+    if (!ctx->shards.empty()) {
+        rpf_stats_t t{};
+        t.nbh_min = 0x7fffffff;
+        for (rpf_ctx *c : ctx->shards) {
+            rpf_stats_t u{};
+            if ((rc = rpf_get_stats(c, &u)) != RPF_OK) { ctx->err = c->err; return rc; }
+            t.pixels_filtered += u.pixels_filtered; t.nbh_sum += u.nbh_sum; t.nan_channels += u.nan_channels;
+            t.kernel_launches += u.kernel_launches; t.halo_bytes += u.halo_bytes;
+            if (u.pixels_filtered) { t.nbh_min = std::min(t.nbh_min, u.nbh_min); t.nbh_max = std::max(t.nbh_max, u.nbh_max); }
+            t.last_filter_ms = std::max(t.last_filter_ms, u.last_filter_ms);
+        }
+        if (!t.pixels_filtered) t.nbh_min = 0;
+        t.halo_bytes += static_cast<long long>(ctx->halo_bytes);
+        *out = t;
+        return RPF_OK;
+    }
     unsigned long long c[4];
     CU(ctx, cudaMemcpy(c, ctx->d_counters, sizeof c, cudaMemcpyDeviceToHost));
     out->pixels_filtered = ctx->pixels_filtered;
@@ -935,15 +1109,143 @@ extern "C" int rpf_get_stats(rpf_ctx *ctx, rpf_stats_t *out) {
     out->nbh_max = static_cast<int>(c[3]);
     out->kernel_launches = ctx->launches;
     out->last_filter_ms = ctx->last_ms;
+    out->halo_bytes = static_cast<long long>(ctx->halo_bytes);
     return RPF_OK;
 }
 
 extern "C" int rpf_reset_stats(rpf_ctx *ctx) {
     if (!ctx) return RPF_ERR_INVALID;
+    ctx->halo_bytes = 0;
+    if (!ctx->shards.empty()) {
+        for (rpf_ctx *c : ctx->shards) {
+            const int rc = rpf_reset_stats(c);
+            if (rc != RPF_OK) { ctx->err = c->err; return rc; }
+        }
+        return RPF_OK;
+    }
     CU(ctx, cudaSetDevice(ctx->cfg.device));
     int rc = rpf_synchronize(ctx);
     if (rc != RPF_OK) return rc;
     ctx->launches = 0;
     for (int k = 0; k < RPF_NUM_KERNELS; ++k) { ctx->k_ms[k] = 0.0; ctx->k_launches[k] = 0; }
     return reset_counters(ctx);
+}
+
+// ---- row bands: creation, attachment (rpf_bands.inl has the schedules) -------------------------------------------------
+static void band_release(rpf_ctx *ctx) {
+    if (ctx->nccl_comm) {
+        if (NcclApi *nc = nccl_api()) nc->CommDestroy(static_cast<ncclComm_t>(ctx->nccl_comm));
+        ctx->nccl_comm = nullptr;
+    }
+    if (ctx->ev_edge) cudaEventDestroy(ctx->ev_edge);
+    if (ctx->ev_copy) cudaEventDestroy(ctx->ev_copy);
+    if (ctx->ev_start) cudaEventDestroy(ctx->ev_start);
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+    ctx->ev_edge = ctx->ev_copy = ctx->ev_start = nullptr;
+    ctx->copy_stream = nullptr;
+}
+
+static int create_sharded(rpf_ctx **out, const rpf_config *cfg, int ndev) {
+    const int G = cfg->n_gpus;
+    if (G > RPF_MAX_GPUS) return fail(nullptr, RPF_ERR_INVALID, "rpf_create: n_gpus %d above RPF_MAX_GPUS", G);
+    for (int g = 0; g < G; ++g) {
+        if (cfg->device_ids[g] < 0 || cfg->device_ids[g] >= ndev)
+            return fail(nullptr, RPF_ERR_INVALID, "rpf_create: device_ids[%d] = %d, the process sees %d device(s)", g, cfg->device_ids[g], ndev);
+        for (int h = 0; h < g; ++h)
+            if (cfg->device_ids[h] == cfg->device_ids[g]) return fail(nullptr, RPF_ERR_INVALID, "rpf_create: device %d listed twice", cfg->device_ids[g]);
+    }
+    const int max_box = cfg->max_box > 0 ? cfg->max_box : 55;
+    if ((max_box & 1) == 0) return fail(nullptr, RPF_ERR_INVALID, "rpf_create: max_box must be odd");
+    rpf_ctx *par = new rpf_ctx;
+    par->cfg = *cfg;
+    par->S = 1ull * cfg->width * cfg->height * cfg->spp;
+    par->npix = cfg->width * cfg->height;
+    par->halo_rows = b_delta(max_box);
+    par->shard_own0.resize(G + 1);
+    if (band_plan(cfg->height, G, &max_box, 1, par->shard_own0.data()) != RPF_OK) {
+        delete par;
+        return fail(nullptr, RPF_ERR_INVALID, "rpf_create: %d rows cannot be split into %d bands of at least %d rows (box %d)", cfg->height, G,
+                    b_delta(max_box), max_box);
+    }
+    for (int g = 0; g < G; ++g) {
+        par->shard_buf0.push_back(std::max(0, par->shard_own0[g] - par->halo_rows));
+        par->shard_buf1.push_back(std::min(cfg->height, par->shard_own0[g + 1] + par->halo_rows));
+        rpf_config sub = *cfg;
+        sub.n_gpus = 0;
+        sub.device = cfg->device_ids[g];
+        sub.height = par->shard_buf1[g] - par->shard_buf0[g];
+        rpf_ctx *c = nullptr;
+        int rc = rpf_create(&c, &sub);
+        if (rc == RPF_OK && (rc = ensure_band_streams(c)) != RPF_OK) { g_create_err = c->err; rpf_destroy(c); }
+        if (rc != RPF_OK) {
+            for (rpf_ctx *d : par->shards) rpf_destroy(d);
+            delete par;
+            return rc;
+        }
+        c->sub.row_g0 = par->shard_buf0[g];
+        par->shards.push_back(c);
+    }
+    // halos travel with cudaMemcpyPeerAsync; with peer access they go straight over NVLink, without it through the host
+    for (int g = 0; g + 1 < G; ++g) {
+        int can = 0;
+        const int a = cfg->device_ids[g], b = cfg->device_ids[g + 1];
+        if (cudaDeviceCanAccessPeer(&can, a, b) == cudaSuccess && can) {
+            cudaSetDevice(a); cudaDeviceEnablePeerAccess(b, 0);
+            cudaSetDevice(b); cudaDeviceEnablePeerAccess(a, 0);
+            cudaGetLastError();  // "already enabled" is fine
+        }
+    }
+    *out = par;
+    return RPF_OK;
+}
+
+extern "C" int rpf_band_plan(int height, int n_bands, const int *box_sizes, int n_iter, int *own0) {
+    return band_plan(height, n_bands, box_sizes, n_iter, own0);
+}
+
+extern "C" int rpf_band_unique_id(void *out128) {
+    if (!out128) return RPF_ERR_INVALID;
+    NcclApi *nc = nccl_api();
+    if (!nc) return fail(nullptr, RPF_ERR_UNSUPPORTED, "rpf_band_unique_id: NCCL is not available (%s)", nccl_api() ? "" : "dlopen libnccl.so.2 failed");
+    ncclUniqueId id;
+    if (nc->GetUniqueId(&id) != ncclSuccess) return fail(nullptr, RPF_ERR_CUDA, "ncclGetUniqueId failed");
+    static_assert(sizeof id == 128, "ncclUniqueId is 128 bytes");
+    memcpy(out128, &id, sizeof id);
+    return RPF_OK;
+}
+
+extern "C" int rpf_band_attach(rpf_ctx *ctx, const rpf_band *band, const void *nccl_unique_id) {
+    if (!ctx || !band) return fail(ctx, RPF_ERR_INVALID, "rpf_band_attach: null argument");
+    NOT_SHARDED(ctx, "rpf_band_attach");
+    if (band->world < 1 || band->rank < 0 || band->rank >= band->world || band->own0 < band->buf0 || band->own1 <= band->own0 ||
+        band->own1 > band->buf0 + ctx->cfg.height || band->buf0 < 0 || band->buf0 + ctx->cfg.height > band->global_height)
+        return fail(ctx, RPF_ERR_INVALID, "rpf_band_attach: inconsistent band (rows [%d,%d) of a buffer holding [%d,%d), frame of %d rows)", band->own0,
+                    band->own1, band->buf0, band->buf0 + ctx->cfg.height, band->global_height);
+    band_release(ctx);
+    ctx->band = *band;
+    ctx->sub.row_g0 = band->buf0;
+    if (band->world == 1) return RPF_OK;
+    if (!nccl_unique_id) return fail(ctx, RPF_ERR_INVALID, "rpf_band_attach: null NCCL unique id");
+    NcclApi *nc = nccl_api();
+    if (!nc) { ctx->band.world = 1; return fail(ctx, RPF_ERR_UNSUPPORTED, "rpf_band_attach: NCCL is not available (dlopen libnccl.so.2 failed)"); }
+    int rc = ensure_band_streams(ctx);
+    if (rc != RPF_OK) return rc;
+    ncclUniqueId id;
+    memcpy(&id, nccl_unique_id, sizeof id);
+    ncclComm_t comm = nullptr;
+    CU(ctx, cudaSetDevice(ctx->cfg.device));
+    NC(ctx, nc->CommInitRank(&comm, band->world, id, band->rank));
+    ctx->nccl_comm = comm;
+    return RPF_OK;
+}
+
+extern "C" int rpf_host_alloc(void **out, size_t bytes) {
+    if (!out) return RPF_ERR_INVALID;
+    *out = nullptr;
+    const cudaError_t e = cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocPortable);
+    return e == cudaSuccess ? RPF_OK : fail(nullptr, RPF_ERR_CUDA, "cudaHostAlloc(%zu) failed: %s", bytes, cudaGetErrorString(e));
+}
+
+extern "C" void rpf_host_free(void *p) {
+    if (p) cudaFreeHost(p);
 }

@@ -223,7 +223,7 @@ __global__ void __launch_bounds__(KO_WARPS * 32) ordered_stats_kernel(const Gene
         const double n = static_cast<double>(N);
         const double m = __ddiv_rn(acc, n);
         double var = __dsub_rn(__ddiv_rn(sq, n), __dmul_rn(m, m));
-        if ((p.flags & FLAG_P3) && !(var > 0.0) && var == var) var = 0.0;  // P3: sqrt(max(0,var)), NaN kept
+        if ((p.flags & FLAG_P3) && !(var > 0.0)) var = 0.0;  // P3: sqrt(max(0,var)); std::max(0.0, NaN) is 0 too (ops.h:141)
         rec[REC_M + lane] = m;
         rec[REC_SD + lane] = __dsqrt_rn(var);
         rec[REC_RLO + lane] = lo;

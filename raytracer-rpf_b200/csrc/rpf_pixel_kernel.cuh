@@ -198,7 +198,7 @@ __global__ void __launch_bounds__(THREADS, 4) rpf_pixel_kernel(const FilterParam
         const double n = static_cast<double>(N);
         const double m = __ddiv_rn(ps.sumx[c], n);
         double var = __dsub_rn(__ddiv_rn(ps.sumsq[c], n), __dmul_rn(m, m));
-        if ((p.flags & FLAG_P3) && !(var > 0.0) && var == var) var = 0.0;  // P3: sqrt(max(0,var)), NaN kept
+        if ((p.flags & FLAG_P3) && !(var > 0.0)) var = 0.0;  // P3: sqrt(max(0,var)); std::max(0.0, NaN) is 0 too (ops.h:141)
         const double sd = __dsqrt_rn(var);
         ps.M[c] = m;
         ps.SD[c] = sd;

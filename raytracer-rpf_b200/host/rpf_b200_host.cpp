@@ -1,7 +1,10 @@
 // rpf_b200_host.cpp -- see rpf_b200_host.h. Host C++ only; all device work happens behind include/rpf_b200.h.
 #include "rpf_b200_host.h"
 
+#include <algorithm>
+#include <chrono>
 #include <memory>
+#include <thread>
 
 #include "rpf_b200.h"
 
@@ -11,9 +14,46 @@ namespace {
 struct CtxDeleter {
     void operator()(rpf_ctx *c) const { rpf_destroy(c); }
 };
+struct PinnedDeleter {
+    void operator()(void *p) const { rpf_host_free(p); }
+};
+template <class T>
+using Pinned = std::unique_ptr<T, PinnedDeleter>;
+
+template <class T>
+Pinned<T> pinned(size_t n, std::string *error) {
+    void *p = nullptr;
+    if (rpf_host_alloc(&p, n * sizeof(T)) != RPF_OK) {
+        if (error) *error = std::string("rpf_host_alloc: ") + rpf_last_error(nullptr);
+        return Pinned<T>();
+    }
+    return Pinned<T>(static_cast<T *>(p));
+}
+
 bool failed(std::string *error, const std::string &what, const rpf_ctx *ctx) {
     if (error) *error = what + ": " + rpf_last_error(ctx);
     return false;
+}
+
+double ms_since(std::chrono::steady_clock::time_point t0) {
+    return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+}
+
+// body(i) for i in [0, count): the caller's pool, or one std::thread per hardware thread over interleaved indices
+void parallel_for(const RPFB200Options &opt, int64_t count, const std::function<void(int64_t)> &body) {
+    if (opt.parallelFor) {
+        opt.parallelFor(body, count);
+        return;
+    }
+    const int nt = static_cast<int>(std::min<int64_t>(std::max(1u, std::thread::hardware_concurrency()), count));
+    if (nt <= 1) {
+        for (int64_t i = 0; i < count; ++i) body(i);
+        return;
+    }
+    std::vector<std::thread> pool;
+    for (int t = 0; t < nt; ++t)
+        pool.emplace_back([&, t] { for (int64_t i = t; i < count; i += nt) body(i); });
+    for (auto &th : pool) th.join();
 }
 }  // namespace
 
@@ -34,20 +74,32 @@ static bool run(SamplingFilm &film, const RPFB200Options &opt, const rpf_film_de
                 return false;
             }
     const size_t S = static_cast<size_t>(W) * H * spp;
+    if (fdesc && opt.devices.size() > 1) {
+        if (error) *error = "Film reconstruction on the device needs a single-GPU context (RPFB200Options::devices)";
+        return false;
+    }
 
     // pack: plane[c][(y*W + x)*spp + s]; SampleData::data order (sd.h:62-94). The producer writes pbrt Floats into the
-    // doubles (sd.h:62-94), so narrowing to float is exact for a fresh film.
-    std::vector<float> planes(static_cast<size_t>(RPF_NUM_CHANNELS) * S);
-    std::vector<double> colours(3 * S);
-    for (int x = 0; x < W; ++x)
-        for (int y = 0; y < H; ++y) {
+    // doubles (sd.h:62-94), so narrowing to float is exact for a fresh film. The container is samples[x][y] (x-major,
+    // sample_film.cpp:16-22); one task per image row writes contiguous runs of every plane into page-locked memory.
+    auto t0 = std::chrono::steady_clock::now();
+    Pinned<float> planes = pinned<float>(static_cast<size_t>(RPF_NUM_CHANNELS) * S, error);
+    Pinned<double> colours = pinned<double>(3 * S, error);
+    if (!planes || !colours) return false;
+    float *pl = planes.get();
+    double *co = colours.get();
+    parallel_for(opt, H, [&](int64_t y) {
+        for (int x = 0; x < W; ++x) {
             const SampleDataSet &px = film.samples[x][y];
             const size_t base = (static_cast<size_t>(y) * W + x) * spp;
             for (size_t s = 0; s < spp; ++s) {
-                for (int c = 0; c < RPF_NUM_CHANNELS; ++c) planes[c * S + base + s] = static_cast<float>(px[s].data[c]);
-                for (int k = 0; k < 3; ++k) colours[k * S + base + s] = px[s].data[2 + k];
+                const auto &d = px[s].data;
+                for (int c = 0; c < RPF_NUM_CHANNELS; ++c) pl[c * S + base + s] = static_cast<float>(d[c]);
+                for (int k = 0; k < 3; ++k) co[k * S + base + s] = d[2 + k];
             }
         }
+    });
+    const double packMs = ms_since(t0);
 
     rpf_config cfg{};
     cfg.width = W;
@@ -55,20 +107,35 @@ static bool run(SamplingFilm &film, const RPFB200Options &opt, const rpf_film_de
     cfg.spp = static_cast<int>(spp);
     cfg.device = opt.device;
     cfg.flags = opt.flags;
+    cfg.debug = opt.debugStats ? 1 : 0;
+    if (opt.devices.size() > 1) {
+        if (opt.devices.size() > RPF_MAX_GPUS) {
+            if (error) *error = "RPFB200Options::devices lists more than RPF_MAX_GPUS devices";
+            return false;
+        }
+        cfg.n_gpus = static_cast<int>(opt.devices.size());
+        for (size_t g = 0; g < opt.devices.size(); ++g) cfg.device_ids[g] = opt.devices[g];
+        cfg.max_box = opt.boxSizes.empty() ? 0 : *std::max_element(opt.boxSizes.begin(), opt.boxSizes.end());
+    } else if (opt.devices.size() == 1)
+        cfg.device = opt.devices[0];
     rpf_ctx *raw = nullptr;
     if (rpf_create(&raw, &cfg) != RPF_OK) return failed(error, "rpf_create", nullptr);
     std::unique_ptr<rpf_ctx, CtxDeleter> ctx(raw);
 
     if (opt.keepProbability < 1.0 && rpf_set_subsampling(ctx.get(), opt.keepProbability, opt.rngSeed, 0) != RPF_OK)
         return failed(error, "rpf_set_subsampling", ctx.get());
+    t0 = std::chrono::steady_clock::now();
     const float *ptrs[RPF_NUM_CHANNELS];
-    for (int c = 0; c < RPF_NUM_CHANNELS; ++c) ptrs[c] = planes.data() + c * S;
+    for (int c = 0; c < RPF_NUM_CHANNELS; ++c) ptrs[c] = pl + c * S;
     if (rpf_upload(ctx.get(), ptrs) != RPF_OK) return failed(error, "rpf_upload", ctx.get());
     // colours re-entering the filter after an earlier pass are doubles (sd.h:205-207): keep every bit
-    if (rpf_upload_colors_f64(ctx.get(), colours.data()) != RPF_OK) return failed(error, "rpf_upload_colors_f64", ctx.get());
+    if (rpf_upload_colors_f64(ctx.get(), co) != RPF_OK) return failed(error, "rpf_upload_colors_f64", ctx.get());
+    if (rpf_synchronize(ctx.get()) != RPF_OK) return failed(error, "rpf_synchronize", ctx.get());
+    const double uploadMs = ms_since(t0);
     if ((opt.paper.w_epsilon != 0.0 || opt.paper.min_sigma != 0.0 || opt.paper.world_pos_sigmas != 0.0) &&
         rpf_set_paper_mode(ctx.get(), &opt.paper) != RPF_OK)
         return failed(error, "rpf_set_paper_mode", ctx.get());
+    t0 = std::chrono::steady_clock::now();
     if (!opt.sigmaSeeds.empty()) {
         if (opt.sigmaSeeds.size() != opt.boxSizes.size()) {
             if (error) *error = "RPFB200Options: sigmaSeeds must hold one value per box size";
@@ -80,33 +147,52 @@ static bool run(SamplingFilm &film, const RPFB200Options &opt, const rpf_film_de
         return failed(error, "rpf_filter", ctx.get());
     if (opt.hdrClampSigmas > 0.0 && rpf_hdr_clamp(ctx.get(), opt.hdrClampSigmas, 0, 0) != RPF_OK)
         return failed(error, "rpf_hdr_clamp", ctx.get());
-    if (rpf_download_colors_f64(ctx.get(), colours.data()) != RPF_OK) return failed(error, "rpf_download_colors_f64", ctx.get());
+    if (rpf_synchronize(ctx.get()) != RPF_OK) return failed(error, "rpf_synchronize", ctx.get());
+    const double filterWallMs = ms_since(t0);
+    t0 = std::chrono::steady_clock::now();
+    if (rpf_download_colors_f64(ctx.get(), co) != RPF_OK) return failed(error, "rpf_download_colors_f64", ctx.get());
+    const double downloadMs = ms_since(t0);
     rpf_stats_t st{};
     if (rpf_get_stats(ctx.get(), &st) != RPF_OK) return failed(error, "rpf_get_stats", ctx.get());
+    std::vector<int> nbh;
+    if (opt.debugStats && report) {
+        nbh.resize(static_cast<size_t>(W) * H);
+        if (rpf_download_debug(ctx.get(), nbh.data(), nullptr, nullptr, nullptr) != RPF_OK) return failed(error, "rpf_download_debug", ctx.get());
+    }
     if (fdesc && rgb) {  // rpf.cpp:776-804 on the device, samples still resident
-        std::vector<float> rayWeight(S);
-        for (int x = 0; x < W; ++x)
-            for (int y = 0; y < H; ++y)
-                for (size_t s = 0; s < spp; ++s) rayWeight[(static_cast<size_t>(y) * W + x) * spp + s] = film.samples[x][y][s].rayWeight;
+        Pinned<float> rayWeight = pinned<float>(S, error);
+        if (!rayWeight) return false;
+        float *rw = rayWeight.get();
+        parallel_for(opt, H, [&](int64_t y) {
+            for (int x = 0; x < W; ++x)
+                for (size_t s = 0; s < spp; ++s) rw[(static_cast<size_t>(y) * W + x) * spp + s] = film.samples[x][y][s].rayWeight;
+        });
         rgb->resize(3 * static_cast<size_t>(fdesc->pixel_x1 - fdesc->pixel_x0) * (fdesc->pixel_y1 - fdesc->pixel_y0));
-        if (rpf_reconstruct_film(ctx.get(), fdesc, rayWeight.data(), rgb->data()) != RPF_OK)
+        if (rpf_reconstruct_film(ctx.get(), fdesc, rw, rgb->data()) != RPF_OK)
             return failed(error, "rpf_reconstruct_film", ctx.get());
     }
 
     // rpf.cpp:715,732: only the three colour slots change
-    for (int x = 0; x < W; ++x)
+    t0 = std::chrono::steady_clock::now();
+    parallel_for(opt, W, [&](int64_t x) {
         for (int y = 0; y < H; ++y) {
             SampleDataSet &px = film.samples[x][y];
             const size_t base = (static_cast<size_t>(y) * W + x) * spp;
             for (size_t s = 0; s < spp; ++s)
-                for (int k = 0; k < 3; ++k) px[s].data[2 + k] = colours[k * S + base + s];
+                for (int k = 0; k < 3; ++k) px[s].data[2 + k] = co[k * S + base + s];
         }
+    });
+    const double unpackMs = ms_since(t0);
     if (report) {
         report->nanChannels = st.nan_channels;
         report->meanNeighbourhood = st.pixels_filtered ? static_cast<double>(st.nbh_sum) / st.pixels_filtered : 0.0;
         report->minNeighbourhood = st.nbh_min;
         report->maxNeighbourhood = st.nbh_max;
         report->filterMs = st.last_filter_ms;
+        report->packMs = packMs; report->uploadMs = uploadMs; report->filterWallMs = filterWallMs;
+        report->downloadMs = downloadMs; report->unpackMs = unpackMs;
+        report->gpus = opt.devices.size() > 1 ? static_cast<int>(opt.devices.size()) : 1;
+        report->neighbourhood.swap(nbh);
     }
     return true;
 }

@@ -8,6 +8,8 @@
 #ifndef RPF_B200_HOST_H
 #define RPF_B200_HOST_H
 
+#include <cstdint>
+#include <functional>
 #include <string>
 #include <vector>
 
@@ -19,7 +21,12 @@ namespace pbrt {
 struct RPFB200Options {
     std::vector<int> boxSizes{7};  // rpf.cpp:767 ships {7}; the comment there lists {55, 35, 17, 7}
     double sigmaSeed = 0.002;      // rpf.cpp:533
-    int device = 0;                // CUDA device ordinal
+    int device = 0;                // CUDA device ordinal (one GPU)
+    std::vector<int> devices;      // two or more ordinals: one row band per device inside this process (rpf_config.n_gpus)
+    bool debugStats = false;       // keep the per-pixel neighbourhood sizes of the last pass (RPFB200Report::neighbourhood)
+    // Runs body(i) for i in [0, count) on the caller's thread pool -- the integrator passes pbrt's ParallelFor
+    // (core/parallel.h:101), the pool FillSampleFilm used (rpf.cpp:235). Empty: a std::thread per hardware thread.
+    std::function<void(const std::function<void(int64_t)> &, int64_t)> parallelFor;
     int flags = 0;                 // RPF_FLAG_* of include/rpf_b200.h; 0 = REF_DEFINED
     double keepProbability = 1.0;  // < 1: random neighbour subsampling (rpf_set_subsampling; not the reference's semantics)
     unsigned long long rngSeed = 0;
@@ -34,6 +41,11 @@ struct RPFB200Report {
     double meanNeighbourhood = 0;    // "RPF/Neighborhood Size" (rpf.cpp:588)
     int minNeighbourhood = 0, maxNeighbourhood = 0;
     double filterMs = 0;             // device time of all passes
+    // host wall-clock milliseconds around the device work: SamplingFilm -> pinned structure-of-arrays planes, the uploads,
+    // the passes (filter call to completion), the download, planes -> SamplingFilm
+    double packMs = 0, uploadMs = 0, filterWallMs = 0, downloadMs = 0, unpackMs = 0;
+    int gpus = 1;
+    std::vector<int> neighbourhood;  // per pixel, index y*W+x, last pass (only with RPFB200Options::debugStats)
 };
 
 // Returns true on success. On failure nothing in samplingFilm is modified and *error holds the reason

@@ -27,6 +27,7 @@ ABI_SYMBOLS = [
     "rpf_synth_planes", "rpf_reconstruct_film", "rpf_film_filter_table",
     "rpf_buffer_write", "rpf_buffer_info_read", "rpf_buffer_read", "rpf_set_subsampling",
     "rpf_set_paper_mode", "rpf_filter_sigmas", "rpf_hdr_clamp", "rpf_fused_max_candidates",
+    "rpf_band_plan", "rpf_band_unique_id", "rpf_band_attach", "rpf_host_alloc", "rpf_host_free",
 ]
 
 
@@ -36,13 +37,19 @@ class RPFError(RuntimeError):
 
 class Config(C.Structure):
     _fields_ = [("width", C.c_int), ("height", C.c_int), ("spp", C.c_int), ("device", C.c_int),
-                ("flags", C.c_int), ("debug", C.c_int)]
+                ("flags", C.c_int), ("debug", C.c_int), ("n_gpus", C.c_int), ("device_ids", C.c_int * 8), ("max_box", C.c_int)]
 
 
 class Stats(C.Structure):
     _fields_ = [("pixels_filtered", C.c_longlong), ("nbh_sum", C.c_longlong), ("nbh_min", C.c_int),
                 ("nbh_max", C.c_int), ("nan_channels", C.c_longlong), ("kernel_launches", C.c_longlong),
-                ("last_filter_ms", C.c_double)]
+                ("last_filter_ms", C.c_double), ("halo_bytes", C.c_longlong)]
+
+
+class Band(C.Structure):
+    """rpf_band: this context is one row band of a larger frame, held by one process of `world`."""
+    _fields_ = [("global_height", C.c_int), ("buf0", C.c_int), ("own0", C.c_int), ("own1", C.c_int), ("rank", C.c_int),
+                ("world", C.c_int)]
 
 
 class PaperOpts(C.Structure):
@@ -142,12 +149,36 @@ def lib():
         L.rpf_get_kernel_times.argtypes = [vp, C.POINTER(KernelTimes)]
         L.rpf_max_neighbourhood.argtypes = []
         L.rpf_synth_planes.argtypes = [i, i, i, C.c_ulonglong, i, i, i, vp]
+        L.rpf_band_plan.argtypes = [i, i, vp, i, vp]
+        L.rpf_band_unique_id.argtypes = [vp]
+        L.rpf_band_attach.argtypes = [vp, C.POINTER(Band), vp]
+        L.rpf_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
+        L.rpf_host_free.argtypes = [vp]
+        L.rpf_host_free.restype = None
         _lib = L
     return _lib
 
 
 def _p(a):
     return a.ctypes.data_as(C.c_void_p)
+
+
+def band_plan(height, n_bands, box_sizes):
+    """rpf_band_plan: first owned row of each of n_bands equal-work row bands, [n_bands + 1] ints (host only)."""
+    bx = np.asarray(box_sizes, np.int32)
+    out = np.zeros(n_bands + 1, np.int32)
+    rc = lib().rpf_band_plan(height, n_bands, _p(bx), len(bx), _p(out))
+    if rc != 0:
+        raise RPFError(f"rpf_band_plan({height} rows, {n_bands} bands, boxes {list(box_sizes)}) failed ({rc})")
+    return [int(v) for v in out]
+
+
+def nccl_unique_id():
+    buf = (C.c_char * 128)()
+    rc = lib().rpf_band_unique_id(buf)
+    if rc != 0:
+        raise RPFError(f"rpf_band_unique_id failed ({rc}): {lib().rpf_last_error(None).decode()}")
+    return bytes(buf)
 
 
 def synth_planes(width, height, spp, seed=1234, kind=0, x_off=0, y_off=0, out=None):
@@ -163,7 +194,9 @@ def synth_planes(width, height, spp, seed=1234, kind=0, x_off=0, y_off=0, out=No
 class RPFFilter:
     """One device context = one SamplingFilm (reference src/custom/sample_film.h:28-45) resident in HBM."""
 
-    def __init__(self, width, height, spp, device=0, flags=FLAGS_DEFINED, debug=False, force_general=False, force_large=False):
+    def __init__(self, width, height, spp, device=0, flags=FLAGS_DEFINED, debug=False, force_general=False, force_large=False,
+                 devices=None, max_box=0):
+        """devices: list of CUDA ordinals -> one process, one row band per device (rpf_config.n_gpus / device_ids)."""
         if force_general:
             flags |= FLAG_FORCE_GENERAL
         if force_large:
@@ -171,7 +204,9 @@ class RPFFilter:
         self.W, self.H, self.P = width, height, spp
         self.S = width * height * spp
         self._h = C.c_void_p()
-        cfg = Config(width, height, spp, device, flags, 1 if debug else 0)
+        devs = list(devices) if devices else []
+        cfg = Config(width, height, spp, device, flags, 1 if debug else 0, len(devs) if len(devs) > 1 else 0,
+                     (C.c_int * 8)(*(devs + [0] * (8 - len(devs)))), max_box)
         rc = lib().rpf_create(C.byref(self._h), C.byref(cfg))
         if rc != 0:
             raise RPFError(f"rpf_create failed ({rc}): {lib().rpf_last_error(None).decode()}")
@@ -268,6 +303,12 @@ class RPFFilter:
     def set_subsampling(self, keep_probability, rng_seed=0, global_row0=0):
         """Random neighbour subsampling (include/rpf_subsample.h); keep_probability >= 1 switches it off."""
         self._check(lib().rpf_set_subsampling(self._h, C.c_double(keep_probability), C.c_ulonglong(rng_seed), global_row0))
+
+    def attach_band(self, global_height, buf0, own0, own1, rank, world, nccl_unique_id=None):
+        """One band per process (rpf_band_attach): apply() then runs the band schedule with NCCL halo exchange."""
+        b = Band(global_height, buf0, own0, own1, rank, world)
+        uid = None if nccl_unique_id is None else (C.c_char * 128).from_buffer_copy(bytes(nccl_unique_id))
+        self._check(lib().rpf_band_attach(self._h, C.byref(b), uid))
 
     def swap_colors(self):
         self._check(lib().rpf_swap_colors(self._h))
