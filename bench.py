@@ -1,14 +1,22 @@
 #!/usr/bin/env python
-"""bench.py -- RPF filter throughput on B200 (metric of BASELINE.json: Msamples/s, % of HBM roofline).
+"""bench.py -- RPF filter throughput on B200 (metric of BASELINE.json: Msamples/s, % of HBM roofline, relMSE vs ref).
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
   N>1: python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
-A step is one rpf_filter pass schedule (all configured box sizes) over one synthetic frame. The default workload is
-BASELINE.json configs[1]: 1280x720, 8 spp, four RPF iterations with the box sizes 55/35/17/7 of north_star (the
-reference ships {7} and keeps {55,35,17,7} in a comment, rpf.cpp:767; `--boxes 7` times the shipped schedule).
-Row bands are sharded across ranks with halo exchange of the filtered colours between passes (NCCL point-to-point);
-total work is fixed as N grows ("strong" scaling of one frame). Prints ONE JSON line on rank 0.
+A step is one rpf_filter pass schedule (all configured box sizes) over one frame whose planes are resident in HBM. The
+default workload is BASELINE.json configs[2], north_star's target: a synthetic feature buffer of 1920x1080, 8 spp, four
+RPF iterations with the box sizes 55/35/17/7 (the reference ships {7} and keeps {55,35,17,7} in a comment, rpf.cpp:767;
+`--boxes 7` times the shipped schedule, `--config sample720` is configs[1], `--buffer file.rpfb` filters a rendered
+feature buffer). With N ranks the frame is cut into N equal-work row bands (rpf_band_plan); the halo exchange of the
+filtered colours between passes runs inside the library (rpf_band_attach: ncclSend / ncclRecv on a copy stream while
+the interior rows are filtered). Total work is fixed as N grows ("strong" scaling of one frame).
+
+Printed on rank 0, ONE JSON line. Besides the contract's keys:
+  parity    the GPU result of the timed configuration against the CPU oracle on a 24x24-pixel window (straddling a band
+            boundary when N > 1): per-pixel max abs error and relMSE of the per-pixel mean image, per-sample max abs, N exact
+  checksum  64-bit sum of the bit patterns of all owned output colours: identical for every N (the path is bit-deterministic)
+  ranks     min / max / sum over ranks of the step time and of every kernel's time
 """
 import argparse
 import json
@@ -26,6 +34,8 @@ sys.path.insert(0, os.path.join(ROOT, "raytracer-rpf_b200"))
 METRIC = "rpf_filter_msamples_per_s"
 UNIT = "Msamples/s"
 ALG_BYTES_PER_SAMPLE_ITER = 88  # 19 fp32 channels read + 3 fp32 colours written
+CONFIGS = {"sample720": (1280, 720, 8), "fullhd": (1920, 1080, 8), "4k16": (3840, 2160, 16), "stress64": (1920, 1080, 64)}
+WINDOW = 24  # parity window, pixels
 
 
 def parse():
@@ -34,41 +44,62 @@ def parse():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--width", type=int, default=1280)
-    ap.add_argument("--height", type=int, default=720)
-    ap.add_argument("--spp", type=int, default=8)
+    ap.add_argument("--width", type=int, default=None)
+    ap.add_argument("--height", type=int, default=None)
+    ap.add_argument("--spp", type=int, default=None)
     ap.add_argument("--boxes", default=os.environ.get("RPF_BENCH_BOXES", "55,35,17,7"))
     ap.add_argument("--seed", type=float, default=0.002, help="sigma_fc_seed, reference literal rpf.cpp:533")
-    ap.add_argument("--config", default=None, choices=["sample720", "fullhd", "4k16", "stress64"],
-                    help="BASELINE.json configs[1..4]: 1280x720x8 (default), 1920x1080x8, 3840x2160x16, 1920x1080x64")
+    ap.add_argument("--config", default="fullhd", choices=sorted(CONFIGS),
+                    help="BASELINE.json configs[1..4]: sample720 = 1280x720x8, fullhd = 1920x1080x8 (default, north_star's "
+                         "target), 4k16 = 3840x2160x16, stress64 = 1920x1080x64")
+    ap.add_argument("--buffer", default=None, help="filter this feature-buffer file (.rpfb, rpf_buffer_write) instead of a synthetic frame")
     ap.add_argument("--subsample", type=float, default=1.0,
                     help="optional neighbour subsampling (keep probability; 1 = off = the reference's semantics and the default)")
+    ap.add_argument("--band", default=None, help="RANK/WORLD: run that one band of the sharded frame alone on one GPU, no exchange "
+                                                 "(for ncu captures of a band-shaped launch; not a benchmark)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    return ap.parse_args()
+    ap.add_argument("--no-parity", action="store_true")
+    a = ap.parse_args()
+    w, h, p = CONFIGS[a.config]
+    a.width, a.height, a.spp = a.width or w, a.height or h, a.spp or p
+    return a
 
 
-CONFIGS = {"sample720": (1280, 720, 8), "fullhd": (1920, 1080, 8), "4k16": (3840, 2160, 16), "stress64": (1920, 1080, 64)}
+def workload_of(args, boxes):
+    if args.buffer:
+        return f"rendered feature buffer {os.path.basename(args.buffer)} {args.width}x{args.height} {args.spp} spp, boxes {boxes}, sigma seed {args.seed}"
+    w = f"synthetic all-noisy feature buffer {args.width}x{args.height} {args.spp} spp, boxes {boxes}, sigma seed {args.seed}"
+    if args.subsample < 1.0:
+        w += f", neighbour subsampling keep {args.subsample} (NOT the reference's semantics)"
+    return w
 
 
-def measured_traffic(kernel, workload_key):
-    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture (profiles/r1/traffic.json,
-    written by tools/traffic_from_ncu.py): dram__bytes_read.sum + dram__bytes_write.sum, averaged over the launches of
-    one step. None when no capture exists for this workload."""
-    try:
-        with open(os.path.join(ROOT, "profiles", "r1", "traffic.json")) as f:
-            t = json.load(f)
-        return t[workload_key][kernel]["dram_bytes_per_launch"]
-    except Exception:
-        return None
+def config_of(args, boxes):
+    """The same dict in both arms (`--impl ours` and `--impl reference`)."""
+    return {"workload": workload_of(args, boxes),
+            "l2": f"inputs ({19 * 4 * args.width * args.height * args.spp / 1e9:.2f} GB of planes per frame) exceed the 126 MB L2; no flush needed"}
+
+
+def measured_traffic(kernel, key):
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture (profiles/r2/traffic.json,
+    written by tools/traffic_from_ncu.py): dram__bytes_read.sum + dram__bytes_write.sum averaged over its launches of one
+    step. None when no capture exists for this workload / band shape."""
+    for rnd in ("r2", "r1"):
+        try:
+            with open(os.path.join(ROOT, "profiles", rnd, "traffic.json")) as f:
+                return json.load(f)[key][kernel]["dram_bytes_per_launch"]
+        except Exception:
+            continue
+    return None
 
 
 def peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-            return float(json.load(f)["hbm_gbs"]), "measured"
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json, burst copy)"
     except Exception:
-        return 6650.0, "fallback"
+        return 6650.0, "fallback (B200_PROFILING.md)"
 
 
 class ClockSampler(threading.Thread):
@@ -99,75 +130,173 @@ class ClockSampler(threading.Thread):
                 "reasons": reasons, "samples": len(sm)}
 
 
-def crop_for_cpu(boxes, cores, W, H):
-    """Bounded CPU sample: a centre crop filtered as a frame of its own (about 10-30 s on 8-16 cores, measured:
-    80x80 with boxes 55/35/17/7 = 27 s on 8 cores, 256x256 with box 7 = 2.7 s on 16). Pixels near the crop's edge see
-    truncated boxes, as the border pixels of the full frame do, so the CPU figure is mildly optimistic."""
-    side = 80 if max(boxes) >= 17 else 256
-    return min(side, W), min(side, H)
+def checksum64(a):
+    """Sum of the 64-bit patterns of a float64 array, modulo 2^64."""
+    return int(np.ascontiguousarray(a).view(np.uint64).sum(dtype=np.uint64))
 
 
-def cpu_reference_run(args, boxes, steps, warmup):
-    """Times the reference's own filter code (oracle/_ref REF_DEFINED build of rpf.cpp:497-733 + mi.cpp), or the oracle
-    port when that library is absent, on a bounded crop of the workload with all host cores."""
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
-    import ctypes as C
-    import oracle_bind as ob
+def load_buffer(path):
     import rpf_b200
+    planes, _, info = rpf_b200.read_buffer(path)
+    return planes, info["width"], info["height"], info["spp"]
+
+
+class Frame:
+    """Where the samples come from: the counter-based synthetic generator (any sub-rectangle on its own) or a file."""
+
+    def __init__(self, args):
+        import rpf_b200
+        self.rpf = rpf_b200
+        self.file_planes = None
+        if args.buffer:
+            pl, w, h, p = load_buffer(args.buffer)
+            args.width, args.height, args.spp = w, h, p
+            self.file_planes = pl.reshape(19, h, w, p)
+        self.W, self.H, self.P = args.width, args.height, args.spp
+
+    def rect(self, x0, y0, w, h, out=None):
+        """float32 [19, w*h*P]: the pixels [x0,x0+w) x [y0,y0+h) of the frame as a frame of their own."""
+        if self.file_planes is not None:
+            a = np.ascontiguousarray(self.file_planes[:, y0:y0 + h, x0:x0 + w, :]).reshape(19, -1)
+            if out is not None:
+                out[...] = a
+                return out
+            return a
+        return self.rpf.synth_planes(w, h, self.P, seed=1234, kind=0, x_off=x0, y_off=y0, out=out)
+
+
+def oracle_window(frame, boxes, seed, wx0, wy0, ww, wh):
+    """The CPU oracle's result on the window [wx0,wx0+ww) x [wy0,wy0+wh) of the frame after all passes. The filter is local
+    (a pixel after the passes depends on samples within sum b_delta pixels), so the oracle works on a crop around the
+    window, clipped at the frame, and each pass only filters the pixels later passes can still reach.
+    -> (colours [3, wh, ww, P] float64, N of the last pass [wh, ww])"""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_bind as ob
+    deltas = [(b - 1) // 2 for b in boxes]
+    halo = sum(deltas)
+    cx0, cy0 = max(0, wx0 - halo), max(0, wy0 - halo)
+    cx1, cy1 = min(frame.W, wx0 + ww + halo), min(frame.H, wy0 + wh + halo)
+    cw, ch = cx1 - cx0, cy1 - cy0
+    crop = frame.rect(cx0, cy0, cw, ch)
+    col = crop[2:5].astype(np.float64)
+    out = None
+    for i, b in enumerate(boxes):
+        r = sum(deltas[i + 1:])  # what the later passes still reach
+        rows = (max(0, wy0 - r - cy0), min(ch, wy0 + wh + r - cy0))
+        cols = (max(0, wx0 - r - cx0), min(cw, wx0 + ww + r - cx0))
+        out = ob.oracle_filter(crop, cw, ch, frame.P, [b], seed=seed, colors=col, rows=rows, cols=cols, debug=True)
+        col = out["colors"]
+    c = col.reshape(3, ch, cw, frame.P)[:, wy0 - cy0:wy0 - cy0 + wh, wx0 - cx0:wx0 - cx0 + ww]
+    n = out["N"].reshape(ch, cw)[wy0 - cy0:wy0 - cy0 + wh, wx0 - cx0:wx0 - cx0 + ww]
+    return c, n
+
+
+def parity_report(gpu_c, gpu_n, ora_c, ora_n, window, straddles):
+    """BASELINE.json / north_star bars: per-pixel max abs error <= 1e-3 and image relMSE <= 1e-5 in linear RGB, on the
+    per-pixel mean of the filtered sample colours (what the box-filter Film produces)."""
+    nan_equal = bool(np.array_equal(np.isnan(gpu_c), np.isnan(ora_c)))
+    gi, oi = np.nan_to_num(gpu_c).mean(axis=3), np.nan_to_num(ora_c).mean(axis=3)
+    m = ~np.isnan(ora_c) & ~np.isnan(gpu_c)
+    return {"vs": "oracle", "window": list(window), "straddles_band_boundary": bool(straddles),
+            "max_abs": float(np.abs(gi - oi).max()), "relmse": float(np.mean((gi - oi) ** 2 / (oi ** 2 + 1e-2))),
+            "max_abs_sample": float(np.abs(gpu_c[m] - ora_c[m]).max(initial=0.0)), "nan_pattern_equal": nan_equal,
+            "n_exact": bool(np.array_equal(gpu_n, ora_n)), "tolerance": {"max_abs": 1e-3, "relmse": 1e-5},
+            "pass": bool(nan_equal and np.abs(gi - oi).max() <= 1e-3 and np.mean((gi - oi) ** 2 / (oi ** 2 + 1e-2)) <= 1e-5
+                         and np.array_equal(gpu_n, ora_n))}
+
+
+def box_fill(side, box):
+    """Mean fraction of a box x box neighbourhood that lies inside a side x side frame (1 = no pixel sees a cut box);
+    the square of the one-dimensional fraction, so sqrt(fill(w)) * sqrt(fill(h)) is the fill of a w x h frame."""
+    d = (box - 1) // 2
+    y = np.arange(side)
+    rows = np.minimum(side - 1, y + d) - np.maximum(0, y - d) + 1
+    return float((rows.mean() / box) ** 2)
+
+
+def cpu_reference_run(args, frame, boxes, steps, warmup):
+    """Times the reference's own filter code (oracle/_ref REF_DEFINED build of rpf.cpp:497-733 + mi.cpp), or the oracle
+    port when that library is absent, with all host cores on a bounded sample: a centre crop of the workload, filtered as
+    a frame of its own, large enough that every core has at least four 16x16 tiles (the reference's unit of parallelism,
+    rpf.cpp:542). Pixels near the crop's edge see cut boxes; the per-box fill factors and the figure corrected to the
+    full frame's fill are reported next to the measured one (work per pixel ~ candidates per pixel)."""
+    import ctypes as C
     cores = os.cpu_count() or 1
-    cw, ch = crop_for_cpu(boxes, cores, args.width, args.height)
-    planes = rpf_b200.synth_planes(cw, ch, args.spp, seed=1234, kind=0, x_off=(args.width - cw) // 2,
-                                   y_off=(args.height - ch) // 2)
-    S = cw * ch * args.spp
+    tiles = 4 * cores
+    side = 16 * int(np.ceil(np.sqrt(tiles)))
+    cw, ch = min(side, frame.W), min(side, frame.H)
+    planes = frame.rect((frame.W - cw) // 2, (frame.H - ch) // 2, cw, ch)
+    S = cw * ch * frame.P
     path = os.path.join(ROOT, "oracle", "_ref", "libref_rpf_defined.so")
     kind = "reference" if os.path.exists(path) else "port"
+    per_box = {b: 0.0 for b in boxes}
     if kind == "reference":
         lib = C.CDLL(path)
         lib.ref_apply_rpf_filter.argtypes = [C.c_int] * 3 + [C.c_void_p] * 2 + [C.c_int] * 2 + [C.c_double]
 
-        def run():
+        def run(record):
             col = planes[2:5].astype(np.float64)
             for b in boxes:
-                lib.ref_apply_rpf_filter(cw, ch, args.spp, planes.ctypes.data, col.ctypes.data, b, cores, args.seed)
+                t = time.perf_counter()
+                lib.ref_apply_rpf_filter(cw, ch, frame.P, planes.ctypes.data, col.ctypes.data, b, cores, args.seed)
+                if record:
+                    per_box[b] += time.perf_counter() - t
     else:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import oracle_bind as ob
         ob.build_oracle()
 
-        def run():
-            ob.oracle_filter(planes, cw, ch, args.spp, boxes, seed=args.seed, threads=cores)
+        def run(record):
+            col = planes[2:5].astype(np.float64)
+            for b in boxes:
+                t = time.perf_counter()
+                col = ob.oracle_filter(planes, cw, ch, frame.P, [b], seed=args.seed, colors=col, threads=cores)["colors"]
+                if record:
+                    per_box[b] += time.perf_counter() - t
     for _ in range(warmup):
-        run()
+        run(False)
     t0 = time.perf_counter()
     for _ in range(steps):
-        run()
+        run(True)
     dt = (time.perf_counter() - t0) / steps
+    fill = {b: (float((np.sqrt(box_fill(cw, b)) * np.sqrt(box_fill(ch, b)))),
+                float((np.sqrt(box_fill(frame.W, b)) * np.sqrt(box_fill(frame.H, b))))) for b in boxes}
+    dt_full = sum(per_box[b] / steps * fill[b][1] / fill[b][0] for b in boxes)
     return {"value": S / dt / 1e6, "unit": UNIT, "cores": cores, "kind": kind,
-            "sample": f"{cw}x{ch} px centre crop of the {args.width}x{args.height}x{args.spp}spp frame, boxes {boxes}, "
-                      f"{dt:.2f} s per pass schedule"}, dt
+            "sample": f"{cw}x{ch} px centre crop ({(cw // 16) * (ch // 16)} tiles of 16x16 for {cores} cores) of the "
+                      f"{frame.W}x{frame.H}x{frame.P}spp frame filtered as a frame of its own, boxes {boxes}, {dt:.2f} s per pass schedule",
+            "per_box_s": {str(b): per_box[b] / steps for b in boxes},
+            "box_fill_crop_vs_frame": {str(b): [round(fill[b][0], 4), round(fill[b][1], 4)] for b in boxes},
+            "extrapolated_full_frame_value": S / dt_full / 1e6 if dt_full > 0 else None,
+            "extrapolation": "per box: measured seconds x (fill of the full frame / fill of the crop), fill = mean in-frame fraction "
+                             "of the box; `value` is the measured figure, uncorrected"}, dt
+
+
+def reference_arm(args, boxes, rank):
+    if rank != 0:
+        return
+    frame = Frame(args)
+    base, dt = cpu_reference_run(args, frame, boxes, max(1, args.steps), min(args.warmup, 1))
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "rendered" if args.buffer else "synthetic",
+        "config": config_of(args, boxes), "cpu_baseline": base,
+        "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+def spread(vals):
+    return {"min": float(min(vals)), "max": float(max(vals)), "sum": float(sum(vals))}
 
 
 def main():
     args = parse()
-    if args.config:
-        args.width, args.height, args.spp = CONFIGS[args.config]
     boxes = [int(b) for b in args.boxes.split(",")]
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    workload = f"synthetic all-noisy feature buffer {args.width}x{args.height} {args.spp} spp, boxes {boxes}, sigma seed {args.seed}"
-    if args.subsample < 1.0:
-        workload += f", neighbour subsampling keep {args.subsample} (NOT the reference's semantics)"
-
     if args.impl == "reference":
-        if rank != 0:
-            return
-        base, dt = cpu_reference_run(args, boxes, max(1, args.steps), min(args.warmup, 1))
-        print(json.dumps({
-            "impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload}, "cpu_baseline": base,
-            "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
-        return
+        return reference_arm(args, boxes, rank)
 
     # The contract is ONE JSON line on stdout. Libraries write there too (NCCL prints its version banner on fd 1), so the
     # real stdout is kept aside for the result and fd 1 points at stderr for everything else.
@@ -184,23 +313,38 @@ def main():
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     torch.cuda.set_device(local_rank)
-    W, H, P = args.width, args.height, args.spp
-    band = bands.make_band(rank, world, H, boxes)
+    frame = Frame(args)
+    W, H, P = frame.W, frame.H, frame.P
+    emulate = None
+    if args.band:  # one band of a sharded frame alone on this GPU (ncu captures): no neighbours, no exchange
+        er, ew = (int(v) for v in args.band.split("/"))
+        emulate = bands.make_band(er, ew, H, boxes)
+    band = emulate or bands.make_band(rank, world, H, boxes)
     lh = band.local_height
     S_loc = W * lh * P
-    row = W * P
     host = torch.empty((19, S_loc), dtype=torch.float32, pin_memory=True)
     planes = host.numpy()
-    rpf_b200.synth_planes(W, lh, P, seed=1234, kind=0, x_off=0, y_off=band.buf0, out=planes)
+    frame.rect(0, band.buf0, W, lh, out=planes)
     out_host = torch.empty((3, S_loc), dtype=torch.float32, pin_memory=True)
-    ctx = rpf_b200.RPFFilter(W, lh, P, device=local_rank)
+    ctx = rpf_b200.RPFFilter(W, lh, P, device=local_rank, debug=True)
+    if emulate is None:
+        bands.attach(ctx, band, dist)  # rpf_band_attach: the library exchanges the halos itself (NCCL) from here on
+    else:
+        ctx.attach_band(H, band.buf0, band.buf0, band.buf1, 0, 1)  # global rows for the RNG; every held row "owned" below
     if args.subsample < 1.0:
         ctx.set_subsampling(args.subsample, 1234, band.buf0)
     ctx.upload(planes)
     ctx.synchronize()
+    o0, o1 = band.local_own
 
     def step():
-        bands.run_passes(ctx, band, boxes, args.seed, dist, local_rank)
+        ctx.reset_colors()  # every step filters the same fresh frame (0.1 ms on the device), not the previous step's output
+        if emulate is None:
+            ctx.apply(boxes, args.seed)
+        else:
+            for b in boxes:
+                ctx.filter_rows(b, o0, o1, args.seed)
+                ctx.swap_colors()
 
     def barrier():
         ctx.synchronize()
@@ -212,7 +356,6 @@ def main():
         step()
     barrier()
     ctx.reset_stats()
-    ctx.set_profiling(True)  # a CUDA event pair around every kernel launch, on the stream the kernels run on
     sampler = ClockSampler(local_rank)
     sampler.start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -226,23 +369,62 @@ def main():
     barrier()
     wall = time.perf_counter() - t0
     sampler.stop_flag = True
-    dev_s = ev0.elapsed_time(ev1) / 1e3
+    my_dev_s = ev0.elapsed_time(ev1) / 1e3
     st = ctx.stats()
+
+    # per-kernel device time: a SEPARATE pass with an event pair around every launch (none of it inside the timed region)
+    ctx.reset_stats()
+    ctx.set_profiling(True)
+    step()
+    barrier()
     ktimes = ctx.kernel_times()
     ctx.set_profiling(False)
-    t = torch.tensor([dev_s, wall], dtype=torch.float64, device=f"cuda:{local_rank}")
-    if dist is not None:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    dev_s, wall = t.tolist()
-    total_samples = W * H * P
+    kern_mine = {k: {"ms": ms, "launches": n} for k, (ms, n) in ktimes.items() if n}
+
+    def gather(obj):
+        if dist is None:
+            return [obj]
+        box = [None] * world
+        dist.all_gather_object(box, obj)
+        return box
+
+    per_rank = gather({"dev_s": my_dev_s, "wall": wall, "kern": kern_mine, "st": st, "rows": [band.own0, band.own1]})
+    dev_s = max(r["dev_s"] for r in per_rank)
+    wall = max(r["wall"] for r in per_rank)
+    total_samples = W * H * P if emulate is None else W * (o1 - o0) * P
     value = total_samples * args.steps / dev_s / 1e6
 
-    # e2e: host planes -> device, all passes, colours back to the host, every step (through the public C ABI)
+    # ---- the result itself: checksum of the owned colours, parity window against the oracle -------------------------------
+    final = ctx.download_colors_f64().reshape(3, lh, W, P)
+    dbg_n = ctx.download_debug()["N"].reshape(lh, W)
+    parts = gather({"sum": checksum64(final[:, o0:o1]), "rows": [band.own0, band.own1]})
+    checksum = sum(p["sum"] for p in parts) % (1 << 64)
+    parity = None
+    if not args.no_parity and emulate is None:
+        ww, wh = min(WINDOW, W), min(WINDOW, H)
+        wx0 = (W - ww) // 2
+        plan = rpf_b200.band_plan(H, world, boxes) if world > 1 else None
+        wy0 = max(0, min(H - wh, plan[1] - wh // 2)) if plan else (H - wh) // 2
+        a, b = max(wy0, band.own0), min(wy0 + wh, band.own1)
+        mine = None
+        if a < b:
+            mine = (a, final[:, a - band.buf0:b - band.buf0, wx0:wx0 + ww].copy(), dbg_n[a - band.buf0:b - band.buf0, wx0:wx0 + ww].copy())
+        pieces = [p for p in gather(mine) if p is not None]
+        if rank == 0:
+            gc = np.zeros((3, wh, ww, P))
+            gn = np.zeros((wh, ww), np.int32)
+            for (ya, c, n) in pieces:
+                gc[:, ya - wy0:ya - wy0 + c.shape[1]] = c
+                gn[ya - wy0:ya - wy0 + n.shape[0]] = n
+            oc, on = oracle_window(frame, boxes, args.seed, wx0, wy0, ww, wh)
+            parity = parity_report(gc, gn, oc, on, (wx0, wy0, ww, wh), plan is not None and wy0 < plan[1] < wy0 + wh)
+
+    # ---- e2e: host planes -> device, all passes, colours back to the host, every step (through the public C ABI) -------------
     e2e = None
-    if not args.no_e2e:
+    if not args.no_e2e and emulate is None:
         def e2e_step():
             ctx.upload(planes)
-            step()
+            ctx.apply(boxes, args.seed)
             ctx.download_colors(out_host.numpy())
         e2e_step()
         barrier()
@@ -251,46 +433,62 @@ def main():
         for _ in range(n_e2e):
             e2e_step()
         barrier()
-        e2e_s = torch.tensor([(time.perf_counter() - t0) / n_e2e], dtype=torch.float64, device=f"cuda:{local_rank}")
-        if dist is not None:
-            dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-        e2e = {"value": total_samples / e2e_s.item() / 1e6, "unit": UNIT,
-               "h2d_bytes_per_step": 19 * S_loc * 4 * world, "d2h_bytes_per_step": 3 * S_loc * 4 * world}
+        e2e_s = max(gather((time.perf_counter() - t0) / n_e2e))
+        sizes = gather(S_loc)  # every rank uploads its band plus halo rows and reads its whole buffer back
+        e2e = {"value": total_samples / e2e_s / 1e6, "unit": UNIT, "h2d_bytes_per_step": sum(19 * s * 4 for s in sizes),
+               "d2h_bytes_per_step": sum(3 * s * 4 for s in sizes)}
 
+    # ---- roofline of the dominant kernel ---------------------------------------------------------------------------------
     peak, peak_src = peaks()
-    own_samples = W * (band.own1 - band.own0) * P
-    # dominant kernel = largest share of the timed region. Its algorithmic bytes: 88 B per sample per pass
-    # (19 fp32 channels read + 3 fp32 colours written) for every pass it takes part in; one launch covers a chunk of rows.
-    kern = {k: {"ms_total": ms, "launches": n, "share_of_step": ms / (dev_s * 1e3)} for k, (ms, n) in ktimes.items() if n}
-    dom = max(kern, key=lambda k: kern[k]["ms_total"]) if kern else None
+    kern = {}
+    for k in sorted({k for r in per_rank for k in r["kern"]}):
+        ms = [r["kern"].get(k, {"ms": 0.0})["ms"] for r in per_rank]
+        kern[k] = {"ms_per_step": spread(ms), "launches_per_step": int(sum(r["kern"].get(k, {"launches": 0})["launches"] for r in per_rank)),
+                   "share_of_step": max(ms) / (dev_s / args.steps * 1e3)}
+    dom = max(kern, key=lambda k: kern[k]["ms_per_step"]["max"]) if kern else None
+    nbh_sum = sum(r["st"]["nbh_sum"] for r in per_rank)
+    px_filtered = sum(r["st"]["pixels_filtered"] for r in per_rank)
     roof = None
     if dom:
         general = dom != "rpf_pixel_kernel"
-        passes = [b for b in boxes if (b * b * P > rpf_b200.lib().rpf_fused_max_candidates()) == general] if dom != "pixel_stats_kernel" else boxes[:1]
-        alg_bytes = ALG_BYTES_PER_SAMPLE_ITER * own_samples * len(passes) * args.steps
-        k_ms, k_n = kern[dom]["ms_total"], kern[dom]["launches"]
+        fused_max = rpf_b200.lib().rpf_fused_max_candidates()
+        passes = [b for b in boxes if (b * b * P > fused_max) == general] if dom != "pixel_stats_kernel" else boxes[:1]
+        slow = max(per_rank, key=lambda r: r["kern"].get(dom, {"ms": 0.0})["ms"])  # the rank whose launches are the longest
+        own_samples = W * (slow["rows"][1] - slow["rows"][0]) * P
+        k_ms, k_n = slow["kern"][dom]["ms"], slow["kern"][dom]["launches"]
+        alg_bytes = ALG_BYTES_PER_SAMPLE_ITER * own_samples * len(passes)  # per step of that rank
         achieved = alg_bytes / (k_ms * 1e-3) / 1e9
-        upd = 96 * st["nbh_sum"]  # joint-histogram updates in the timed region: 96 MI pairs x N per pixel-pass
+        upd = 96 * nbh_sum / args.steps  # joint-histogram updates per step: 96 MI pairs x N per pixel-pass
+        dep_s = max(r["kern"].get("dependency_kernel", {"ms": 0.0})["ms"] for r in per_rank) * 1e-3
         roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": measured_traffic(dom, f"{W}x{H}x{P}:{','.join(map(str, boxes))}") if world == 1 else None,
-                "peak_source": peak_src, "kernel": dom, "kernel_ms_per_launch": k_ms / k_n, "launches_timed": k_n,
+                "traffic": measured_traffic(dom, f"{W}x{H}x{P}:{','.join(map(str, boxes))}:n{world}"),
+                "peak_source": peak_src, "kernel": dom, "kernel_ms_per_launch": k_ms / k_n, "launches_per_step": k_n,
                 "algorithmic_bytes_per_launch": alg_bytes / k_n,
+                "how": "CUDA event pair around every launch on the context's stream, one profiled step right after the timed region; "
+                       "the rank with the longest launches when N > 1",
                 "note": "the path is bound by shared-memory atomic / FP64 issue, not HBM (DESIGN.md section 4)",
-                "on_chip": {"bound": "shared_atomics", "achieved": upd / (dev_s) / 1e9, "peak": 2180.0,
-                            "unit": "G histogram updates/s", "frac": upd / dev_s / 1e9 / 2180.0,
+                "on_chip": {"bound": "shared_atomics", "achieved": upd / (dev_s / args.steps) / 1e9 / world, "peak": 2180.0,
+                            "unit": "G histogram updates/s per GPU", "frac": upd / (dev_s / args.steps) / 1e9 / world / 2180.0,
+                            "in_dependency_kernel": (upd / world / dep_s / 1e9) if dep_s > 0 else None,
                             "peak_source": "profiles/micro/smem_micro.cu: random-address ATOMS, 1024 threads/SM, this pool's B200"}}
     res = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dev_s / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload, "sharding": f"{world} row band(s), halo {band.own0 - band.buf0}/{band.buf1 - band.own1} rows",
-                   "l2": f"inputs ({19 * 4 * W * H * P / 1e9:.2f} GB of planes per frame) exceed the 126 MB L2", "mean_neighbourhood":
-                       st["nbh_sum"] / max(1, st["pixels_filtered"])},
-        "wall_ms_per_step": wall / args.steps * 1e3, "gpu_launches": st["kernel_launches"], "nan_channels": st["nan_channels"],
-        "clocks": sampler.summary(), "roofline": roof, "kernels": kern, "e2e": e2e,
+        "dtype": "f64", "data": "rendered" if args.buffer else "synthetic", "config": config_of(args, boxes),
+        "sharding": {"bands": [r["rows"] for r in per_rank], "plan": "equal work (rpf_band_plan)", "halo_rows": band.own0 - band.buf0 if band.rank else band.buf1 - band.own1,
+                     "exchange": "ncclSend/ncclRecv inside rpf_filter, edge rows first, interior overlapped" if world > 1 else "none",
+                     "halo_bytes_per_step": sum(r["st"]["halo_bytes"] for r in per_rank) / args.steps},
+        "mean_neighbourhood": nbh_sum / max(1, px_filtered),
+        "wall_ms_per_step": wall / args.steps * 1e3, "gpu_launches": int(sum(r["st"]["kernel_launches"] for r in per_rank)),
+        "nan_channels": int(sum(r["st"]["nan_channels"] for r in per_rank)) // max(1, args.steps),
+        "clocks": sampler.summary(), "roofline": roof, "kernels": kern,
+        "ranks": {"step_ms": spread([r["dev_s"] / args.steps * 1e3 for r in per_rank])},
+        "checksum": f"{checksum:016x}", "parity": parity, "e2e": e2e,
     }
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        res["cpu_baseline"], _ = cpu_reference_run(args, boxes, 1, 0)
+    if emulate is not None:
+        res["note"] = f"band {args.band} of the sharded frame alone on one GPU, no exchange: for profiling, NOT a benchmark value"
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and emulate is None:
+        res["cpu_baseline"], _ = cpu_reference_run(args, frame, boxes, 1, 0)
     ctx.close()
     if dist is not None:
         dist.barrier()

@@ -91,6 +91,8 @@ const char *rpf_last_error(const rpf_ctx *ctx); /* ctx may be NULL: last error o
 int rpf_upload(rpf_ctx *ctx, const float *const planes[RPF_NUM_CHANNELS]);
 /* Same, from device-resident planes (synthetic benchmarks, multi-GPU bands). */
 int rpf_upload_device(rpf_ctx *ctx, const float *const d_planes[RPF_NUM_CHANNELS]);
+/* Working colours <- planes[2..4] of the last upload, on the device (stream ordered): filter the resident frame again. */
+int rpf_reset_colors(rpf_ctx *ctx);
 /* Optional: overwrite the working colours with doubles (the reference keeps filtered colours in double
  * between iterations, sd.h:205-207). rgb = [3][width*height*spp]. */
 int rpf_upload_colors_f64(rpf_ctx *ctx, const double *rgb);
@@ -147,6 +149,13 @@ int rpf_download_colors_f64(rpf_ctx *ctx, double *rgb); /* [3][width*height*spp]
  * nbh = N (rpf.cpp:588), alpha [..][3] (rpf.cpp:475), beta [..][12] (rpf.cpp:479), wrc (rpf.cpp:483-487). */
 int rpf_download_debug(rpf_ctx *ctx, int *nbh, double *alpha, double *beta, double *wrc);
 
+/* Component-level probe of one pixel (x, y in context coordinates; negative: off): the next passes leave the 96
+ * MutualInformation values of that pixel (mi.cpp:45-90; order of rpf.cpp:416-442: feature i against r0, r1, p0, p1 at
+ * 4*i + {0..3}, then colour i against r0, r1, p0, p1, f0..f11 at 48 + 16*i + {0..15}), its N, its bin count
+ * (mi.cpp:53-58) and the 19 marginal histograms (mi.cpp:5-21; integer counts, exact). marginals: [19][bins_cap]. */
+int rpf_set_debug_pixel(rpf_ctx *ctx, int x, int y);
+int rpf_download_debug_mi(rpf_ctx *ctx, double *mi /* [96] */, int *n, int *bins, unsigned *marginals, int bins_cap);
+
 /* Film reconstruction for pbrt's default box filter of radius 0.5 (filters/box.cpp:43-47, film.h:121-161):
  * per-pixel mean of the current colours weighted by nothing but rayWeight==1; rgb = [height*width][3] floats. */
 int rpf_reconstruct_box(rpf_ctx *ctx, float *rgb);
@@ -179,8 +188,8 @@ int rpf_film_filter_table(int kind, float radius_x, float radius_y, float alpha,
  * rpf_band_plan (host only, no device): first owned row of each of n_bands bands, own0[0..n_bands] with own0[n_bands] =
  * height, so that every band carries about the same WORK: a row's weight is sum over passes of box^2 * (rows of the
  * box inside the frame) / box -- rows near the top and bottom edge see truncated boxes and are cheaper. Every band owns
- * at least b_delta(largest later box) rows, so the exchange after a pass talks to adjacent bands only; RPF_ERR_INVALID
- * if the frame is too short for that. */
+ * at least b_delta(largest box after the first pass) rows, so the exchange after a pass talks to adjacent bands only;
+ * RPF_ERR_INVALID if the frame is too short for that. */
 int rpf_band_plan(int height, int n_bands, const int *box_sizes, int n_iter, int *own0 /* [n_bands + 1] */);
 
 /* One band per PROCESS (torchrun-style launch, one process per GPU): this context holds global rows [buf0, buf0 +

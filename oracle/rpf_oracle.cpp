@@ -89,15 +89,21 @@ void bin_channels(const double *z /*[n][19]*/, int n, int bins, ChannelBins &cb)
     }
 }
 
-// rpf.cpp:356-488
+// rpf.cpp:356-488. mi_log (optional, 96 doubles): every MutualInformation value in call order, which is
+// feature i against r0, r1, p0, p1 at 4*i + {0..3} (rpf.cpp:416-427), then colour i against r0, r1, p0, p1, f0..f11 at
+// 48 + 16*i + {0..15} (rpf.cpp:429-442).
 void cf_weights(const double *z, int n, int flags, double alpha[NC], double beta[NF], double &wrc,
-                ChannelBins &cb, std::vector<int> &joint, double eps = 0.0) {
+                ChannelBins &cb, std::vector<int> &joint, double eps = 0.0, double *mi_log = nullptr) {
     const int bins = bins_for(n);
     bin_channels(z, n, bins, cb);
+    int calls = 0;
     auto MI = [&](int ca, int cbn) {
-        return mi_from_bins(&cb.bin[static_cast<size_t>(ca) * n], &cb.bin[static_cast<size_t>(cbn) * n],
-                            &cb.hist[static_cast<size_t>(ca) * bins], &cb.hist[static_cast<size_t>(cbn) * bins],
-                            n, bins, joint);
+        const double v = mi_from_bins(&cb.bin[static_cast<size_t>(ca) * n], &cb.bin[static_cast<size_t>(cbn) * n],
+                                      &cb.hist[static_cast<size_t>(ca) * bins], &cb.hist[static_cast<size_t>(cbn) * bins],
+                                      n, bins, joint);
+        if (mi_log) mi_log[calls] = v;
+        ++calls;
+        return v;
     };
     double D_r_f[NF], D_p_f[NF], D_c_f[NF];
     double D_r_c[NC], D_p_c[NC], D_f_c[NC];
@@ -169,6 +175,7 @@ struct PixelScratch {
     std::vector<double> w;        // [P][n]
     ChannelBins cb;
     std::vector<int> joint;
+    double *mi_log = nullptr;     // rpf_oracle_pixel_probe: the 96 MI values of this pixel
 };
 
 // One pixel of rpf.cpp:556-723. Returns number of NaN colour channels written.
@@ -251,7 +258,7 @@ int filter_pixel(const Frame &f, int px, int py, int box, double seed, int flags
             s.z[o] = SD[c] == 0 ? 0 : (s.raw[o] - M[c]) / SD[c];
         }
     double alpha[NC], beta[NF], wrc;
-    cf_weights(s.z.data(), n, flags, alpha, beta, wrc, s.cb, s.joint, paper.w_eps);
+    cf_weights(s.z.data(), n, flags, alpha, beta, wrc, s.cb, s.joint, paper.w_eps, s.mi_log);
     if (n_out) *n_out = n;
     if (alpha_out) std::memcpy(alpha_out, alpha, sizeof alpha);
     if (beta_out) std::memcpy(beta_out, beta, sizeof beta);
@@ -412,4 +419,41 @@ extern "C" void rpf_oracle_cf_weights(const double *z, int n, int flags, double 
     ChannelBins cb;
     std::vector<int> joint;
     cf_weights(z, n, flags, alpha, beta, *wrc, cb, joint);
+}
+
+// One pixel of one pass (box a->box_sizes[0], input colours a->colors or planes[2..4]): the component-level view the GPU
+// exposes through rpf_set_debug_pixel / rpf_download_debug_mi.
+extern "C" int rpf_oracle_pixel_probe(const rpf_oracle_args *a, int px, int py, double *mi96, int *n_out, int *bins_out, int *marg,
+                                      int bins_cap, double *z_out, int n_cap) {
+    if (!a || !a->planes || a->n_iter < 1 || px < 0 || py < 0 || px >= a->width || py >= a->height) return -1;
+    const int W = a->width, H = a->height, P = a->spp;
+    const size_t S = static_cast<size_t>(W) * H * P;
+    std::vector<double> cur(3 * S), out(3 * S);
+    if (a->colors) std::memcpy(cur.data(), a->colors, 3 * S * sizeof(double));
+    else
+        for (int k = 0; k < 3; ++k)
+            for (size_t i = 0; i < S; ++i) cur[k * S + i] = a->planes[(CH_COL + k) * S + i];
+    Frame f{W, H, P, a->planes, S, cur.data()};
+    PixelScratch s;
+    double mi[96];
+    s.mi_log = mi;
+    Subsample sub;
+    Paper paper;
+    paper.w_eps = a->w_epsilon; paper.min_sigma = a->min_sigma; paper.pos_sigmas = a->world_pos_sigmas;
+    int n = 0;
+    filter_pixel(f, px, py, a->box_sizes[0], a->sigma_fc_seed, a->flags, sub, paper, out.data(), s, &n, nullptr, nullptr, nullptr);
+    const int bins = bins_for(n);
+    if (mi96) std::memcpy(mi96, mi, sizeof mi);
+    if (n_out) *n_out = n;
+    if (bins_out) *bins_out = bins;
+    if (marg) {
+        if (bins_cap < bins) return -2;
+        for (int c = 0; c < NCH; ++c)
+            for (int i = 0; i < bins_cap; ++i) marg[c * bins_cap + i] = i < bins ? s.cb.hist[static_cast<size_t>(c) * bins + i] : 0;
+    }
+    if (z_out) {
+        if (n_cap < n) return -3;
+        std::memcpy(z_out, s.z.data(), static_cast<size_t>(n) * NCH * sizeof(double));
+    }
+    return 0;
 }

@@ -82,6 +82,12 @@ void rpf_oracle_cf_weights(const double *z, int n, int flags, double *alpha, dou
  * sigma of the spp samples; a sample with |c - mean| > k_sigmas * sigma in any channel takes the mean in all three. */
 void rpf_oracle_hdr_clamp(double *colors, int width, int height, int spp, int y0, int y1, double k_sigmas);
 
+/* Component view of one pixel of one pass (box_sizes[0]): the 96 MutualInformation values in the order of rpf.cpp:416-442,
+ * N, bins (mi.cpp:53-58), the 19 marginal histograms [19][bins_cap] (mi.cpp:5-21) and optionally the normalised
+ * neighbourhood z [n][19] (rpf.cpp:603-612) so a test can hand its columns to the reference's own MutualInformation. */
+int rpf_oracle_pixel_probe(const rpf_oracle_args *a, int px, int py, double *mi96, int *n_out, int *bins_out, int *marg,
+                           int bins_cap, double *z_out, int n_cap);
+
 #ifdef __cplusplus
 }
 #endif

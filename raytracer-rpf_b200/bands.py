@@ -6,6 +6,12 @@ split into contiguous row bands, one per rank. Features, positions and random pa
 only the 3 colour planes of the rows within b_delta(next box) of a band edge move to the neighbouring rank
 (point-to-point send/recv; there is no collective). This module is backend agnostic: torch.distributed with NCCL on
 GPUs, gloo in the CPU tests.
+
+Since round 2 the schedule itself lives behind the C ABI (csrc/rpf_bands.inl): `attach` hands a context its band and an
+NCCL communicator (rpf_band_attach) and rpf_filter then filters the edge rows first, ships them with ncclSend / ncclRecv
+on a copy stream and filters the interior meanwhile, with no host synchronisation. What is left here is launcher
+plumbing for tests and bench.py: the band layout (rpf_band_plan, equal work) and, for the gloo CPU twin of the exchange,
+`halo_plan` / `exchange_halos`.
 """
 from dataclasses import dataclass
 
@@ -35,7 +41,9 @@ class Band:
 
 
 def make_band(rank, world, height, box_sizes):
-    """Equal-height bands; halo = largest b_delta over all passes (feature rows are needed at that depth)."""
+    """Equal-WORK bands (rpf_band_plan of the C ABI: rows near the top and bottom edge see truncated boxes and weigh
+    less); halo = largest b_delta over all passes (feature rows are needed at that depth)."""
+    import rpf_b200
     halo = max(b_delta(b) for b in box_sizes)
     # the exchange after a pass talks to the two adjacent ranks only: every band must own at least the rows the next
     # pass reaches across its edge, or a pixel would need colours from a rank two bands away
@@ -43,8 +51,8 @@ def make_band(rank, world, height, box_sizes):
     if world > 1 and height // world < reach:
         raise ValueError(f"{height} rows over {world} ranks leaves bands of {height // world} rows, thinner than the "
                          f"{reach}-row halo of the later passes: use fewer ranks")
-    own0 = rank * height // world
-    own1 = (rank + 1) * height // world
+    plan = rpf_b200.band_plan(height, world, box_sizes)
+    own0, own1 = plan[rank], plan[rank + 1]
     return Band(rank, world, height, own0, own1, max(0, own0 - halo), min(height, own1 + halo))
 
 
@@ -102,7 +110,20 @@ class DeviceColors:
         self.__cuda_array_interface__ = {"shape": (3, n), "typestr": "<f8", "data": (ptr, False), "version": 2}
 
 
-def run_passes(ctx, band, boxes, seed, dist=None, device=0, hdr_clamp_sigmas=0.0):
+def attach(ctx, band, dist=None):
+    """Give a context (holding rows [band.buf0, band.buf1)) its band; with world > 1 rank 0 creates the NCCL unique id and
+    torch.distributed carries its 128 bytes to the other ranks (launcher plumbing; the data path never touches torch)."""
+    import rpf_b200
+    uid = None
+    if band.world > 1:
+        import torch
+        box = [rpf_b200.nccl_unique_id() if band.rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        uid = box[0]
+    ctx.attach_band(band.height, band.buf0, band.own0, band.own1, band.rank, band.world, uid)
+
+
+def run_passes_host_exchange(ctx, band, boxes, seed, dist=None, device=0, hdr_clamp_sigmas=0.0):
     """The loop of rpf.cpp:767-775 over one row band on one GPU: each pass filters the owned rows, then the freshly
     written colour rows within b_delta(next box) of a band edge go to the neighbouring ranks (NCCL send/recv over
     NVLink) before the buffers swap. ctx: rpf_b200.RPFFilter holding the band plus its halo rows.
@@ -123,4 +144,17 @@ def run_passes(ctx, band, boxes, seed, dist=None, device=0, hdr_clamp_sigmas=0.0
             torch.cuda.synchronize(device)
         ctx.swap_colors()
     if hdr_clamp_sigmas > 0 and len(boxes):
+        ctx.hdr_clamp(hdr_clamp_sigmas, o0, o1)
+
+
+def run_passes(ctx, band, boxes, seed, dist=None, device=0, hdr_clamp_sigmas=0.0):
+    """All passes over an ATTACHED band context (see `attach`): one rpf_filter / rpf_filter_sigmas call, the exchange
+    happens inside the library. run_passes_host_exchange is the round-1 driver (host-synchronised torch.distributed
+    exchange), kept for A/B measurements."""
+    if hasattr(seed, "__len__"):
+        ctx.apply_sigmas(boxes, list(seed))
+    else:
+        ctx.apply(boxes, seed)
+    if hdr_clamp_sigmas > 0 and len(boxes):
+        o0, o1 = band.local_own
         ctx.hdr_clamp(hdr_clamp_sigmas, o0, o1)

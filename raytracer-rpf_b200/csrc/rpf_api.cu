@@ -69,6 +69,9 @@ struct rpf_ctx {
     double last_ms = 0.0;
     int max_dyn_smem = 0;
     std::string err;
+    long long probe_pixel = -1;     // rpf_set_debug_pixel
+    double *d_probe_mi = nullptr;   // [98]
+    unsigned *d_probe_marg = nullptr;  // [19][PROBE_BINS]
     bool col4_valid = false;        // col4 / the colour slots of rec19 hold the CURRENT colours (general path, once per pass)
     // ---- row bands (rpf_bands.inl) ----
     std::vector<rpf_ctx *> shards;  // n_gpus > 1: this context is the parent of one child per device and owns no device memory
@@ -192,6 +195,8 @@ extern "C" void rpf_destroy(rpf_ctx *ctx) {
     cudaFree(ctx->d_dbg_alpha);
     cudaFree(ctx->d_dbg_beta);
     cudaFree(ctx->d_dbg_wrc);
+    cudaFree(ctx->d_probe_mi);
+    cudaFree(ctx->d_probe_marg);
     for (auto &sp : ctx->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
     for (auto e : ctx->free_events) cudaEventDestroy(e);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
@@ -414,6 +419,27 @@ extern "C" int rpf_upload_device(rpf_ctx *ctx, const float *const d_planes[RPF_N
                                 cudaMemcpyDeviceToDevice, ctx->stream));
     }
     return after_upload(ctx);
+}
+
+// Working colours <- planes[2..4] again (what rpf_upload leaves): a frame that stays resident can be filtered afresh
+// without another upload. Stream ordered.
+extern "C" int rpf_reset_colors(rpf_ctx *ctx) {
+    if (!ctx) return RPF_ERR_INVALID;
+    if (!ctx->uploaded) return fail(ctx, RPF_ERR_STATE, "rpf_reset_colors: no samples uploaded");
+    if (!ctx->shards.empty()) {
+        for (rpf_ctx *c : ctx->shards) {
+            const int rc = rpf_reset_colors(c);
+            if (rc != RPF_OK) { ctx->err = c->err; return rc; }
+        }
+        return RPF_OK;
+    }
+    CU(ctx, cudaSetDevice(ctx->cfg.device));
+    const size_t n = 3 * ctx->S;
+    colors_to_f64_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_planes, ctx->S, ctx->d_col[ctx->cur]);
+    ctx->launches++;
+    CU(ctx, cudaGetLastError());
+    ctx->col4_valid = false;
+    return RPF_OK;
 }
 
 extern "C" int rpf_upload_colors_f64(rpf_ctx *ctx, const double *rgb) {
@@ -653,6 +679,7 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
     p.dbg_beta = ctx->d_dbg_beta;
     p.dbg_wrc = ctx->d_dbg_wrc;
     p.counters = ctx->d_counters;
+    p.probe = DebugProbe{ctx->d_probe_mi ? ctx->probe_pixel : -1, ctx->d_probe_mi, ctx->d_probe_marg};
     for (int r0 = y0; r0 < y1; r0 += static_cast<int>(rows)) {
         p.row0 = r0;
         p.nrows = r0 + rows <= y1 ? static_cast<int>(rows) : y1 - r0;
@@ -743,6 +770,7 @@ static int launch_rows(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
     p.dbg_beta = ctx->d_dbg_beta;
     p.dbg_wrc = ctx->d_dbg_wrc;
     p.counters = ctx->d_counters;
+    p.probe = DebugProbe{ctx->d_probe_mi ? ctx->probe_pixel : -1, ctx->d_probe_mi, ctx->d_probe_marg};
     p.sub = ctx->sub;
     const unsigned grid = static_cast<unsigned>((y1 - y0) * ctx->cfg.width);
     prof_begin(ctx, RPF_K_FUSED);
@@ -1023,6 +1051,47 @@ extern "C" int rpf_download_debug(rpf_ctx *ctx, int *nbh, double *alpha, double 
     return rpf_synchronize(ctx);
 }
 
+// Component-level probe ("histogram counts exact", MI known answers): one pixel's 96 mutual informations
+// and 19 marginal histograms, written by whichever dependency path filters that pixel in the next passes.
+extern "C" int rpf_set_debug_pixel(rpf_ctx *ctx, int x, int y) {
+    if (!ctx) return RPF_ERR_INVALID;
+    NOT_SHARDED(ctx, "rpf_set_debug_pixel");
+    if (x < 0 || y < 0) { ctx->probe_pixel = -1; return RPF_OK; }
+    if (x >= ctx->cfg.width || y >= ctx->cfg.height) return fail(ctx, RPF_ERR_INVALID, "rpf_set_debug_pixel: (%d,%d) outside the context", x, y);
+    CU(ctx, cudaSetDevice(ctx->cfg.device));
+    if (!ctx->d_probe_mi) {
+        CU(ctx, cudaMalloc(&ctx->d_probe_mi, (N_JOINT + 2) * sizeof(double)));
+        CU(ctx, cudaMalloc(&ctx->d_probe_marg, NCH * PROBE_BINS * sizeof(unsigned)));
+    }
+    CU(ctx, cudaMemsetAsync(ctx->d_probe_mi, 0, (N_JOINT + 2) * sizeof(double), ctx->stream));
+    CU(ctx, cudaMemsetAsync(ctx->d_probe_marg, 0, NCH * PROBE_BINS * sizeof(unsigned), ctx->stream));
+    ctx->probe_pixel = static_cast<long long>(y) * ctx->cfg.width + x;
+    return RPF_OK;
+}
+
+extern "C" int rpf_download_debug_mi(rpf_ctx *ctx, double *mi, int *n, int *bins, unsigned *marginals, int bins_cap) {
+    if (!ctx) return RPF_ERR_INVALID;
+    NOT_SHARDED(ctx, "rpf_download_debug_mi");
+    if (!ctx->d_probe_mi || ctx->probe_pixel < 0) return fail(ctx, RPF_ERR_STATE, "rpf_download_debug_mi: no pixel selected (rpf_set_debug_pixel)");
+    CU(ctx, cudaSetDevice(ctx->cfg.device));
+    int rc = rpf_synchronize(ctx);
+    if (rc != RPF_OK) return rc;
+    double h[N_JOINT + 2];
+    CU(ctx, cudaMemcpy(h, ctx->d_probe_mi, sizeof h, cudaMemcpyDeviceToHost));
+    if (mi) memcpy(mi, h, N_JOINT * sizeof(double));
+    const int nb = static_cast<int>(h[N_JOINT + 1]);
+    if (n) *n = static_cast<int>(h[N_JOINT]);
+    if (bins) *bins = nb;
+    if (marginals) {
+        if (bins_cap < nb) return fail(ctx, RPF_ERR_INVALID, "rpf_download_debug_mi: %d bins, room for %d", nb, bins_cap);
+        std::vector<unsigned> m(NCH * PROBE_BINS);
+        CU(ctx, cudaMemcpy(m.data(), ctx->d_probe_marg, m.size() * sizeof(unsigned), cudaMemcpyDeviceToHost));
+        for (int c = 0; c < NCH; ++c)
+            for (int i = 0; i < bins_cap; ++i) marginals[c * bins_cap + i] = i < nb ? m[c * PROBE_BINS + i] : 0u;
+    }
+    return RPF_OK;
+}
+
 extern "C" int rpf_reconstruct_box(rpf_ctx *ctx, float *rgb) {
     if (!ctx || !rgb) return fail(ctx, RPF_ERR_INVALID, "rpf_reconstruct_box: null argument");
     NOT_SHARDED(ctx, "rpf_reconstruct_box");
@@ -1162,7 +1231,8 @@ static int create_sharded(rpf_ctx **out, const rpf_config *cfg, int ndev) {
     par->npix = cfg->width * cfg->height;
     par->halo_rows = b_delta(max_box);
     par->shard_own0.resize(G + 1);
-    if (band_plan(cfg->height, G, &max_box, 1, par->shard_own0.data()) != RPF_OK) {
+    const int plan_boxes[2] = {max_box, max_box};  // any schedule of boxes up to max_box: every band owns b_delta(max_box) rows
+    if (band_plan(cfg->height, G, plan_boxes, 2, par->shard_own0.data()) != RPF_OK) {
         delete par;
         return fail(nullptr, RPF_ERR_INVALID, "rpf_create: %d rows cannot be split into %d bands of at least %d rows (box %d)", cfg->height, G,
                     b_delta(max_box), max_box);

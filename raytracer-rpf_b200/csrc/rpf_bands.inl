@@ -21,10 +21,12 @@ inline int b_delta(int box) { return (box - 1) / 2; }  // rpf.cpp:561
 // ---- equal-work plan -------------------------------------------------------------------------------------------------
 int band_plan(int height, int n, const int *boxes, int n_iter, int *own0) {
     if (height <= 0 || n < 1 || n > height || n_iter < 0 || (n_iter && !boxes) || !own0) return RPF_ERR_INVALID;
+    // the exchange after a pass talks to the two adjacent bands only: a band must own at least the rows any LATER pass
+    // reaches across its edge, or a pixel would need colours from two bands away
     int reach = 0;
     for (int i = 0; i < n_iter; ++i) {
         if (boxes[i] < 1) return RPF_ERR_INVALID;
-        reach = std::max(reach, b_delta(boxes[i]));
+        if (i > 0) reach = std::max(reach, b_delta(boxes[i]));
     }
     const int min_rows = std::max(1, reach);
     if (n > 1 && 1ll * n * min_rows > height) return RPF_ERR_INVALID;
@@ -148,6 +150,8 @@ int attached_filter(rpf_ctx *c, const int *boxes, const double *seeds, double se
             return fail(c, RPF_ERR_INVALID, "box %d reaches %d rows across the band edge, the context holds %d halo rows", boxes[i],
                         b_delta(boxes[i]), b.own0 - b.buf0);
         const bool up = b.rank > 0, down = b.rank + 1 < b.world;
+        if ((up || down) && d > o1 - o0)
+            return fail(c, RPF_ERR_INVALID, "box %d reaches %d rows across a band edge, this band owns %d: use fewer bands", boxes[i + 1], d, o1 - o0);
         int rc = band_pass(c, boxes[i], seeds ? seeds[i] : seed_all, o0, o1, d, up, down, [&]() -> int {
             if (d <= 0 || (!up && !down)) return RPF_OK;
             double *next = c->d_col[c->cur ^ 1];
@@ -190,6 +194,10 @@ int sharded_filter(rpf_ctx *par, const int *boxes, const double *seeds, double s
             return fail(par, RPF_ERR_INVALID, "box %d needs %d halo rows, the sharded context was created for %d (rpf_config.max_box)",
                         boxes[i], b_delta(boxes[i]), par->halo_rows);
         const int d = i + 1 < n_iter ? b_delta(boxes[i + 1]) : 0;
+        for (int g = 0; g < G && G > 1; ++g)
+            if (d > par->shard_own0[g + 1] - par->shard_own0[g])
+                return fail(par, RPF_ERR_INVALID, "box %d reaches %d rows across a band edge, band %d owns %d: use fewer devices", boxes[i + 1], d, g,
+                            par->shard_own0[g + 1] - par->shard_own0[g]);
         // every band marks "my previous pass has drained" before it starts this one: a neighbour may overwrite the halo
         // rows of this band's NEXT buffer (the buffer its previous pass read) only after that
         for (int g = 0; g < G; ++g) {

@@ -57,14 +57,14 @@ __global__ void __launch_bounds__(KW_THREADS, 4) blend_wide_kernel(const General
         const float4 *r16 = p.rec16 + static_cast<size_t>(g) * 4;
         const float4 f0 = __ldg(r16), f1 = __ldg(r16 + 1), f2 = __ldg(r16 + 2), f3 = __ldg(r16 + 3);
         const double4 cc = p.col4[g];
-        dst[0] = (cc.x - ks.mz[0]) * ks.scl[0];
-        dst[1] = (cc.y - ks.mz[1]) * ks.scl[1];
-        dst[2] = (cc.z - ks.mz[2]) * ks.scl[2];
+        dst[0] = scaled(cc.x, ks.mz[0], ks.scl[0]);
+        dst[1] = scaled(cc.y, ks.mz[1], ks.scl[1]);
+        dst[2] = scaled(cc.z, ks.mz[2], ks.scl[2]);
         const float fs[16] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w, f2.x, f2.y, f2.z, f2.w, f3.x, f3.y, f3.z, f3.w};
 #pragma unroll
         for (int k = 3; k < NWZ; ++k) {
             const double x = static_cast<double>(k < 15 ? fs[k + 1] : fs[k - 15]);
-            dst[k] = (x - ks.mz[k]) * ks.scl[k];
+            dst[k] = scaled(x, ks.mz[k], ks.scl[k]);
         }
         if (with_colours) { dst[17] = cc.x; dst[18] = cc.y; dst[19] = cc.z; }
     };
@@ -116,7 +116,10 @@ __global__ void __launch_bounds__(KW_THREADS, 4) blend_wide_kernel(const General
                         arg = fma(d, d, arg);
                         d = zc2 - zj[2];
                         arg = fma(d, d, arg);
-                        if (!(arg > 745.2)) {  // NaN falls through to exp
+                        // NaN falls through to exp; so does a neighbour with an Inf / NaN raw colour, which the reference
+                        // blends in even with weight 0 (rpf.cpp:692: 0 * inf = NaN)
+                        const double cs = (zj[17] + zj[18]) + zj[19];
+                        if (!(arg > 745.2) || !(cs - cs == 0.0)) {
 #pragma unroll
                             for (int k = 3; k < NWZ; ++k) {
                                 const double e = zr[k] - zj[k];

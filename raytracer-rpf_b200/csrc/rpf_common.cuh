@@ -27,6 +27,15 @@ struct SubsampleParams {
     int row_g0;   // global row of this context's row 0 (row bands)
 };
 
+// Component-level probe of ONE pixel (rpf_set_debug_pixel): its 96 mutual informations in task order (task_channels below),
+// N, the bin count, and the 19 marginal histograms (mi.cpp:5-21) -- what SURVEY.md 8(c) pins as "histogram counts exact".
+constexpr int PROBE_BINS = 1024;  // sqrt(2^20 candidates)
+struct DebugProbe {
+    long long pixel;      // y*W+x in context coordinates, -1: off
+    double *mi;           // [96] MI values, [96] = N, [97] = bins
+    unsigned *marg;       // [19][PROBE_BINS]
+};
+
 // Device view of the frame: 19 float planes, each S = W*H*P samples, index (y*W+x)*P+s.
 struct FrameView {
     const float *planes;
@@ -59,6 +68,7 @@ struct FilterParams {
     unsigned long long *counters;  // [0] sum N, [1] NaN channels, [2] min N, [3] max N
     SubsampleParams sub;
     double w_eps;           // paper mode: epsilon added to the denominators of the W ratios (0 = reference)
+    DebugProbe probe;
 };
 
 // Non-colour channels are staged as floats in slots 0..15: slot -> channel.

@@ -91,6 +91,7 @@ struct GeneralParams {
     int *dbg_n;
     double *dbg_alpha, *dbg_beta, *dbg_wrc;
     unsigned long long *counters;
+    DebugProbe probe;
 };
 
 // 256-bit gathers (LDG.E.256 on sm_100): a sample's 64-byte feature record in two requests instead of four, its
@@ -610,6 +611,14 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
             if (tid < NC) p.dbg_alpha[pix * NC + tid] = ks.alpha[tid];
             if (tid < NF) p.dbg_beta[pix * NF + tid] = ks.beta[tid];
         }
+        if (p.probe.mi && static_cast<long long>(pix) == p.probe.pixel) {
+            if (tid < N_JOINT) p.probe.mi[tid] = ks.mi[tid];
+            if (tid == 0) { p.probe.mi[N_JOINT] = static_cast<double>(N); p.probe.mi[N_JOINT + 1] = static_cast<double>(nb); }
+            for (int k = tid; k < NCH * PROBE_BINS; k += NT) {
+                const int c = k / PROBE_BINS, i = k - c * PROBE_BINS;
+                p.probe.marg[k] = i < nb ? marg[c * L.nbs + i] : 0u;
+            }
+        }
     }
 }
 
@@ -665,7 +674,7 @@ __global__ void __launch_bounds__(KC_THREADS, 4) blend_kernel(const GeneralParam
         for (int k = 0; k < NWZ; ++k) {
             // z order: colour, features (slots 4..15), position (slots 0, 1)
             const double x = k < 3 ? col[k] : static_cast<double>(k < 15 ? fs[k + 1] : fs[k - 15]);
-            z[k] = (x - ks.mz[k]) * ks.scl[k];
+            z[k] = scaled(x, ks.mz[k], ks.scl[k]);
         }
     };
     for (int n = tid; n < P; n += KC_THREADS) {
@@ -716,7 +725,7 @@ __global__ void __launch_bounds__(KC_THREADS, 4) blend_kernel(const GeneralParam
                 const double cj[NC] = {cc.x, cc.y, cc.z};
                 double zj[NWZ];
 #pragma unroll
-                for (int k = 0; k < 3; ++k) zj[k] = (cj[k] - ks.mz[k]) * ks.scl[k];
+                for (int k = 0; k < 3; ++k) zj[k] = scaled(cj[k], ks.mz[k], ks.scl[k]);
                 unsigned pass = 0u;
 #pragma unroll
                 for (int ii = 0; ii < KC_IC; ++ii) {
@@ -731,12 +740,16 @@ __global__ void __launch_bounds__(KC_THREADS, 4) blend_kernel(const GeneralParam
                         if (!(arg > 745.2)) pass |= 1u << ii;  // NaN passes on to exp
                     }
                 }
+                // A neighbour whose raw colour is Inf or NaN poisons every own sample it is blended into even with weight 0
+                // (rpf.cpp:692: 0 * inf = NaN), so it is never skipped: the cut is only a shortcut for finite colours.
+                const bool finite_c = (cj[0] - cj[0] == 0.0) && (cj[1] - cj[1] == 0.0) && (cj[2] - cj[2] == 0.0);
+                if (!finite_c) pass = (P - i0 >= KC_IC) ? ((1u << KC_IC) - 1u) : ((1u << (P - i0)) - 1u);
                 if (pass == 0u) continue;
                 const float fs[16] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w, f2.x, f2.y, f2.z, f2.w, f3.x, f3.y, f3.z, f3.w};
 #pragma unroll
                 for (int k = 3; k < NWZ; ++k) {
                     const double x = static_cast<double>(k < 15 ? fs[k + 1] : fs[k - 15]);
-                    zj[k] = (x - ks.mz[k]) * ks.scl[k];
+                    zj[k] = scaled(x, ks.mz[k], ks.scl[k]);
                 }
 #pragma unroll
                 for (int ii = 0; ii < KC_IC; ++ii) {

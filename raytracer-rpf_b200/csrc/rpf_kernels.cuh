@@ -150,6 +150,13 @@ __device__ __forceinline__ double normalise(double x, double m, double sd) {
     return sd == 0.0 ? 0.0 : __ddiv_rn(__dsub_rn(x, m), sd);
 }
 
+// Weight-space coordinate of a raw value: (x - mean) * sqrt(coefficient) / sigma. A channel that is constant over the
+// neighbourhood has scale 0 and coordinate 0 whatever x is (ops.h:44-51 returns 0 for sigma == 0 without dividing) -- also
+// when x is Inf or NaN, which under P3 always comes with sigma 0 (the variance of a non-finite channel is NaN).
+__device__ __forceinline__ double scaled(double x, double m, double scale) {
+    return scale == 0.0 ? 0.0 : (x - m) * scale;
+}
+
 // Small per-pixel scalars in shared memory.
 struct PixelSmall {
     double mu[NF], sd3[NF];          // centre pixel feature statistics

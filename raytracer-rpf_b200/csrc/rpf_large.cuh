@@ -242,6 +242,14 @@ __global__ void __launch_bounds__(KL_THREADS, 1) dependency_large_kernel(const G
         if (tid < NC) rec[REC_ALPHA + tid] = ks.alpha[tid];
         if (tid < NF) rec[REC_BETA + tid] = ks.beta[tid];
         if (tid == 0) rec[REC_WRC] = ks.wrc;
+        if (p.probe.mi && static_cast<long long>(pix) == p.probe.pixel) {
+            if (tid < N_JOINT) p.probe.mi[tid] = ks.mi[tid];
+            if (tid == 0) { p.probe.mi[N_JOINT] = static_cast<double>(N); p.probe.mi[N_JOINT + 1] = static_cast<double>(nb); }
+            for (int k = tid; k < NCH * PROBE_BINS; k += KL_THREADS) {
+                const int c = k / PROBE_BINS, i = k - c * PROBE_BINS;
+                p.probe.marg[k] = i < nb ? marg[c * L.nbs + i] : 0u;
+            }
+        }
         if (p.dbg_n) {
             if (tid == 0) { p.dbg_n[pix] = N; p.dbg_wrc[pix] = ks.wrc; }
             if (tid < NC) p.dbg_alpha[pix * NC + tid] = ks.alpha[tid];

@@ -387,6 +387,15 @@ __global__ void __launch_bounds__(THREADS, 4) rpf_pixel_kernel(const FilterParam
             atomicMax(&p.counters[3], static_cast<unsigned long long>(N));
         }
         __syncthreads();
+        if (p.probe.mi && static_cast<long long>(pix) == p.probe.pixel) {
+            if (tid < N_JOINT) p.probe.mi[tid] = ps.mi[tid];
+            if (tid == 0) { p.probe.mi[N_JOINT] = static_cast<double>(N); p.probe.mi[N_JOINT + 1] = static_cast<double>(nb); }
+            if (tid < NCH) {  // marginal counts straight from the bin indices (the lane-private tables are gone by now)
+                unsigned *m = p.probe.marg + tid * PROBE_BINS;
+                for (int i = 0; i < PROBE_BINS; ++i) m[i] = 0u;
+                for (int j = 0; j < N; ++j) m[bins[j * 20 + tid]] += 1u;
+            }
+        }
         if (p.dbg_n) {
             if (tid == 0) { p.dbg_n[pix] = N; p.dbg_wrc[pix] = ps.wrc; }
             if (tid < NC) p.dbg_alpha[pix * NC + tid] = ps.alpha[tid];
@@ -426,7 +435,7 @@ __global__ void __launch_bounds__(THREADS, 4) rpf_pixel_kernel(const FilterParam
                 } else {
                     x = static_cast<double>(__ldg(p.f.planes + static_cast<size_t>(k < 2 ? k : k + 2) * S + g));
                 }
-                z[k] = (x - ps.mz[k]) * ps.scl[k];
+                z[k] = scaled(x, ps.mz[k], ps.scl[k]);
             }
         };
         for (int n = tid; n < P; n += THREADS) {

@@ -79,6 +79,29 @@ static bool run(SamplingFilm &film, const RPFB200Options &opt, const rpf_film_de
         return false;
     }
 
+    // the context first: without a usable device nothing else needs to happen (there is no CPU path)
+    rpf_config cfg{};
+    cfg.width = W;
+    cfg.height = H;
+    cfg.spp = static_cast<int>(spp);
+    cfg.device = opt.device;
+    cfg.flags = opt.flags;
+    cfg.debug = opt.debugStats ? 1 : 0;
+    if (opt.devices.size() > 1) {
+        if (opt.devices.size() > RPF_MAX_GPUS) {
+            if (error) *error = "RPFB200Options::devices lists more than RPF_MAX_GPUS devices";
+            return false;
+        }
+        cfg.n_gpus = static_cast<int>(opt.devices.size());
+        for (size_t g = 0; g < opt.devices.size(); ++g) cfg.device_ids[g] = opt.devices[g];
+        cfg.max_box = opt.boxSizes.empty() ? 0 : *std::max_element(opt.boxSizes.begin(), opt.boxSizes.end());
+    } else if (opt.devices.size() == 1)
+        cfg.device = opt.devices[0];
+    rpf_ctx *raw = nullptr;
+    if (rpf_create(&raw, &cfg) != RPF_OK) return failed(error, "rpf_create", nullptr);
+    std::unique_ptr<rpf_ctx, CtxDeleter> ctx(raw);
+
+
     // pack: plane[c][(y*W + x)*spp + s]; SampleData::data order (sd.h:62-94). The producer writes pbrt Floats into the
     // doubles (sd.h:62-94), so narrowing to float is exact for a fresh film. The container is samples[x][y] (x-major,
     // sample_film.cpp:16-22); one task per image row writes contiguous runs of every plane into page-locked memory.
@@ -100,27 +123,6 @@ static bool run(SamplingFilm &film, const RPFB200Options &opt, const rpf_film_de
         }
     });
     const double packMs = ms_since(t0);
-
-    rpf_config cfg{};
-    cfg.width = W;
-    cfg.height = H;
-    cfg.spp = static_cast<int>(spp);
-    cfg.device = opt.device;
-    cfg.flags = opt.flags;
-    cfg.debug = opt.debugStats ? 1 : 0;
-    if (opt.devices.size() > 1) {
-        if (opt.devices.size() > RPF_MAX_GPUS) {
-            if (error) *error = "RPFB200Options::devices lists more than RPF_MAX_GPUS devices";
-            return false;
-        }
-        cfg.n_gpus = static_cast<int>(opt.devices.size());
-        for (size_t g = 0; g < opt.devices.size(); ++g) cfg.device_ids[g] = opt.devices[g];
-        cfg.max_box = opt.boxSizes.empty() ? 0 : *std::max_element(opt.boxSizes.begin(), opt.boxSizes.end());
-    } else if (opt.devices.size() == 1)
-        cfg.device = opt.devices[0];
-    rpf_ctx *raw = nullptr;
-    if (rpf_create(&raw, &cfg) != RPF_OK) return failed(error, "rpf_create", nullptr);
-    std::unique_ptr<rpf_ctx, CtxDeleter> ctx(raw);
 
     if (opt.keepProbability < 1.0 && rpf_set_subsampling(ctx.get(), opt.keepProbability, opt.rngSeed, 0) != RPF_OK)
         return failed(error, "rpf_set_subsampling", ctx.get());

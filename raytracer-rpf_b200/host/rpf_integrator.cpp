@@ -260,6 +260,9 @@ void RPFIntegrator::Render(const Scene &scene) {
             // no CPU filter exists in this build: say so and stop, as the reference stops on its own fatal condition
             // (rpf.cpp:702-705)
             Error("RPF B200 filter failed: %s", err.c_str());
+            fflush(stdout);
+            fflush(stderr);
+            ParallelCleanup();  // pbrt's workers must be joined first or exit() hangs in static destruction
             exit(1);
         }
         for (int n : rep.neighbourhood) ReportValue(neighborhoodSize, static_cast<int64_t>(n));

@@ -28,6 +28,7 @@ ABI_SYMBOLS = [
     "rpf_buffer_write", "rpf_buffer_info_read", "rpf_buffer_read", "rpf_set_subsampling",
     "rpf_set_paper_mode", "rpf_filter_sigmas", "rpf_hdr_clamp", "rpf_fused_max_candidates",
     "rpf_band_plan", "rpf_band_unique_id", "rpf_band_attach", "rpf_host_alloc", "rpf_host_free",
+    "rpf_set_debug_pixel", "rpf_download_debug_mi", "rpf_reset_colors",
 ]
 
 
@@ -84,7 +85,7 @@ def write_buffer(path, planes, width, height, spp, ray_weight=None, sample_origi
     info = BufferInfo(width, height, spp, sample_origin[0], sample_origin[1], 0)
     ptrs = (C.c_void_p * NCH)(*[planes[c].ctypes.data for c in range(NCH)])
     rw = None if ray_weight is None else np.ascontiguousarray(ray_weight, np.float32)
-    rc = lib().rpf_buffer_write(path.encode(), C.byref(info), ptrs, None if rw is None else _p(rw))
+    rc = hostio().rpf_buffer_write(path.encode(), C.byref(info), ptrs, None if rw is None else _p(rw))
     if rc != 0:
         raise RPFError(f"rpf_buffer_write({path}) failed ({rc})")
 
@@ -92,12 +93,12 @@ def write_buffer(path, planes, width, height, spp, ray_weight=None, sample_origi
 def read_buffer(path):
     """-> (planes [19, S] float32, ray_weight [S] float32, info dict)"""
     info = BufferInfo()
-    rc = lib().rpf_buffer_info_read(path.encode(), C.byref(info))
+    rc = hostio().rpf_buffer_info_read(path.encode(), C.byref(info))
     if rc != 0:
         raise RPFError(f"{path}: not a feature-buffer file ({rc})")
     S = info.width * info.height * info.spp
     planes, rw = np.empty((NCH, S), np.float32), np.empty(S, np.float32)
-    rc = lib().rpf_buffer_read(path.encode(), _p(planes), _p(rw))
+    rc = hostio().rpf_buffer_read(path.encode(), _p(planes), _p(rw))
     if rc != 0:
         raise RPFError(f"{path}: truncated or unreadable ({rc})")
     return planes, rw, {k: getattr(info, k) for k, _ in BufferInfo._fields_}
@@ -112,6 +113,21 @@ class KernelTimes(C.Structure):
 
 
 _lib = None
+_hostio = None
+
+
+def hostio():
+    """lib/librpf_hostio.so: the two host-only helpers of the ABI (rpf_synth_planes, rpf_buffer_*), without CUDA. A process
+    that only generates or reads feature buffers (bench.py's CPU reference arm) never maps the GPU library."""
+    global _hostio
+    if _hostio is None:
+        path = os.path.join(os.path.dirname(LIB_PATH), "librpf_hostio.so")
+        if not os.path.exists(path):
+            raise RPFError(f"{path} is not built (run `python -c 'import __graft_entry__ as g; g.build()'`)")
+        L = C.CDLL(path)
+        L.rpf_synth_planes.argtypes = [C.c_int, C.c_int, C.c_int, C.c_ulonglong, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        _hostio = L
+    return _hostio
 
 
 def lib():
@@ -155,6 +171,9 @@ def lib():
         L.rpf_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
         L.rpf_host_free.argtypes = [vp]
         L.rpf_host_free.restype = None
+        L.rpf_reset_colors.argtypes = [vp]
+        L.rpf_set_debug_pixel.argtypes = [vp, i, i]
+        L.rpf_download_debug_mi.argtypes = [vp, vp, C.POINTER(i), C.POINTER(i), vp, i]
         _lib = L
     return _lib
 
@@ -185,7 +204,7 @@ def synth_planes(width, height, spp, seed=1234, kind=0, x_off=0, y_off=0, out=No
     """Synthetic feature buffer of SURVEY.md 8(d): float32 [19, W*H*spp] (host side, deterministic)."""
     planes = out if out is not None else np.empty((NCH, width * height * spp), np.float32)
     assert planes.dtype == np.float32 and planes.flags.c_contiguous and planes.size == NCH * width * height * spp
-    rc = lib().rpf_synth_planes(width, height, spp, seed, kind, x_off, y_off, _p(planes))
+    rc = hostio().rpf_synth_planes(width, height, spp, seed, kind, x_off, y_off, _p(planes))
     if rc != 0:
         raise RPFError(f"rpf_synth_planes failed ({rc})")
     return planes
@@ -238,6 +257,10 @@ class RPFFilter:
         ptrs = (C.c_void_p * NCH)(*[dev_ptr + 4 * self.S * c for c in range(NCH)])
         self._check(lib().rpf_upload_device(self._h, ptrs))
 
+    def reset_colors(self):
+        """Working colours <- the uploaded planes[2..4] (device side)."""
+        self._check(lib().rpf_reset_colors(self._h))
+
     def upload_colors_f64(self, rgb):
         rgb = np.ascontiguousarray(rgb, np.float64)
         assert rgb.shape == (3, self.S)
@@ -258,6 +281,16 @@ class RPFFilter:
         N, al, be, w = np.zeros(n, np.int32), np.zeros((n, 3)), np.zeros((n, 12)), np.zeros(n)
         self._check(lib().rpf_download_debug(self._h, _p(N), _p(al), _p(be), _p(w)))
         return dict(N=N, alpha=al, beta=be, wrc=w)
+
+    def set_debug_pixel(self, x, y):
+        self._check(lib().rpf_set_debug_pixel(self._h, x, y))
+
+    def download_debug_mi(self, bins_cap=1024):
+        """-> dict(mi [96], N, bins, marginals [19, bins]) of the pixel chosen with set_debug_pixel."""
+        mi, n, nb = np.zeros(96), C.c_int(), C.c_int()
+        marg = np.zeros((NCH, bins_cap), np.uint32)
+        self._check(lib().rpf_download_debug_mi(self._h, _p(mi), C.byref(n), C.byref(nb), _p(marg), bins_cap))
+        return dict(mi=mi, N=n.value, bins=nb.value, marginals=marg[:, :nb.value].copy())
 
     def reconstruct_box(self):
         out = np.empty((self.H, self.W, 3), np.float32)

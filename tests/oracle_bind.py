@@ -206,3 +206,24 @@ def oracle_film(W, H, P, pfilm, colors, ray_weight, table, rx, ry, bounds, scale
     lib.rpf_oracle_film(W, H, P, _p(pfilm), _p(colors), None if rw is None else _p(rw), _p(table), rx, ry, x0, y0, x1, y1,
                         scale, max_lum, _p(rgb))
     return rgb
+
+
+def oracle_pixel_probe(planes, W, H, P, box, px, py, seed=0.002, flags=DEFINED, colors=None, bins_cap=1024):
+    """One pixel of one pass: dict(mi [96], N, bins, marginals [19, bins], z [N, 19])."""
+    planes = np.ascontiguousarray(planes, dtype=np.float32)
+    bx = np.asarray([box], dtype=np.int32)
+    a = OracleArgs()
+    a.width, a.height, a.spp = W, H, P
+    col = None if colors is None else np.ascontiguousarray(colors, np.float64)
+    a.planes, a.colors, a.box_sizes = _p(planes), (None if col is None else _p(col)), _p(bx)
+    a.n_iter, a.sigma_fc_seed, a.flags = 1, seed, flags
+    lib = oracle()
+    lib.rpf_oracle_pixel_probe.argtypes = [C.POINTER(OracleArgs), C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                           C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+    mi, n, nb = np.zeros(96), C.c_int(), C.c_int()
+    marg = np.zeros((NCH, bins_cap), np.int32)
+    ncap = box * box * P
+    z = np.zeros((ncap, NCH))
+    rc = lib.rpf_oracle_pixel_probe(C.byref(a), px, py, _p(mi), C.byref(n), C.byref(nb), _p(marg), bins_cap, _p(z), ncap)
+    assert rc == 0, rc
+    return dict(mi=mi, N=n.value, bins=nb.value, marginals=marg[:, :nb.value].copy(), z=z[:n.value].copy())
