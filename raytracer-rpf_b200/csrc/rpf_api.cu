@@ -499,6 +499,8 @@ static bool plan_general(long long ncap, int spp, int static_smem, GeneralPlan &
         if (avail < atleast(1)) continue;
         L.nt = v == 0 ? 512 : 1024;
         L.bins_in_smem = bins_bytes + atleast(8) <= avail;
+        // neighbourhoods whose CAPACITY does not fit (boxes 35 / 55) still mostly accept few enough samples: per-pixel choice
+        L.bins_dyn = !L.bins_in_smem && !L.idx_global && !(getenv("RPF_BINS_DYN") && atoi(getenv("RPF_BINS_DYN")) == 0);
         const int region = L.bins_in_smem ? avail - bins_bytes : avail;
         L.off_bins = L.bins_in_smem ? L.off_region + region : 0;
         L.region_words = region / 4;
@@ -1319,3 +1321,17 @@ extern "C" int rpf_host_alloc(void **out, size_t bytes) {
 extern "C" void rpf_host_free(void *p) {
     if (p) cudaFreeHost(p);
 }
+
+#ifdef RPF_PHASE_TIMERS
+// development build only: cycles per phase of dependency_kernel since the last call (thread 0 of every CTA; [6] = team 0
+// waiting at the barrier after its fill, [7] = team 0's sweep)
+extern "C" int rpf_debug_phase_cycles(rpf_ctx *ctx, unsigned long long *out8) {
+    if (!ctx || !out8) return RPF_ERR_INVALID;
+    int rc = rpf_synchronize(ctx);
+    if (rc != RPF_OK) return rc;
+    CU(ctx, cudaMemcpyFromSymbol(out8, g_phase_cycles, 8 * sizeof(unsigned long long)));
+    unsigned long long z[8] = {};
+    CU(ctx, cudaMemcpyToSymbol(g_phase_cycles, z, sizeof z));
+    return RPF_OK;
+}
+#endif

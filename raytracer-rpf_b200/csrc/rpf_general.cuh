@@ -33,6 +33,8 @@ struct GeneralPlan {
     int hw;          // words per joint histogram (two u16 cells per word), multiple of 4
     int nbs;         // words per marginal histogram
     int bins_in_smem;
+    int bins_dyn;    // bins_in_smem == 0 only: decide PER PIXEL -- a pixel whose N accepted samples leave room for eight tables of
+                     // its own size keeps its bins in shared memory (end of the histogram region), the others use bins_scratch
     int off_gsm, off_marg, off_region, off_bins, kb_smem;  // KB dynamic shared memory layout (bytes)
     int region_words;  // capacity of the histogram region in 32-bit words
     int kb_grid;
@@ -178,9 +180,18 @@ __device__ __forceinline__ int block_exclusive_scan(int v, int *wsum /* [NT/32 +
     return r;
 }
 
+#ifdef RPF_PHASE_TIMERS
+// Development build only (lib/librpf_b200_timers.so): SM cycles per phase of dependency_kernel, summed over CTAs by thread 0.
+__device__ unsigned long long g_phase_cycles[8];
+#define PHASE_MARK(i) do { if (threadIdx.x == 0) { const long long t_ = clock64(); atomicAdd(&g_phase_cycles[i], static_cast<unsigned long long>(t_ - t_phase)); t_phase = t_; } } while (0)
+#else
+#define PHASE_MARK(i) do { } while (0)
+#endif
+
 struct KBSmall {
     double M[NCH], SD[NCH], lo[NCH], hi[NCH];
-    double A[NCH], Bc[NCH], tol[NCH];  // bin estimate te = x*A + Bc, trusted unless within tol*(|te|+1) of an integer
+    double2 AB[NCH];                   // bin estimate te = x*A + Bc ({A, Bc}: one 16-byte load), trusted unless within
+    double tol[NCH];                   // tol[c] of an integer; the binning loop uses the largest of the 19 for every channel
     int flat[NCH];
     unsigned long long Sm[NCH];        // sum n ln n of each marginal (fixed point)
     unsigned long long Sab[N_JOINT];   // sum n ln n of each joint table (fixed point)
@@ -198,11 +209,12 @@ struct KBSmall {
 // trunc((((x-M)/SD) - lo)/(hi-lo) * nb) with every operation rounded; one FMA estimates it, and only when the estimate is
 // too close to an integer for its error bound (or is NaN) do the reference's exact divisions run. A flat channel has
 // A = 0, Bc = 0.5 (always bin 0); a NaN sigma makes A NaN (always the exact path).
-__device__ __forceinline__ int bin_value(double x, int c, const KBSmall &ks, int nb, double dnb) {
-    const double te = fma(x, ks.A[c], ks.Bc[c]);
+__device__ __forceinline__ int bin_value(double x, int c, const KBSmall &ks, int nb, double dnb, double tol) {
+    const double2 ab = ks.AB[c];
+    const double te = fma(x, ab.x, ab.y);
     const double r = rint(te);
     int b;
-    if (fabs(te - r) > ks.tol[c] * (fabs(te) + 1.0)) {
+    if (fabs(te - r) > tol) {
         b = __double2int_rz(te);
     } else {
         if (ks.flat[c]) return 0;
@@ -213,7 +225,7 @@ __device__ __forceinline__ int bin_value(double x, int c, const KBSmall &ks, int
 }
 
 // Per-pixel constants of the dependency kernels: the slot permutation step, and per channel the normalised extremes and
-// the FMA bin estimate te = x*A + Bc with its trust tolerance. Threads 0..18 own a channel, thread 32 the permutation.
+// the FMA bin estimate te = x*A + Bc with its (absolute) trust tolerance. Threads 0..18 own a channel, thread 32 the permutation.
 __device__ __forceinline__ void kb_prepare_pixel(KBSmall &ks, const double *rec, int N, double dnb, int tid) {
     if (tid == 32) {
         // slot -> sample permutation step: adjacent slots hold samples far apart in enumeration order, so the lanes
@@ -241,9 +253,9 @@ __device__ __forceinline__ void kb_prepare_pixel(KBSmall &ks, const double *rec,
         double A = rsd * rr, Bc = (-m * rsd - lo) * rr;
         if (flat) { A = 0.0; Bc = 0.5; }
         if (!flat && !(hi > lo)) A = __longlong_as_double(0x7ff8000000000000ll);  // sigma is NaN: always the exact path
-        ks.A[c] = A;
-        ks.Bc[c] = Bc;
-        ks.tol[c] = 1e-9 + 1e-14 * (fabs(m * A) + fabs(Bc) + fabs(rhi * A) + fabs(rlo * A));
+        ks.AB[c] = make_double2(A, Bc);
+        // te lies in [0, nb] (lo / hi are the true extremes), so tol * (nb + 2) bounds the relative form tol * (|te| + 1)
+        ks.tol[c] = (1e-9 + 1e-14 * (fabs(m * A) + fabs(Bc) + fabs(rhi * A) + fabs(rlo * A))) * (dnb + 2.0);
     }
 }
 
@@ -310,11 +322,10 @@ __device__ __forceinline__ void team_sync(int team, int nthreads) {
 // other set while slower threads may still be sweeping the set of unit i.
 template <int G, int NT>
 __device__ __forceinline__ void joint_phase(const GeneralParams &p, KBSmall &ks, const uint32_t *bins, unsigned *region,
-                                            const unsigned long long *hsm, int N, int nb, int hwn, int teams, int sets) {
+                                            const unsigned long long *hsm, int N, int nb, int hwn, int teams, int sets, int nq) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tw = (NT / 32) / teams, team = warp / tw;
     const int tn = tw * 32, tt = tid - team * tn;
-    const int nq = p.pl.nq;
     const int nfull = N >> 2, ntail = N & 3;
     constexpr int SUBS = 4 / G;
     int set = 0;
@@ -369,7 +380,14 @@ __device__ __forceinline__ void joint_phase(const GeneralParams &p, KBSmall &ks,
                 }
             }
         }
+#ifdef RPF_PHASE_TIMERS
+        long long t_fill = 0;
+        if (tid == 0) t_fill = clock64();
+#endif
         team_sync(team, tn);
+#ifdef RPF_PHASE_TIMERS
+        if (tid == 0) { const long long t_ = clock64(); atomicAdd(&g_phase_cycles[6], static_cast<unsigned long long>(t_ - t_fill)); t_fill = t_; }
+#endif
         // sweep: sum n ln n over the cells, zero them. Counts 0 and 1 contribute nothing (n ln n = 0) and skip the lookup.
 #pragma unroll
         for (int j = 0; j < G; ++j) {
@@ -384,6 +402,10 @@ __device__ __forceinline__ void joint_phase(const GeneralParams &p, KBSmall &ks,
                 if (any == 0u) continue;
                 r4[k] = make_uint4(0u, 0u, 0u, 0u);
                 const unsigned wv[4] = {v.x, v.y, v.z, v.w};
+                // Predicated lookups on purpose: a quarter of the lanes take part, all at a handful of small addresses, so each costs
+                // one shared-memory wavefront. Measured alternatives (profiles/r2/ab_v24.txt): one unconditional lookup per
+                // PAIR of cells from a 256-entry table (fewer instructions, but 32 random 8-byte addresses per load) +2.5 %; counting
+                // the cells equal to 2 and 3 in packed form without any table +6 %.
                 if ((any & 0xfe00fe00u) == 0u) {  // every count below KB_GSM: shared-memory table only
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
@@ -403,15 +425,18 @@ __device__ __forceinline__ void joint_phase(const GeneralParams &p, KBSmall &ks,
         }
         if (sets == 1) team_sync(team, tn);
         else set ^= 1;
+#ifdef RPF_PHASE_TIMERS
+        if (tid == 0) atomicAdd(&g_phase_cycles[7], static_cast<unsigned long long>(clock64() - t_fill));
+#endif
     }
 }
 
 // Rare: recompute one pair cell by cell with the reference's expression and rounding (mi.cpp:66-87). Whole CTA.
 template <int NT>
 __device__ void exact_pair(const GeneralParams &p, KBSmall &ks, const uint32_t *bins, unsigned *region, const unsigned *marg,
-                           int t, int N, int nb) {
+                           int t, int N, int nb, int nq) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int nq = p.pl.nq, nbs = p.pl.nbs;
+    const int nbs = p.pl.nbs;
     int a, b;
     task_channels(t, a, b);
     const double dn = static_cast<double>(N);
@@ -462,9 +487,8 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
     unsigned *region = reinterpret_cast<unsigned *>(smem + L.off_region);
     unsigned short *idx16 = reinterpret_cast<unsigned short *>(region);
     uint32_t *idx32 = reinterpret_cast<uint32_t *>(p.big_scratch + static_cast<size_t>(blockIdx.x) * p.big_stride);
-    uint32_t *bins = L.bins_in_smem ? reinterpret_cast<uint32_t *>(smem + L.off_bins)
-                                    : reinterpret_cast<uint32_t *>(p.bins_scratch + static_cast<size_t>(blockIdx.x) * NCH * L.nq * 4);
-    const int nq = L.nq;
+    uint32_t *const bins_fixed = L.bins_in_smem ? reinterpret_cast<uint32_t *>(smem + L.off_bins)
+                                                : reinterpret_cast<uint32_t *>(p.bins_scratch + static_cast<size_t>(blockIdx.x) * NCH * L.nq * 4);
     const int npix = p.nrows * W;
 
     for (int k = tid; k < KB_GSM; k += NT) gsm[k] = p.hq[k];  // n ln n for small counts
@@ -481,11 +505,26 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
         double *rec = p.rec + static_cast<size_t>(pl) * REC_DOUBLES;
 
         // ---- per-channel constants --------------------------------------------------------------------
+#ifdef RPF_PHASE_TIMERS
+        long long t_phase = clock64();
+#endif
         const int N = static_cast<int>(rec[REC_N]);
         if (N > 65535) continue;  // block-uniform: u16 cells / u8 bins stop here; dependency_large_kernel takes the pixel
         int nb = static_cast<int>(__dsqrt_rn(static_cast<double>(N)));  // mi.cpp:53-58
         if (nb < 1) nb = 1;
         const double dnb = static_cast<double>(nb);
+        // where this pixel's packed bins live (block-uniform): see GeneralPlan::bins_dyn
+        uint32_t *bins = bins_fixed;
+        int nq = L.nq, region_words = L.region_words;
+        if (L.bins_dyn) {
+            const int nqp = (N + 3) >> 2, hwp = (((nb * nb + 1) >> 1) + 3) & ~3;
+            const int need = (NCH * nqp + 3) & ~3;  // words, 16-byte granular
+            if (need + 8 * hwp <= L.region_words) {
+                nq = nqp;
+                region_words = L.region_words - need;
+                bins = region + region_words;
+            }
+        }
         kb_prepare_pixel(ks, rec, N, dnb, tid);
         for (int k = tid; k < N_JOINT; k += NT) { ks.susp[k] = 0; ks.Sab[k] = 0ull; }
         for (int k = tid; k < NCH * L.nbs; k += NT) marg[k] = 0u;
@@ -509,10 +548,14 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
             }
         }
         __syncthreads();
+        PHASE_MARK(0);  // prepare + mask decode
 
         // ---- normalise + bin: one slot per thread, u8 bins (channel-major byte arrays), marginal counts ------------
         {
             const unsigned Q = static_cast<unsigned>(ks.Q), uN = static_cast<unsigned>(N);
+            double tolmax = ks.tol[0];  // one trust tolerance for all channels: the largest (a NaN one is skipped; its channel's
+#pragma unroll                          // estimate is NaN as well and takes the exact path anyway)
+            for (int c = 1; c < NCH; ++c) tolmax = fmax(tolmax, ks.tol[c]);
             uint8_t *bin8 = reinterpret_cast<uint8_t *>(bins);
             const int cstride = nq * 4;
             for (unsigned m = tid; m < uN; m += NT) {
@@ -524,7 +567,7 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
                 const Rec16 r16 = load_rec16(p.rec16, g);
                 const double4 cc = load_col4(p.col4, g);
                 auto put = [&](int c, double x) {
-                    const int b = bin_value(x, c, ks, nb, dnb);
+                    const int b = bin_value(x, c, ks, nb, dnb, tolmax);
                     bin8[c * cstride + m] = static_cast<uint8_t>(b);
                     atomicAdd(&marg[c * L.nbs + b], 1u);
                 };
@@ -542,6 +585,7 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
             }
         }
         __syncthreads();
+        PHASE_MARK(1);  // gather + binning
 
         // ---- marginals: S_c = sum_i n_i ln n_i ---------------------------------------------------------------------
         for (int c = warp; c < NCH; c += NT / 32) {
@@ -554,7 +598,7 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
         // The histogram region (idx16 is dead now) is cut into slots of the ACTUAL table size (nb*nb u16 cells).
         {
             const int hwn = (((nb * nb + 1) >> 1) + 3) & ~3;
-            const int slots = L.region_words / hwn;
+            const int slots = region_words / hwn;
             int Gp, sets = 1, teams = 1;
             if (slots >= 4) {
                 Gp = 4;
@@ -576,11 +620,13 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
                 for (int k = tid; k < (teams * sets * Gp * hwn) >> 2; k += NT) r4[k] = make_uint4(0u, 0u, 0u, 0u);
             }
             __syncthreads();
-            if (Gp == 4) joint_phase<4, NT>(p, ks, bins, region, gsm, N, nb, hwn, teams, sets);
-            else if (Gp == 2) joint_phase<2, NT>(p, ks, bins, region, gsm, N, nb, hwn, teams, sets);
-            else joint_phase<1, NT>(p, ks, bins, region, gsm, N, nb, hwn, teams, sets);
+            PHASE_MARK(2);  // marginal sums + table clear
+            if (Gp == 4) joint_phase<4, NT>(p, ks, bins, region, gsm, N, nb, hwn, teams, sets, nq);
+            else if (Gp == 2) joint_phase<2, NT>(p, ks, bins, region, gsm, N, nb, hwn, teams, sets, nq);
+            else joint_phase<1, NT>(p, ks, bins, region, gsm, N, nb, hwn, teams, sets, nq);
         }
         __syncthreads();
+        PHASE_MARK(3);  // joint tables: atomics + sweeps
         if (tid < N_JOINT) {
             int a, b;
             task_channels(tid, a, b);
@@ -598,7 +644,7 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
         __syncthreads();
         if (ks.any_susp) {  // block-uniform, rare
             for (int t = 0; t < N_JOINT; ++t)
-                if (ks.susp[t]) exact_pair<NT>(p, ks, bins, region, marg, t, N, nb);
+                if (ks.susp[t]) exact_pair<NT>(p, ks, bins, region, marg, t, N, nb, nq);
         }
 
         // ---- dependencies -> alpha, beta, W_r_c (rpf.cpp:416-487) ------------------------------------------
@@ -611,6 +657,7 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
             if (tid < NC) p.dbg_alpha[pix * NC + tid] = ks.alpha[tid];
             if (tid < NF) p.dbg_beta[pix * NF + tid] = ks.beta[tid];
         }
+        PHASE_MARK(4);  // MI, exact recomputes, weights
         if (p.probe.mi && static_cast<long long>(pix) == p.probe.pixel) {
             if (tid < N_JOINT) p.probe.mi[tid] = ks.mi[tid];
             if (tid == 0) { p.probe.mi[N_JOINT] = static_cast<double>(N); p.probe.mi[N_JOINT + 1] = static_cast<double>(nb); }
@@ -719,8 +766,6 @@ __global__ void __launch_bounds__(KC_THREADS, 4) blend_kernel(const GeneralParam
                 candidate_sample(p.cd, t, px, py, B, P, W, H, g, centre);
                 // colour terms first, for all own samples of this round: at the reference's sigma most neighbours are cut
                 // by every own sample, and then the other 14 channels are never scaled (they are two thirds of the work)
-                const float4 *r16 = p.rec16 + static_cast<size_t>(g) * 4;
-                const float4 f0 = __ldg(r16), f1 = __ldg(r16 + 1), f2 = __ldg(r16 + 2), f3 = __ldg(r16 + 3);
                 const double4 cc = load_col4(p.col4, g);
                 const double cj[NC] = {cc.x, cc.y, cc.z};
                 double zj[NWZ];
@@ -745,6 +790,10 @@ __global__ void __launch_bounds__(KC_THREADS, 4) blend_kernel(const GeneralParam
                 const bool finite_c = (cj[0] - cj[0] == 0.0) && (cj[1] - cj[1] == 0.0) && (cj[2] - cj[2] == 0.0);
                 if (!finite_c) pass = (P - i0 >= KC_IC) ? ((1u << KC_IC) - 1u) : ((1u << (P - i0)) - 1u);
                 if (pass == 0u) continue;
+                // the 64-byte feature record is fetched only now: at the reference's sigma almost every neighbour is cut by its
+                // colour terms alone, and its 32-byte colour record is then all that ever leaves L2
+                const float4 *r16 = p.rec16 + static_cast<size_t>(g) * 4;
+                const float4 f0 = __ldg(r16), f1 = __ldg(r16 + 1), f2 = __ldg(r16 + 2), f3 = __ldg(r16 + 3);
                 const float fs[16] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w, f2.x, f2.y, f2.z, f2.w, f3.x, f3.y, f3.z, f3.w};
 #pragma unroll
                 for (int k = 3; k < NWZ; ++k) {

@@ -151,7 +151,7 @@ __global__ void __launch_bounds__(KL_THREADS, 1) dependency_large_kernel(const G
                 const Rec16 r16 = load_rec16(p.rec16, g);
                 const double4 cc = load_col4(p.col4, g);
                 auto put = [&](int c, double x) {
-                    const int b = bin_value(x, c, ks, nb, dnb);
+                    const int b = bin_value(x, c, ks, nb, dnb, ks.tol[c]);
                     sc.bins[c * cs + m] = static_cast<uint16_t>(b);
                     atomicAdd(&marg[c * L.nbs + b], 1u);
                 };
