@@ -67,6 +67,14 @@ typedef struct rpf_config {
      * that overlap the interior rows. Results are bit-identical to n_gpus = 1. */
     int n_gpus;
     int device_ids[RPF_MAX_GPUS];
+    /* Channel layout: a sample record is position (2) | colour (3) | n_random random parameters |
+     * n_features features, and rpf_upload takes 5 + n_random + n_features planes in that order. 0 / 0 = the reference's
+     * record, 2 random parameters (pLens.xy) and 12 features (n0, p0, n1, p1; sd.h:46,62-94). This build also carries
+     * 5 / 12 (+ time and the light sample u, v as random parameters) and 5 / 15 (+ a texture colour as three more features);
+     * rpf_layout_supported tells. The wider layouts take the general path: box*box*spp <= 65,535 and spp < 16. Every formula
+     * is the reference's with the loop bounds SD_N_RANDOM / SD_N_FEATURES (sd.h:40-43) lifted to the layout's counts. */
+    int n_random;
+    int n_features;
     int max_box;  /* n_gpus > 1 only: largest box size rpf_filter will be given; every band keeps b_delta(max_box) halo
                      rows of all planes. 0 = 55 (north_star's schedule 55/35/17/7). */
 } rpf_config;
@@ -230,6 +238,13 @@ typedef struct rpf_kernel_times_t {
 int rpf_set_profiling(rpf_ctx *ctx, int on);
 int rpf_get_kernel_times(rpf_ctx *ctx, rpf_kernel_times_t *out);
 
+/* Channel layout of a context: planes rpf_upload expects (19 for the reference's record), MutualInformation pairs per pixel
+ * (n_features * (n_random + 2) + 3 * (n_random + 2 + n_features): 96 for the reference, rpf.cpp:416-442). ctx may be NULL:
+ * the reference layout. rpf_layout_supported: 1 if this build has kernels for the layout (0 / 0 = the reference's). */
+int rpf_num_channels(const rpf_ctx *ctx);
+int rpf_num_pairs(const rpf_ctx *ctx);
+int rpf_layout_supported(int n_random, int n_features);
+
 /* Largest neighbourhood (box*box*spp candidate samples) this build can filter, for error messages and tests. */
 int rpf_max_neighbourhood(void);
 /* Largest box*box*spp served by the fused shared-memory kernel (one CTA per pixel); larger neighbourhoods take the
@@ -242,6 +257,11 @@ int rpf_fused_max_candidates(void);
  * (x_off,y_off) shift the generator so a row band of a larger frame can be generated on its own. */
 int rpf_synth_planes(int width, int height, int spp, unsigned long long seed, int kind, int x_off, int y_off,
                      float *planes /* [19][width*height*spp] */);
+
+/* Same for a wider channel layout (rpf_config.n_random / n_features): planes [5 + n_random + n_features][width*height*spp].
+ * The 19 reference channels are those of rpf_synth_planes. kind 2 = kind 0 with every extra random parameter constant. */
+int rpf_synth_planes_layout(int width, int height, int spp, unsigned long long seed, int kind, int x_off, int y_off,
+                            int n_random, int n_features, float *planes);
 
 /* Feature-buffer files: lossless dump / load of what the integrator emits per sample, replacing
  * the lossy debug EXRs of visualizeSF (rpf.cpp:37-101). Host side only; layout in raytracer-rpf_b200/csrc/rpf_io.cpp. */

@@ -17,9 +17,24 @@
 
 namespace {
 
-constexpr int NCH = 19;
-constexpr int NF = 12, NC = 3, NR = 2, NP = 2;
-constexpr int CH_POS = 0, CH_COL = 2, CH_RND = 5, CH_FEAT = 7;  // sd.h:62-94
+// A sample record is position (2) | colour (3) | NR random parameters | NF features. The reference's SampleData is NR = 2
+// (pLens.xy), NF = 12 (n0, p0, n1, p1): sd.h:40-46,62-94. Every loop below runs over the layout's counts, so a wider
+// record (time and light samples as random parameters, a texture colour as features) is filtered by the
+// reference's formulas with SD_N_RANDOM / SD_N_FEATURES lifted -- there is no reference output for those, the default
+// layout is the one pinned against oracle/_ref.
+constexpr int NC = 3, NP = 2;
+constexpr int CH_POS = 0, CH_COL = 2, CH_RND = 5;
+constexpr int MAX_CH = 32, MAX_F = 27;
+struct Layout {
+    int NR = 2, NF = 12;
+    int NCH = 19, CH_FEAT = 7;
+    Layout() = default;
+    Layout(int nr, int nf) : NR(nr > 0 ? nr : 2), NF(nf > 0 ? nf : 12) {
+        NCH = NP + NC + NR + NF;
+        CH_FEAT = CH_RND + NR;
+    }
+    int pairs() const { return NF * (NR + NP) + NC * (NR + NP + NF); }
+};
 
 // mi.cpp:53-58: bins default to max(1,(int)sqrt(N))
 inline int bins_for(int n) {
@@ -72,7 +87,8 @@ struct ChannelBins {
 
 // mi.cpp:5-21 per channel, once per neighbourhood (the reference redoes this inside each of the
 // 96 MutualInformation calls with identical results).
-void bin_channels(const double *z /*[n][19]*/, int n, int bins, ChannelBins &cb) {
+void bin_channels(const double *z /*[n][NCH]*/, int n, int bins, ChannelBins &cb, const Layout &ly) {
+    const int NCH = ly.NCH;
     cb.bin.assign(static_cast<size_t>(NCH) * n, 0);
     cb.hist.assign(static_cast<size_t>(NCH) * bins, 0);
     std::vector<double> col(n);
@@ -92,10 +108,11 @@ void bin_channels(const double *z /*[n][19]*/, int n, int bins, ChannelBins &cb)
 // rpf.cpp:356-488. mi_log (optional, 96 doubles): every MutualInformation value in call order, which is
 // feature i against r0, r1, p0, p1 at 4*i + {0..3} (rpf.cpp:416-427), then colour i against r0, r1, p0, p1, f0..f11 at
 // 48 + 16*i + {0..15} (rpf.cpp:429-442).
-void cf_weights(const double *z, int n, int flags, double alpha[NC], double beta[NF], double &wrc,
-                ChannelBins &cb, std::vector<int> &joint, double eps = 0.0, double *mi_log = nullptr) {
+void cf_weights(const double *z, int n, int flags, double alpha[NC], double *beta /*[NF]*/, double &wrc,
+                ChannelBins &cb, std::vector<int> &joint, double eps = 0.0, double *mi_log = nullptr, const Layout &ly = Layout()) {
+    const int NR = ly.NR, NF = ly.NF, CH_FEAT = ly.CH_FEAT;
     const int bins = bins_for(n);
-    bin_channels(z, n, bins, cb);
+    bin_channels(z, n, bins, cb, ly);
     int calls = 0;
     auto MI = [&](int ca, int cbn) {
         const double v = mi_from_bins(&cb.bin[static_cast<size_t>(ca) * n], &cb.bin[static_cast<size_t>(cbn) * n],
@@ -105,7 +122,7 @@ void cf_weights(const double *z, int n, int flags, double alpha[NC], double beta
         ++calls;
         return v;
     };
-    double D_r_f[NF], D_p_f[NF], D_c_f[NF];
+    double D_r_f[MAX_F], D_p_f[MAX_F], D_c_f[MAX_F];
     double D_r_c[NC], D_p_c[NC], D_f_c[NC];
     for (int k = 0; k < NF; ++k) D_r_f[k] = D_p_f[k] = D_c_f[k] = 0;
     for (int k = 0; k < NC; ++k) D_r_c[k] = D_p_c[k] = D_f_c[k] = 0;
@@ -137,7 +154,7 @@ void cf_weights(const double *z, int n, int flags, double alpha[NC], double beta
         return (p2 && den == 0) ? 0.0 : num / den;
     };
     // rpf.cpp:461-466
-    double W_c_f[NF], W_r_f[NF], W_r_c[NC];
+    double W_c_f[MAX_F], W_r_f[MAX_F], W_r_c[NC];
     for (int i = 0; i < NF; ++i) {
         // verbatim reads D_f_ck[i], in bounds only for i<3; beyond that the reference is undefined
         // and this restatement reports NaN in verbatim mode.
@@ -159,9 +176,10 @@ namespace {
 
 struct Frame {
     int W, H, P;
-    const float *planes;  // [19][S]
+    const float *planes;  // [NCH][S]
     size_t S;
     const double *col_in; // [3][S] current iteration's input colours
+    Layout ly;
     double value(int c, size_t idx) const {
         if (c >= CH_COL && c < CH_COL + NC) return col_in[static_cast<size_t>(c - CH_COL) * S + idx];
         return static_cast<double>(planes[static_cast<size_t>(c) * S + idx]);
@@ -170,8 +188,8 @@ struct Frame {
 
 struct PixelScratch {
     std::vector<size_t> nbh;      // accepted sample indices in reference order
-    std::vector<double> raw;      // [n][19]
-    std::vector<double> z;        // [n][19]
+    std::vector<double> raw;      // [n][NCH]
+    std::vector<double> z;        // [n][NCH]
     std::vector<double> w;        // [P][n]
     ChannelBins cb;
     std::vector<int> joint;
@@ -193,9 +211,11 @@ struct Paper {
 int filter_pixel(const Frame &f, int px, int py, int box, double seed, int flags, const Subsample &sub, const Paper &paper, double *col_out,
                  PixelScratch &s, int *n_out, double *alpha_out, double *beta_out, double *wrc_out) {
     const int P = f.P, W = f.W, H = f.H;
+    const Layout &ly = f.ly;
+    const int NF = ly.NF, NCH = ly.NCH, CH_FEAT = ly.CH_FEAT;
     const size_t base = (static_cast<size_t>(py) * W + px) * P;
     // rpf.cpp:338-347 (FillMeanAndStddev) with ops.h:111-144: sequential sums, population sigma, no clamp
-    double mu[NF], sd3[NF];
+    double mu[MAX_F], sd3[MAX_F];
     for (int k = 0; k < NF; ++k) {
         double sum = 0, sq = 0;
         for (int i = 0; i < P; ++i) {
@@ -206,7 +226,7 @@ int filter_pixel(const Frame &f, int px, int py, int box, double seed, int flags
         mu[k] = sum / static_cast<double>(P);
         const double sd = std::sqrt(sq / static_cast<double>(P) - mu[k] * mu[k]);
         sd3[k] = sd * 3;  // rpf.cpp:579 multiplyArray(stdDev, 3)
-        const bool world_pos = (k >= 3 && k < 6) || k >= 9;  // p0, p1 of sd.h:62-94
+        const bool world_pos = (k >= 3 && k < 6) || (k >= 9 && k < 12);  // p0, p1 of sd.h:62-94
         if (world_pos && paper.pos_sigmas > 0) sd3[k] = sd * paper.pos_sigmas;
         if (paper.min_sigma > 0 && sd3[k] < paper.min_sigma) sd3[k] = paper.min_sigma;  // a NaN sigma stays NaN (accepts)
     }
@@ -237,7 +257,7 @@ int filter_pixel(const Frame &f, int px, int py, int box, double seed, int flags
     s.raw.resize(static_cast<size_t>(n) * NCH);
     for (int j = 0; j < n; ++j)
         for (int c = 0; c < NCH; ++c) s.raw[static_cast<size_t>(j) * NCH + c] = f.value(c, s.nbh[j]);
-    double M[NCH], SD[NCH];
+    double M[MAX_CH], SD[MAX_CH];
     for (int c = 0; c < NCH; ++c) {
         double sum = 0, sq = 0;
         for (int j = 0; j < n; ++j) {
@@ -257,11 +277,11 @@ int filter_pixel(const Frame &f, int px, int py, int box, double seed, int flags
             const size_t o = static_cast<size_t>(j) * NCH + c;
             s.z[o] = SD[c] == 0 ? 0 : (s.raw[o] - M[c]) / SD[c];
         }
-    double alpha[NC], beta[NF], wrc;
-    cf_weights(s.z.data(), n, flags, alpha, beta, wrc, s.cb, s.joint, paper.w_eps, s.mi_log);
+    double alpha[NC], beta[MAX_F], wrc;
+    cf_weights(s.z.data(), n, flags, alpha, beta, wrc, s.cb, s.joint, paper.w_eps, s.mi_log, ly);
     if (n_out) *n_out = n;
     if (alpha_out) std::memcpy(alpha_out, alpha, sizeof alpha);
-    if (beta_out) std::memcpy(beta_out, beta, sizeof beta);
+    if (beta_out) std::memcpy(beta_out, beta, NF * sizeof(double));
     if (wrc_out) *wrc_out = wrc;
     // rpf.cpp:531,662-664
     const double sigma_p = static_cast<double>(box / 4);  // integer division
@@ -328,7 +348,7 @@ extern "C" int rpf_oracle_filter(rpf_oracle_args *a) {
         const double seed = a->sigma_seeds ? a->sigma_seeds[it] : a->sigma_fc_seed;
         const bool last = it == a->n_iter - 1;
         nxt = cur;  // pixels outside the filtered window keep their colours
-        Frame f{W, H, P, a->planes, S, cur.data()};
+        Frame f{W, H, P, a->planes, S, cur.data(), Layout(a->n_random, a->n_features)};
         // 16x16 tiles handed out dynamically, like ParallelFor2D at rpf.cpp:542
         const int T = 16, tx = (x1 - x0 + T - 1) / T, ty = (y1 - y0 + T - 1) / T;
         std::atomic<int> next{0};
@@ -345,7 +365,7 @@ extern "C" int rpf_oracle_filter(rpf_oracle_args *a) {
                         nans += filter_pixel(f, x, y, box, seed, a->flags, sub, paper, nxt.data(), s,
                                              last && a->nbh_size ? a->nbh_size + p : nullptr,
                                              last && a->alpha ? a->alpha + p * 3 : nullptr,
-                                             last && a->beta ? a->beta + p * 12 : nullptr,
+                                             last && a->beta ? a->beta + p * Layout(a->n_random, a->n_features).NF : nullptr,
                                              last && a->wrc ? a->wrc + p : nullptr);
                     }
             }
@@ -433,17 +453,19 @@ extern "C" int rpf_oracle_pixel_probe(const rpf_oracle_args *a, int px, int py, 
     else
         for (int k = 0; k < 3; ++k)
             for (size_t i = 0; i < S; ++i) cur[k * S + i] = a->planes[(CH_COL + k) * S + i];
-    Frame f{W, H, P, a->planes, S, cur.data()};
+    Frame f{W, H, P, a->planes, S, cur.data(), Layout(a->n_random, a->n_features)};
     PixelScratch s;
-    double mi[96];
+    double mi[1024];
     s.mi_log = mi;
+    const Layout ly(a->n_random, a->n_features);
+    const int NCH = ly.NCH;
     Subsample sub;
     Paper paper;
     paper.w_eps = a->w_epsilon; paper.min_sigma = a->min_sigma; paper.pos_sigmas = a->world_pos_sigmas;
     int n = 0;
     filter_pixel(f, px, py, a->box_sizes[0], a->sigma_fc_seed, a->flags, sub, paper, out.data(), s, &n, nullptr, nullptr, nullptr);
     const int bins = bins_for(n);
-    if (mi96) std::memcpy(mi96, mi, sizeof mi);
+    if (mi96) std::memcpy(mi96, mi, ly.pairs() * sizeof(double));
     if (n_out) *n_out = n;
     if (bins_out) *bins_out = bins;
     if (marg) {

@@ -64,6 +64,10 @@ typedef struct rpf_oracle_args {
     double w_epsilon, min_sigma, world_pos_sigmas;
     const double *sigma_seeds;
     double hdr_clamp_sigmas;
+    /* Channel layout: position (2) | colour (3) | n_random random parameters | n_features features;
+     * planes holds 5 + n_random + n_features of them, beta has n_features entries per pixel. 0 / 0 = the reference's record
+     * (2 / 12, sd.h:40-46), the only layout with a reference output to pin against. */
+    int n_random, n_features;
 } rpf_oracle_args;
 
 /* returns 0 on success, <0 on bad arguments */
@@ -82,7 +86,7 @@ void rpf_oracle_cf_weights(const double *z, int n, int flags, double *alpha, dou
  * sigma of the spp samples; a sample with |c - mean| > k_sigmas * sigma in any channel takes the mean in all three. */
 void rpf_oracle_hdr_clamp(double *colors, int width, int height, int spp, int y0, int y1, double k_sigmas);
 
-/* Component view of one pixel of one pass (box_sizes[0]): the 96 MutualInformation values in the order of rpf.cpp:416-442,
+/* Component view of one pixel of one pass (box_sizes[0]): the MutualInformation values (96 for the reference layout) in the order of rpf.cpp:416-442,
  * N, bins (mi.cpp:53-58), the 19 marginal histograms [19][bins_cap] (mi.cpp:5-21) and optionally the normalised
  * neighbourhood z [n][19] (rpf.cpp:603-612) so a test can hand its columns to the reference's own MutualInformation. */
 int rpf_oracle_pixel_probe(const rpf_oracle_args *a, int px, int py, double *mi96, int *n_out, int *bins_out, int *marg,

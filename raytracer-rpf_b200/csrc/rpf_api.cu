@@ -11,22 +11,27 @@
 #include <string>
 #include <vector>
 
-#include "rpf_pixel_kernel.cuh"
-#include "rpf_general.cuh"
-#include "rpf_membership.cuh"
-#include "rpf_large.cuh"
-#include "rpf_blend_wide.cuh"
+#include "rpf_layouts.cuh"  // every kernel, once per channel layout
 
-using namespace rpf;
+using namespace rpf_types;
+
+struct rpf_ctx;
+// One channel layout = one compiled copy of the kernels (rpf_layouts.cuh) and of their launch code (rpf_launch.inl).
+struct LayoutOps {
+    int nr, nf, nch, n_joint, rec19;
+    int (*launch_rows)(rpf_ctx *, int box, double seed, int y0, int y1);
+    int (*configure)(rpf_ctx *);
+};
 
 struct rpf_ctx {
     rpf_config cfg{};
+    const LayoutOps *ops = nullptr;  // the context's channel layout (rpf_config.n_random / n_features)
     size_t S = 0;
     int npix = 0;
-    float *d_planes = nullptr;      // [19][S]
+    float *d_planes = nullptr;      // [nch][S]
     double *d_col[2] = {nullptr, nullptr};  // [3][S] each: current / next
     int cur = 0;
-    double *d_pstat = nullptr;      // [npix][24]
+    double *d_pstat = nullptr;      // [npix][2 nf]
     int pstat_y0 = 0, pstat_y1 = 0; // rows with valid per-pixel statistics
     double *d_gtab = nullptr, *d_gpre = nullptr, *d_hln = nullptr;
     unsigned long long *d_gq = nullptr, *d_hq = nullptr;
@@ -71,7 +76,7 @@ struct rpf_ctx {
     std::string err;
     long long probe_pixel = -1;     // rpf_set_debug_pixel
     double *d_probe_mi = nullptr;   // [98]
-    unsigned *d_probe_marg = nullptr;  // [19][PROBE_BINS]
+    unsigned *d_probe_marg = nullptr;  // [nch][PROBE_BINS]
     bool col4_valid = false;        // col4 / the colour slots of rec19 hold the CURRENT colours (general path, once per pass)
     // ---- row bands (rpf_bands.inl) ----
     std::vector<rpf_ctx *> shards;  // n_gpus > 1: this context is the parent of one child per device and owns no device memory
@@ -120,37 +125,6 @@ extern "C" int rpf_fused_max_candidates(void) {
     int v = kFusedDefaultMax;
     if (const char *e = getenv("RPF_FUSED_MAX")) v = atoi(e);
     return v < 0 ? 0 : (v > kFusedHardMax ? kFusedHardMax : v);
-}
-
-static bool plan_smem(long long ncap, int spp, int limit, SmemLayout &L) {
-    if (ncap > rpf_fused_max_candidates()) return false;
-    L.ncap = static_cast<int>(ncap);
-    L.nstride = L.ncap | 1;
-    const int nb = bins_for(L.ncap);
-    // words per lane of a joint histogram (4 u8 cells per word); also large enough for the exact path's
-    // contiguous u16 table of nb*nb+nb entries spread over the warp's 32 columns
-    L.wpl = (nb * nb + 3) / 4;
-    while (L.wpl * 128 < 2 * (nb * nb + nb)) ++L.wpl;
-    int off = 0;
-    L.off_idx = off; off = align16(off + 4 * L.ncap);
-    L.off_bins = off; off = align16(off + 20 * L.ncap);
-    L.off_gtab = off; off = align16(off + 8 * (L.ncap + 1));
-    L.off_small = off;
-    L.off_big = off;
-    const long long raw = 1ll * L.nstride * (NC * 8 + 16 * 4);
-    const long long wgt = 18ll * spp * 8;
-    for (int mw = 4; mw >= 1; mw >>= 1) {
-        // with four histogram warps the last one only holds the 19 marginals (nb cells per lane)
-        const long long hist = mw == 4 ? (3ll * L.wpl + (nb + 3) / 4) * 128 : 1ll * mw * L.wpl * 128;
-        long long big = raw > wgt ? raw : wgt;
-        if (hist > big) big = hist;
-        if (off + big <= limit) {
-            L.mi_warps = mw;
-            L.total = static_cast<int>(off + big);
-            return true;
-        }
-    }
-    return false;
 }
 
 static const int kSmemLimit = 227 * 1024 - 6 * 1024;  // minus static PixelSmall and the per-CTA reserve
@@ -244,7 +218,7 @@ static int ensure_gtab(rpf_ctx *ctx, int n) {
     if (n + 2 <= ctx->gtab_n) return RPF_OK;
     const int m = n + 2;
     std::vector<double> g(m), pre(m + 1), hln(m + 1);
-    const int mq = m > KB_GSM ? m : KB_GSM;
+    const int mq = m > rpf::KB_GSM ? m : rpf::KB_GSM;
     std::vector<unsigned long long> gq(mq, 0ull), hq(mq + 1, 0ull);  // fixed point, unit 2^-43 (rpf_general.cuh)
     for (int k = 0; k < m; ++k) {
         const long double a = k + 1, b = k;
@@ -272,10 +246,10 @@ static int ensure_gtab(rpf_ctx *ctx, int n) {
     ctx->d_gtab = ctx->d_gpre = ctx->d_hln = nullptr;
     ctx->d_gq = ctx->d_hq = nullptr;
     ctx->gtab_n = 0;
-    CU(ctx, cudaMalloc(&ctx->d_gtab, (m > KB_GSM ? m : KB_GSM) * sizeof(double)));
+    CU(ctx, cudaMalloc(&ctx->d_gtab, (m > rpf::KB_GSM ? m : rpf::KB_GSM) * sizeof(double)));
     CU(ctx, cudaMalloc(&ctx->d_gpre, (m + 1) * sizeof(double)));
     CU(ctx, cudaMalloc(&ctx->d_hln, (m + 1) * sizeof(double)));
-    CU(ctx, cudaMemset(ctx->d_gtab, 0, (m > KB_GSM ? m : KB_GSM) * sizeof(double)));
+    CU(ctx, cudaMemset(ctx->d_gtab, 0, (m > rpf::KB_GSM ? m : rpf::KB_GSM) * sizeof(double)));
     CU(ctx, cudaMemcpy(ctx->d_gtab, g.data(), m * sizeof(double), cudaMemcpyHostToDevice));
     CU(ctx, cudaMemcpy(ctx->d_gpre, pre.data(), (m + 1) * sizeof(double), cudaMemcpyHostToDevice));
     CU(ctx, cudaMemcpy(ctx->d_hln, hln.data(), (m + 1) * sizeof(double), cudaMemcpyHostToDevice));
@@ -288,6 +262,7 @@ static int ensure_gtab(rpf_ctx *ctx, int n) {
 }
 
 static int create_sharded(rpf_ctx **out, const rpf_config *cfg, int ndev);
+static const LayoutOps *find_layout(int n_random, int n_features);
 
 extern "C" int rpf_create(rpf_ctx **out, const rpf_config *cfg) {
     if (!out || !cfg) return fail(nullptr, RPF_ERR_INVALID, "rpf_create: null argument");
@@ -305,8 +280,13 @@ extern "C" int rpf_create(rpf_ctx **out, const rpf_config *cfg) {
     if (cudaGetDeviceProperties(&prop, cfg->device) != cudaSuccess || prop.major != 10)
         return fail(nullptr, RPF_ERR_NO_DEVICE, "rpf_create: device %d is not an sm_100 part (kernels are built for sm_100a only)",
                     cfg->device);
+    const LayoutOps *ops = find_layout(cfg->n_random, cfg->n_features);
+    if (!ops)
+        return fail(nullptr, RPF_ERR_UNSUPPORTED, "rpf_create: no kernels for %d random parameters and %d features in this build (layouts: "
+                    "2/12 = the reference's record, 5/12, 5/15; rpf_layouts.cuh)", cfg->n_random, cfg->n_features);
     rpf_ctx *ctx = new rpf_ctx;
     ctx->cfg = *cfg;
+    ctx->ops = ops;
     ctx->cfg.flags &= ~(RPF_FLAG_FORCE_GENERAL | RPF_FLAG_FORCE_LARGE);
     if (ctx->cfg.flags == 0) ctx->cfg.flags = RPF_FLAGS_DEFINED;
     ctx->S = 1ull * cfg->width * cfg->height * cfg->spp;
@@ -325,38 +305,29 @@ extern "C" int rpf_create(rpf_ctx **out, const rpf_config *cfg) {
     CUC(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     CUC(cudaEventCreate(&ctx->ev0));
     CUC(cudaEventCreate(&ctx->ev1));
-    CUC(cudaMalloc(&ctx->d_planes, NCH * ctx->S * sizeof(float)));
+    CUC(cudaMalloc(&ctx->d_planes, ops->nch * ctx->S * sizeof(float)));
     CUC(cudaMalloc(&ctx->d_col[0], 3 * ctx->S * sizeof(double)));
     CUC(cudaMalloc(&ctx->d_col[1], 3 * ctx->S * sizeof(double)));
-    CUC(cudaMalloc(&ctx->d_pstat, 24ull * ctx->npix * sizeof(double)));
+    CUC(cudaMalloc(&ctx->d_pstat, 2ull * ops->nf * ctx->npix * sizeof(double)));
     CUC(cudaMalloc(&ctx->d_counters, 4 * sizeof(unsigned long long)));
     if (cfg->debug) {
         CUC(cudaMalloc(&ctx->d_dbg_n, ctx->npix * sizeof(int)));
         CUC(cudaMalloc(&ctx->d_dbg_alpha, 3ull * ctx->npix * sizeof(double)));
-        CUC(cudaMalloc(&ctx->d_dbg_beta, 12ull * ctx->npix * sizeof(double)));
+        CUC(cudaMalloc(&ctx->d_dbg_beta, 1ull * ops->nf * ctx->npix * sizeof(double)));
         CUC(cudaMalloc(&ctx->d_dbg_wrc, 1ull * ctx->npix * sizeof(double)));
         CUC(cudaMemset(ctx->d_dbg_n, 0, ctx->npix * sizeof(int)));
     }
-    CUC(cudaFuncSetAttribute(rpf_pixel_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
-    CUC(cudaFuncSetAttribute(rpf_pixel_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
     {
-        cudaFuncAttributes fa;
-        CUC(cudaFuncGetAttributes(&fa, dependency_kernel<1024>));
-        ctx->kb_static_smem = static_cast<int>(fa.sharedSizeBytes);
-        CUC(cudaFuncSetAttribute(dependency_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 227 * 1024 - ctx->kb_static_smem - 1024));
-        CUC(cudaFuncSetAttribute(membership_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        CUC(cudaFuncSetAttribute(membership_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        CUC(cudaFuncSetAttribute(blend_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-        CUC(cudaFuncSetAttribute(dependency_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (228 * 1024) / 2 - ctx->kb_static_smem - 1024));
+        if (ops->configure(ctx) != RPF_OK) {
+            g_create_err = ctx->err;
+            rpf_destroy(ctx);
+            return RPF_ERR_CUDA;
+        }
         ctx->num_sms = prop.multiProcessorCount;
         CUC(cudaMalloc(&ctx->d_work, 2 * sizeof(unsigned int)));
         ctx->force_large = (cfg->flags & RPF_FLAG_FORCE_LARGE) || (getenv("RPF_FORCE_LARGE") && atoi(getenv("RPF_FORCE_LARGE")));
         ctx->force_general = ctx->force_large || (cfg->flags & RPF_FLAG_FORCE_GENERAL) ||
                              (getenv("RPF_FORCE_GENERAL") && atoi(getenv("RPF_FORCE_GENERAL")));
-        CUC(cudaFuncSetAttribute(dependency_large_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 227 * 1024 - ctx->kb_static_smem - 1024));
         if (const char *bw = getenv("RPF_BLEND_WIDE_MIN")) if (atoi(bw) > 0) ctx->blend_wide_min = atoi(bw);
         if (const char *mb = getenv("RPF_SCRATCH_MB")) if (atoll(mb) > 0) ctx->scratch_budget = static_cast<size_t>(atoll(mb)) << 20;
     }
@@ -373,7 +344,7 @@ extern "C" int rpf_create(rpf_ctx **out, const rpf_config *cfg) {
 
 static int after_upload(rpf_ctx *ctx) {
     const size_t n = 3 * ctx->S;
-    colors_to_f64_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_planes, ctx->S,
+    rpf::colors_to_f64_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_planes, ctx->S,
                                                                                           ctx->d_col[ctx->cur]);
     ctx->launches++;
     CU(ctx, cudaGetLastError());
@@ -390,7 +361,7 @@ extern "C" int rpf_upload(rpf_ctx *ctx, const float *const planes[RPF_NUM_CHANNE
         const size_t row = static_cast<size_t>(ctx->cfg.width) * ctx->cfg.spp;
         for (size_t g = 0; g < ctx->shards.size(); ++g) {
             const float *sub[RPF_NUM_CHANNELS];
-            for (int c = 0; c < NCH; ++c) {
+            for (int c = 0; c < ctx->ops->nch; ++c) {
                 if (!planes[c]) return fail(ctx, RPF_ERR_INVALID, "rpf_upload: plane %d is null", c);
                 sub[c] = planes[c] + ctx->shard_buf0[g] * row;
             }
@@ -401,7 +372,7 @@ extern "C" int rpf_upload(rpf_ctx *ctx, const float *const planes[RPF_NUM_CHANNE
         return RPF_OK;
     }
     CU(ctx, cudaSetDevice(ctx->cfg.device));
-    for (int c = 0; c < NCH; ++c) {
+    for (int c = 0; c < ctx->ops->nch; ++c) {
         if (!planes[c]) return fail(ctx, RPF_ERR_INVALID, "rpf_upload: plane %d is null", c);
         CU(ctx, cudaMemcpyAsync(ctx->d_planes + c * ctx->S, planes[c], ctx->S * sizeof(float), cudaMemcpyHostToDevice,
                                 ctx->stream));
@@ -413,7 +384,7 @@ extern "C" int rpf_upload_device(rpf_ctx *ctx, const float *const d_planes[RPF_N
     if (!ctx || !d_planes) return fail(ctx, RPF_ERR_INVALID, "rpf_upload_device: null argument");
     if (!ctx->shards.empty()) return fail(ctx, RPF_ERR_UNSUPPORTED, "rpf_upload_device: not available on a context sharded over several devices");
     CU(ctx, cudaSetDevice(ctx->cfg.device));
-    for (int c = 0; c < NCH; ++c) {
+    for (int c = 0; c < ctx->ops->nch; ++c) {
         if (!d_planes[c]) return fail(ctx, RPF_ERR_INVALID, "rpf_upload_device: plane %d is null", c);
         CU(ctx, cudaMemcpyAsync(ctx->d_planes + c * ctx->S, d_planes[c], ctx->S * sizeof(float),
                                 cudaMemcpyDeviceToDevice, ctx->stream));
@@ -435,7 +406,7 @@ extern "C" int rpf_reset_colors(rpf_ctx *ctx) {
     }
     CU(ctx, cudaSetDevice(ctx->cfg.device));
     const size_t n = 3 * ctx->S;
-    colors_to_f64_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_planes, ctx->S, ctx->d_col[ctx->cur]);
+    rpf::colors_to_f64_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_planes, ctx->S, ctx->d_col[ctx->cur]);
     ctx->launches++;
     CU(ctx, cudaGetLastError());
     ctx->col4_valid = false;
@@ -467,77 +438,10 @@ extern "C" int rpf_upload_colors_f64(rpf_ctx *ctx, const double *rgb) {
 // ---- general path (rpf_general.cuh) ----------------------------------------------------------------------
 static const int kGeneralMaxCandidates = 65535;  // u16 candidate numbers and histogram cells, u8 bins (nb <= 255)
 
-// Shared-memory plan of the dependency kernel for ncap = box*box*spp candidates. Two CTAs of 512 threads per SM when
-// one full-size histogram (the rare pixel that accepts every candidate) fits in half an SM's shared memory, else one CTA
-// of 1024 threads (box 55 at 8 spp: 355 vs 419 ms with two CTAs). Whatever is left
-// after the fixed tables goes to the histogram region (more slots = more warp teams); the bin bytes stay in shared
-// memory only if eight full-size histograms still fit beside them, otherwise they go to an L2-resident per-CTA scratch.
-static bool plan_general(long long ncap, int spp, int static_smem, GeneralPlan &L) {
-    if (ncap > kLargeMaxCandidates) return false;
-    L = GeneralPlan{};
-    L.ncap = static_cast<int>(ncap);
-    L.mw = ((L.ncap + 127) / 128) * 4;
-    // Beyond 65,535 candidates this kernel still serves every pixel whose ACCEPTED count N stays within 65,535 (u16
-    // cells, u8 bins): candidate numbers then go to a 32-bit list in HBM and the per-sample sizes are capped at 65,535.
-    L.idx_global = ncap > kGeneralMaxCandidates;
-    const int neff = L.idx_global ? kGeneralMaxCandidates : L.ncap;
-    L.nq = (neff + 3) / 4;
-    const int nb = bins_for(neff);
-    L.nbs = (nb + 3) & ~3;
-    L.hw = (((nb * nb + 1) / 2) + 3) & ~3;
-    L.off_gsm = 0;
-    L.off_marg = KB_GSM * 8;
-    L.off_region = align16(L.off_marg + NCH * L.nbs * 4);
-    L.kc_smem = spp * 18 * 8;
-    const int idx_bytes = L.idx_global ? 0 : align16(2 * L.ncap);
-    const int bins_bytes = NCH * L.nq * 4;
-    const int hist_bytes = L.hw * 4;
-    auto atleast = [&](int n) { const int h = n * hist_bytes; return h > idx_bytes ? h : idx_bytes; };
-    const int limit[2] = {(228 * 1024) / 2 - static_smem - 1024, 227 * 1024 - static_smem - 1024};
-    for (int v = 0; v < 2; ++v) {
-        const int avail = (limit[v] - L.off_region) & ~15;
-        if (avail < atleast(1)) continue;
-        L.nt = v == 0 ? 512 : 1024;
-        L.bins_in_smem = bins_bytes + atleast(8) <= avail;
-        // neighbourhoods whose CAPACITY does not fit (boxes 35 / 55) still mostly accept few enough samples: per-pixel choice
-        L.bins_dyn = !L.bins_in_smem && !L.idx_global && !(getenv("RPF_BINS_DYN") && atoi(getenv("RPF_BINS_DYN")) == 0);
-        const int region = L.bins_in_smem ? avail - bins_bytes : avail;
-        L.off_bins = L.bins_in_smem ? L.off_region + region : 0;
-        L.region_words = region / 4;
-        L.kb_smem = L.off_region + avail;
-        return true;
-    }
-    return false;
-}
-
-// Plan of dependency_large_kernel (rpf_large.cuh): one CTA of 1024 threads per SM; shared memory = small-count table,
-// 19 marginals, and everything else as the histogram region (u32 cells).
-static bool plan_large(long long ncap, int spp, int static_smem, GeneralPlan &L) {
-    if (ncap > kLargeMaxCandidates) return false;
-    L = GeneralPlan{};
-    L.large = 1;
-    L.ncap = static_cast<int>(ncap);
-    L.mw = ((L.ncap + 127) / 128) * 4;
-    L.nq = (L.ncap + 3) / 4;
-    const int nb = bins_for(L.ncap);
-    L.nbs = (nb + 3) & ~3;
-    L.off_gsm = 0;
-    L.off_marg = KB_GSM * 8;
-    L.off_region = align16(L.off_marg + NCH * L.nbs * 4);
-    L.kc_smem = spp * 18 * 8;
-    const int limit = 227 * 1024 - static_smem - 1024;
-    const int avail = (limit - L.off_region) & ~15;
-    if (avail < nb * 4 * 4) return false;
-    L.nt = KL_THREADS;
-    L.region_words = avail / 4;
-    L.kb_smem = L.off_region + avail;
-    return true;
-}
-
 // n ln n in units of 2^-38 for counts up to n (rpf_large.cuh)
 static int ensure_hql(rpf_ctx *ctx, int n) {
     if (n + 2 <= ctx->hql_n) return RPF_OK;
-    const int m = (n + 2 > KB_GSM ? n + 2 : KB_GSM) + 1;
+    const int m = (n + 2 > rpf::KB_GSM ? n + 2 : rpf::KB_GSM) + 1;
     std::vector<unsigned long long> h(m, 0ull);
     for (int k = 2; k < m; ++k) {
         const long double a = k;
@@ -565,225 +469,50 @@ static int ensure_buffer(rpf_ctx *ctx, T **ptr, size_t *have, size_t need) {
     return RPF_OK;
 }
 
-static int ensure_pstat(rpf_ctx *ctx, const FrameView &f, int y0, int y1) {
-    (void)y0; (void)y1;
-    if (ctx->pstat_y1 > ctx->pstat_y0) return RPF_OK;
-    // Features never change between iterations (rpf.cpp:715 writes colours only): computed once per upload, for EVERY
-    // row of the context (0.16 ms at 720p) -- callers may filter any rows in any order (rpf_filter_rows), and a cached
-    // interval merged across a gap would leave rows in between uninitialised.
-    const long long n = 1ll * ctx->cfg.height * ctx->cfg.width * NF;
-    prof_begin(ctx, RPF_K_PIXEL_STATS);
-    pixel_stats_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, ctx->stream>>>(f, 0, ctx->cfg.height, ctx->d_pstat, ctx->min_sigma,
-                                                                                         ctx->pos_sigmas);
-    prof_end(ctx);
-    ctx->launches++;
-    CU(ctx, cudaGetLastError());
-    ctx->pstat_y0 = 0;
-    ctx->pstat_y1 = ctx->cfg.height;
-    return RPF_OK;
+// ---- the launch code of every layout ------------------------------------------------------------------------------------------
+#define RPF_NS rpf
+#define RPF_NR 2
+#define RPF_NF 12
+#define RPF_FULL 1
+#include "rpf_launch.inl"
+#undef RPF_NS
+#undef RPF_NR
+#undef RPF_NF
+#undef RPF_FULL
+#define RPF_NS rpf_r5f12
+#define RPF_NR 5
+#define RPF_NF 12
+#define RPF_FULL 0
+#include "rpf_launch.inl"
+#undef RPF_NS
+#undef RPF_NR
+#undef RPF_NF
+#undef RPF_FULL
+#define RPF_NS rpf_r5f15
+#define RPF_NR 5
+#define RPF_NF 15
+#define RPF_FULL 0
+#include "rpf_launch.inl"
+#undef RPF_NS
+#undef RPF_NR
+#undef RPF_NF
+#undef RPF_FULL
+
+static const LayoutOps *const kLayouts[] = {&rpf::kOps, &rpf_r5f12::kOps, &rpf_r5f15::kOps};
+
+static const LayoutOps *find_layout(int n_random, int n_features) {
+    if (n_random == 0) n_random = 2;      // 0 = the reference's record (sd.h:46)
+    if (n_features == 0) n_features = 12;
+    for (const LayoutOps *o : kLayouts)
+        if (o->nr == n_random && o->nf == n_features) return o;
+    return nullptr;
 }
 
-static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
-    GeneralParams p{};
-    const long long ncap = 1ll * box * box * ctx->cfg.spp;
-    // Up to 65,535 candidates: dependency_kernel. Beyond: dependency_kernel for the pixels that accept at most 65,535
-    // samples and dependency_large_kernel (plan pl_large) for the rest. RPF_FLAG_FORCE_LARGE: the large kernel only.
-    GeneralPlan pl_large{};
-    bool use_small = !ctx->force_large && plan_general(ncap, ctx->cfg.spp, ctx->kb_static_smem, p.pl);
-    const bool use_large = (!use_small || p.pl.idx_global) && plan_large(ncap, ctx->cfg.spp, ctx->kb_static_smem, pl_large);
-    if (use_small && p.pl.idx_global && !use_large) use_small = false;
-    if (!use_small && !use_large)
-        return fail(ctx, RPF_ERR_UNSUPPORTED, "neighbourhood of box %d x %d spp = %lld candidates exceeds this build (max %d)", box,
-                    ctx->cfg.spp, ncap, kLargeMaxCandidates);
-    if (!use_small) p.pl = pl_large;
-    if ((KW_THREADS * KW_ZS + ctx->cfg.spp * 18) * 8 > 100 * 1024) return fail(ctx, RPF_ERR_UNSUPPORTED, "spp %d too large for the blend kernel", ctx->cfg.spp);
-    int rc = RPF_OK;
-    if (use_large) rc = ensure_hql(ctx, pl_large.ncap);
-    if (rc == RPF_OK && use_small) rc = ensure_gtab(ctx, p.pl.idx_global ? kGeneralMaxCandidates : p.pl.ncap);
-    if (rc != RPF_OK) return rc;
-    p.f = FrameView{ctx->d_planes, ctx->S, ctx->cfg.width, ctx->cfg.height, ctx->cfg.spp};
-    rc = ensure_pstat(ctx, p.f, y0, y1);
-    if (rc != RPF_OK) return rc;
-    const int W = ctx->cfg.width;
-    const size_t per_pixel = static_cast<size_t>(p.pl.mw) * 4 + REC_DOUBLES * 8;
-    long long rows = static_cast<long long>(ctx->scratch_budget / (per_pixel * W));
-    if (rows < 1) rows = 1;
-    if (rows > y1 - y0) rows = y1 - y0;
-    const long long chunk_px = rows * W;
-    auto grid_for = [&](GeneralPlan &L) -> int {
-        int occ = 0;
-        cudaError_t e;
-        if (L.large) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dependency_large_kernel, KL_THREADS, L.kb_smem);
-        else if (L.nt == 512) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dependency_kernel<512>, 512, L.kb_smem);
-        else e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dependency_kernel<1024>, 1024, L.kb_smem);
-        if (e != cudaSuccess || occ < 1) return 0;
-        L.kb_grid = static_cast<int>(chunk_px < 1ll * occ * ctx->num_sms ? chunk_px : 1ll * occ * ctx->num_sms);
-        return L.kb_grid;
-    };
-    if (!grid_for(p.pl) || (use_small && use_large && !grid_for(pl_large)))
-        return fail(ctx, RPF_ERR_CUDA, "dependency kernel does not fit on an SM with %d bytes of shared memory", p.pl.kb_smem);
-    if ((rc = ensure_buffer(ctx, &ctx->d_mask, &ctx->mask_bytes, static_cast<size_t>(chunk_px) * p.pl.mw * 4)) != RPF_OK) return rc;
-    if ((rc = ensure_buffer(ctx, &ctx->d_rec, &ctx->rec_bytes, static_cast<size_t>(chunk_px) * REC_DOUBLES * 8)) != RPF_OK) return rc;
-    // big_scratch per persistent CTA: the large kernel keeps 4 B candidate number + 19 u16 bins per candidate (rows padded
-    // to 4); dependency_kernel beyond 65,535 candidates keeps its 32-bit candidate list there
-    const GeneralPlan &PL = use_large ? (use_small ? pl_large : p.pl) : p.pl;
-    size_t big_stride = 0;
-    int big_grid = 0;
-    if (use_large) { big_stride = static_cast<size_t>(PL.nq) * 168; big_grid = PL.kb_grid; }
-    if (use_small && p.pl.idx_global) {
-        const size_t st = (static_cast<size_t>(p.pl.ncap) * 4 + 15) & ~static_cast<size_t>(15);
-        if (st > big_stride) big_stride = st;
-        if (p.pl.kb_grid > big_grid) big_grid = p.pl.kb_grid;
-    }
-    p.big_stride = big_stride;
-    if (big_stride && (rc = ensure_buffer(ctx, &ctx->d_big, &ctx->big_bytes, static_cast<size_t>(big_grid) * big_stride)) != RPF_OK) return rc;
-    if (use_small && !p.pl.bins_in_smem &&
-        (rc = ensure_buffer(ctx, &ctx->d_bins, &ctx->bins_bytes, static_cast<size_t>(p.pl.kb_grid) * NCH * p.pl.nq * 4)) != RPF_OK)
-        return rc;
-    if (!ctx->d_rec16) {
-        CU(ctx, cudaMalloc(&ctx->d_rec16, ctx->S * 4 * sizeof(float4)));
-        CU(ctx, cudaMalloc(&ctx->d_col4, ctx->S * sizeof(double4)));
-        CU(ctx, cudaMalloc(&ctx->d_rec19, ctx->S * REC19 * sizeof(double)));
-    }
-    if (!ctx->rec16_valid) {
-        pack_features_kernel<<<static_cast<unsigned>((4 * ctx->S + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_planes, ctx->S, ctx->d_rec16);
-        pack_rec19_kernel<<<static_cast<unsigned>((ctx->S * REC19 + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_planes, ctx->S, ctx->d_rec19);
-        ctx->launches += 2;
-        ctx->rec16_valid = true;
-    }
-    if (!ctx->col4_valid) {  // once per pass, however many row ranges the pass is launched in (band edges first, then the interior)
-        pack_colors_kernel<<<static_cast<unsigned>((ctx->S + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_col[ctx->cur], ctx->S, ctx->d_col4, ctx->d_rec19);
-        ctx->launches++;
-        CU(ctx, cudaGetLastError());
-        ctx->col4_valid = true;
-    }
-    p.rec16 = ctx->d_rec16;
-    p.col4 = ctx->d_col4;
-    p.rec19 = ctx->d_rec19;
-    p.col_in = ctx->d_col[ctx->cur];
-    p.col_out = ctx->d_col[ctx->cur ^ 1];
-    p.pstat = ctx->d_pstat;
-    p.gq = ctx->d_gq;
-    p.hq = p.pl.large ? ctx->d_hql : ctx->d_hq;
-    p.large_min_n = 0;
-    p.big_scratch = ctx->d_big;
-    p.box = box;
-    p.cd = make_cand_decode(box, ctx->cfg.spp);
-    p.flags = ctx->cfg.flags;
-    p.seed = seed;
-    p.w_eps = ctx->w_eps;
-    p.mask = ctx->d_mask;
-    p.rec = ctx->d_rec;
-    p.bins_scratch = ctx->d_bins;
-    p.work_counter = ctx->d_work;
-    p.dbg_n = ctx->d_dbg_n;
-    p.dbg_alpha = ctx->d_dbg_alpha;
-    p.dbg_beta = ctx->d_dbg_beta;
-    p.dbg_wrc = ctx->d_dbg_wrc;
-    p.counters = ctx->d_counters;
-    p.probe = DebugProbe{ctx->d_probe_mi ? ctx->probe_pixel : -1, ctx->d_probe_mi, ctx->d_probe_marg};
-    for (int r0 = y0; r0 < y1; r0 += static_cast<int>(rows)) {
-        p.row0 = r0;
-        p.nrows = r0 + rows <= y1 ? static_cast<int>(rows) : y1 - r0;
-        const unsigned npx = static_cast<unsigned>(p.nrows * W);
-        CU(ctx, cudaMemsetAsync(ctx->d_work, 0, 2 * sizeof(unsigned int), ctx->stream));
-        {
-            MembershipParams m{};
-            m.f = p.f;
-            m.pstat = ctx->d_pstat;
-            m.mask = ctx->d_mask;
-            m.box = box;
-            m.row0 = p.row0;
-            m.nrows = p.nrows;
-            m.mw = p.pl.mw;
-            m.sub = ctx->sub;
-            membership_tile(box, m.tx, m.ty);
-            m.tiles_x = (W + m.tx - 1) / m.tx;
-            m.col_rows = m.ty + box - 1;
-            const size_t row_bytes = (static_cast<size_t>(ctx->cfg.spp) * NF + 2) * sizeof(double);
-            m.rb_rows = m.col_rows;
-            const size_t memb_kb = getenv("RPF_MEMB_SMEM_KB") ? static_cast<size_t>(atoi(getenv("RPF_MEMB_SMEM_KB"))) : 40;  // 40 KB per CTA: five CTAs per SM (82 vs 87 ms at box 55)
-            while (m.rb_rows > 1 && m.rb_rows * row_bytes > memb_kb * 1024) m.rb_rows = (m.rb_rows + 1) / 2;
-            const unsigned tiles = static_cast<unsigned>(m.tiles_x) * static_cast<unsigned>((p.nrows + m.ty - 1) / m.ty);
-            prof_begin(ctx, RPF_K_MEMBERSHIP);
-            if (m.sub.keep_q24 < RPF_SUBSAMPLE_ALL) membership_kernel<true><<<tiles, m.tx * m.ty, m.rb_rows * row_bytes, ctx->stream>>>(m);
-            else membership_kernel<false><<<tiles, m.tx * m.ty, m.rb_rows * row_bytes, ctx->stream>>>(m);
-            prof_end(ctx);
-        }
-        prof_begin(ctx, RPF_K_ORDERED_STATS);
-        ordered_stats_kernel<<<(npx + KO_WARPS - 1) / KO_WARPS, KO_WARPS * 32, 0, ctx->stream>>>(p);
-        prof_end(ctx);
-        const unsigned gridb = npx < static_cast<unsigned>(p.pl.kb_grid) ? npx : static_cast<unsigned>(p.pl.kb_grid);
-        prof_begin(ctx, RPF_K_DEPENDENCY);
-        if (p.pl.large) dependency_large_kernel<<<gridb, KL_THREADS, p.pl.kb_smem, ctx->stream>>>(p);
-        else if (p.pl.nt == 512) dependency_kernel<512><<<gridb, 512, p.pl.kb_smem, ctx->stream>>>(p);
-        else dependency_kernel<1024><<<gridb, 1024, p.pl.kb_smem, ctx->stream>>>(p);
-        if (use_small && use_large) {  // the pixels dependency_kernel left: more than 65,535 accepted samples
-            GeneralParams q = p;
-            q.pl = pl_large;
-            q.hq = ctx->d_hql;
-            q.large_min_n = kGeneralMaxCandidates + 1;
-            q.work_counter = ctx->d_work + 1;
-            const unsigned gridl = npx < static_cast<unsigned>(pl_large.kb_grid) ? npx : static_cast<unsigned>(pl_large.kb_grid);
-            dependency_large_kernel<<<gridl, KL_THREADS, pl_large.kb_smem, ctx->stream>>>(q);
-            ctx->launches++;
-        }
-        prof_end(ctx);
-        prof_begin(ctx, RPF_K_BLEND);
-        // few samples per pixel: a thread per neighbour with the own samples' accumulators in registers; many: own samples
-        // across threads, neighbours staged through shared memory (rpf_blend_wide.cuh)
-        if (ctx->cfg.spp >= ctx->blend_wide_min) blend_wide_kernel<<<npx, KW_THREADS, (KW_THREADS * KW_ZS + ctx->cfg.spp * 18) * 8, ctx->stream>>>(p);
-        else blend_kernel<<<npx, KC_THREADS, p.pl.kc_smem, ctx->stream>>>(p);
-        prof_end(ctx);
-        ctx->launches += 4;
-        CU(ctx, cudaGetLastError());
-    }
-    ctx->pixels_filtered += 1ll * (y1 - y0) * W;
-    return RPF_OK;
-}
+static int launch_rows(rpf_ctx *ctx, int box, double seed, int y0, int y1) { return ctx->ops->launch_rows(ctx, box, seed, y0, y1); }
 
-static int launch_rows(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
-    if (!ctx->uploaded) return fail(ctx, RPF_ERR_STATE, "rpf_filter: no samples uploaded");
-    if (box < 1 || (box & 1) == 0) return fail(ctx, RPF_ERR_INVALID, "box size %d must be odd and positive (rpf.cpp:561)", box);
-    if (y0 < 0 || y1 > ctx->cfg.height || y0 >= y1) return fail(ctx, RPF_ERR_INVALID, "bad row range [%d,%d)", y0, y1);
-    if (!(seed > 0.0)) return fail(ctx, RPF_ERR_INVALID, "sigma_fc_seed must be positive");
-    FilterParams p{};
-    // the fused shared-memory-resident kernel serves small neighbourhoods; everything else takes the general path
-    if (ctx->force_general || !plan_smem(1ll * box * box * ctx->cfg.spp, ctx->cfg.spp, ctx->max_dyn_smem, p.sm))
-        return launch_general(ctx, box, seed, y0, y1);
-    int rc = ensure_gtab(ctx, p.sm.ncap);
-    if (rc != RPF_OK) return rc;
-    p.f = FrameView{ctx->d_planes, ctx->S, ctx->cfg.width, ctx->cfg.height, ctx->cfg.spp};
-    rc = ensure_pstat(ctx, p.f, y0, y1);
-    if (rc != RPF_OK) return rc;
-    p.col_in = ctx->d_col[ctx->cur];
-    p.col_out = ctx->d_col[ctx->cur ^ 1];
-    p.pstat = ctx->d_pstat;
-    p.gtab = ctx->d_gtab;
-    p.gpre = ctx->d_gpre;
-    p.box = box;
-    p.y0 = y0;
-    p.y1 = y1;
-    p.flags = ctx->cfg.flags;
-    p.seed = seed;
-    p.w_eps = ctx->w_eps;
-    p.dbg_n = ctx->d_dbg_n;
-    p.dbg_alpha = ctx->d_dbg_alpha;
-    p.dbg_beta = ctx->d_dbg_beta;
-    p.dbg_wrc = ctx->d_dbg_wrc;
-    p.counters = ctx->d_counters;
-    p.probe = DebugProbe{ctx->d_probe_mi ? ctx->probe_pixel : -1, ctx->d_probe_mi, ctx->d_probe_marg};
-    p.sub = ctx->sub;
-    const unsigned grid = static_cast<unsigned>((y1 - y0) * ctx->cfg.width);
-    prof_begin(ctx, RPF_K_FUSED);
-    if (p.sub.keep_q24 < RPF_SUBSAMPLE_ALL) rpf_pixel_kernel<true><<<grid, THREADS, p.sm.total, ctx->stream>>>(p);
-    else rpf_pixel_kernel<false><<<grid, THREADS, p.sm.total, ctx->stream>>>(p);
-    prof_end(ctx);
-    ctx->launches++;
-    CU(ctx, cudaGetLastError());
-    ctx->pixels_filtered += grid;
-    return RPF_OK;
-}
+extern "C" int rpf_num_channels(const rpf_ctx *ctx) { return ctx && ctx->ops ? ctx->ops->nch : RPF_NUM_CHANNELS; }
+extern "C" int rpf_num_pairs(const rpf_ctx *ctx) { return ctx && ctx->ops ? ctx->ops->n_joint : 96; }
+extern "C" int rpf_layout_supported(int n_random, int n_features) { return find_layout(n_random, n_features) != nullptr; }
 
 static int finish_timing(rpf_ctx *ctx) {
     if (ctx->timing_pending) {
@@ -860,7 +589,7 @@ extern "C" int rpf_hdr_clamp(rpf_ctx *ctx, double k_sigmas, int y0, int y1) {
     ctx->col4_valid = false;
     CU(ctx, cudaSetDevice(ctx->cfg.device));
     const long long n = 1ll * (y1 - y0) * ctx->cfg.width;
-    hdr_clamp_kernel<<<static_cast<unsigned>((n + 127) / 128), 128, 0, ctx->stream>>>(ctx->d_col[ctx->cur], ctx->S, ctx->cfg.width,
+    rpf::hdr_clamp_kernel<<<static_cast<unsigned>((n + 127) / 128), 128, 0, ctx->stream>>>(ctx->d_col[ctx->cur], ctx->S, ctx->cfg.width,
                                                                                       ctx->cfg.spp, y0, y1, k_sigmas);
     ctx->launches++;
     CU(ctx, cudaGetLastError());
@@ -1002,7 +731,7 @@ extern "C" int rpf_download_colors(rpf_ctx *ctx, float *r, float *g, float *b) {
             CU(ctx, cudaSetDevice(c->cfg.device));
             float *tmp = reinterpret_cast<float *>(c->d_col[c->cur ^ 1]);
             const size_t n3 = 3 * c->S;
-            colors_to_f32_kernel<<<static_cast<unsigned>((n3 + 255) / 256), 256, 0, c->stream>>>(c->d_col[c->cur], n3, tmp);
+            rpf::colors_to_f32_kernel<<<static_cast<unsigned>((n3 + 255) / 256), 256, 0, c->stream>>>(c->d_col[c->cur], n3, tmp);
             c->launches++;
             CU(ctx, cudaGetLastError());
             const size_t lo = static_cast<size_t>(ctx->shard_own0[s] - ctx->shard_buf0[s]) * row, n = static_cast<size_t>(ctx->shard_own0[s + 1] - ctx->shard_own0[s]) * row;
@@ -1016,7 +745,7 @@ extern "C" int rpf_download_colors(rpf_ctx *ctx, float *r, float *g, float *b) {
     // the "next" colour buffer is dead between passes: use its first 3*S floats as conversion scratch
     float *tmp = reinterpret_cast<float *>(ctx->d_col[ctx->cur ^ 1]);
     const size_t n = 3 * ctx->S;
-    colors_to_f32_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_col[ctx->cur], n, tmp);
+    rpf::colors_to_f32_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_col[ctx->cur], n, tmp);
     ctx->launches++;
     CU(ctx, cudaGetLastError());
     float *dst[3] = {r, g, b};
@@ -1038,7 +767,7 @@ extern "C" int rpf_download_debug(rpf_ctx *ctx, int *nbh, double *alpha, double 
                          n = static_cast<size_t>(ctx->shard_own0[g + 1] - ctx->shard_own0[g]) * W;
             if (nbh) CU(ctx, cudaMemcpyAsync(nbh + go, c->d_dbg_n + lo, n * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
             if (alpha) CU(ctx, cudaMemcpyAsync(alpha + 3 * go, c->d_dbg_alpha + 3 * lo, 3 * n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
-            if (beta) CU(ctx, cudaMemcpyAsync(beta + 12 * go, c->d_dbg_beta + 12 * lo, 12 * n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+            if (beta) CU(ctx, cudaMemcpyAsync(beta + ctx->ops->nf * go, c->d_dbg_beta + ctx->ops->nf * lo, ctx->ops->nf * n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
             if (wrc) CU(ctx, cudaMemcpyAsync(wrc + go, c->d_dbg_wrc + lo, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
         }
         return rpf_synchronize(ctx);
@@ -1048,7 +777,7 @@ extern "C" int rpf_download_debug(rpf_ctx *ctx, int *nbh, double *alpha, double 
     const size_t n = ctx->npix;
     if (nbh) CU(ctx, cudaMemcpyAsync(nbh, ctx->d_dbg_n, n * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
     if (alpha) CU(ctx, cudaMemcpyAsync(alpha, ctx->d_dbg_alpha, 3 * n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
-    if (beta) CU(ctx, cudaMemcpyAsync(beta, ctx->d_dbg_beta, 12 * n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    if (beta) CU(ctx, cudaMemcpyAsync(beta, ctx->d_dbg_beta, ctx->ops->nf * n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     if (wrc) CU(ctx, cudaMemcpyAsync(wrc, ctx->d_dbg_wrc, n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     return rpf_synchronize(ctx);
 }
@@ -1062,11 +791,11 @@ extern "C" int rpf_set_debug_pixel(rpf_ctx *ctx, int x, int y) {
     if (x >= ctx->cfg.width || y >= ctx->cfg.height) return fail(ctx, RPF_ERR_INVALID, "rpf_set_debug_pixel: (%d,%d) outside the context", x, y);
     CU(ctx, cudaSetDevice(ctx->cfg.device));
     if (!ctx->d_probe_mi) {
-        CU(ctx, cudaMalloc(&ctx->d_probe_mi, (N_JOINT + 2) * sizeof(double)));
-        CU(ctx, cudaMalloc(&ctx->d_probe_marg, NCH * PROBE_BINS * sizeof(unsigned)));
+        CU(ctx, cudaMalloc(&ctx->d_probe_mi, (ctx->ops->n_joint + 2) * sizeof(double)));
+        CU(ctx, cudaMalloc(&ctx->d_probe_marg, ctx->ops->nch * PROBE_BINS * sizeof(unsigned)));
     }
-    CU(ctx, cudaMemsetAsync(ctx->d_probe_mi, 0, (N_JOINT + 2) * sizeof(double), ctx->stream));
-    CU(ctx, cudaMemsetAsync(ctx->d_probe_marg, 0, NCH * PROBE_BINS * sizeof(unsigned), ctx->stream));
+    CU(ctx, cudaMemsetAsync(ctx->d_probe_mi, 0, (ctx->ops->n_joint + 2) * sizeof(double), ctx->stream));
+    CU(ctx, cudaMemsetAsync(ctx->d_probe_marg, 0, ctx->ops->nch * PROBE_BINS * sizeof(unsigned), ctx->stream));
     ctx->probe_pixel = static_cast<long long>(y) * ctx->cfg.width + x;
     return RPF_OK;
 }
@@ -1078,17 +807,18 @@ extern "C" int rpf_download_debug_mi(rpf_ctx *ctx, double *mi, int *n, int *bins
     CU(ctx, cudaSetDevice(ctx->cfg.device));
     int rc = rpf_synchronize(ctx);
     if (rc != RPF_OK) return rc;
-    double h[N_JOINT + 2];
-    CU(ctx, cudaMemcpy(h, ctx->d_probe_mi, sizeof h, cudaMemcpyDeviceToHost));
-    if (mi) memcpy(mi, h, N_JOINT * sizeof(double));
-    const int nb = static_cast<int>(h[N_JOINT + 1]);
-    if (n) *n = static_cast<int>(h[N_JOINT]);
+    const int nj = ctx->ops->n_joint;
+    std::vector<double> h(nj + 2);
+    CU(ctx, cudaMemcpy(h.data(), ctx->d_probe_mi, h.size() * sizeof(double), cudaMemcpyDeviceToHost));
+    if (mi) memcpy(mi, h.data(), nj * sizeof(double));
+    const int nb = static_cast<int>(h[nj + 1]);
+    if (n) *n = static_cast<int>(h[nj]);
     if (bins) *bins = nb;
     if (marginals) {
         if (bins_cap < nb) return fail(ctx, RPF_ERR_INVALID, "rpf_download_debug_mi: %d bins, room for %d", nb, bins_cap);
-        std::vector<unsigned> m(NCH * PROBE_BINS);
+        std::vector<unsigned> m(ctx->ops->nch * PROBE_BINS);
         CU(ctx, cudaMemcpy(m.data(), ctx->d_probe_marg, m.size() * sizeof(unsigned), cudaMemcpyDeviceToHost));
-        for (int c = 0; c < NCH; ++c)
+        for (int c = 0; c < ctx->ops->nch; ++c)
             for (int i = 0; i < bins_cap; ++i) marginals[c * bins_cap + i] = i < nb ? m[c * PROBE_BINS + i] : 0u;
     }
     return RPF_OK;
@@ -1100,7 +830,7 @@ extern "C" int rpf_reconstruct_box(rpf_ctx *ctx, float *rgb) {
     CU(ctx, cudaSetDevice(ctx->cfg.device));
     float *tmp = reinterpret_cast<float *>(ctx->d_col[ctx->cur ^ 1]);
     const int n = ctx->npix * 3;
-    reconstruct_box_kernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(ctx->d_col[ctx->cur], ctx->S, ctx->npix, ctx->cfg.spp, tmp);
+    rpf::reconstruct_box_kernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(ctx->d_col[ctx->cur], ctx->S, ctx->npix, ctx->cfg.spp, tmp);
     ctx->launches++;
     CU(ctx, cudaGetLastError());
     CU(ctx, cudaMemcpyAsync(rgb, tmp, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
@@ -1123,7 +853,7 @@ extern "C" int rpf_reconstruct_film(rpf_ctx *ctx, const rpf_film_desc *film, con
         CU(ctx, cudaMalloc(&own, need));
         scratch = own;
     }
-    FilmParams p{};
+    rpf::FilmParams p{};
     p.planes = ctx->d_planes;
     p.col = ctx->d_col[ctx->cur];
     p.S = ctx->S;
@@ -1141,7 +871,7 @@ extern "C" int rpf_reconstruct_film(rpf_ctx *ctx, const rpf_film_desc *film, con
     }
     if (e == cudaSuccess) {
         const unsigned n = static_cast<unsigned>(pw * ph);
-        film_reconstruct_kernel<<<(n + 127) / 128, 128, 0, ctx->stream>>>(p);
+        rpf::film_reconstruct_kernel<<<(n + 127) / 128, 128, 0, ctx->stream>>>(p);
         ctx->launches++;
         e = cudaGetLastError();
     }
@@ -1329,9 +1059,9 @@ extern "C" int rpf_debug_phase_cycles(rpf_ctx *ctx, unsigned long long *out8) {
     if (!ctx || !out8) return RPF_ERR_INVALID;
     int rc = rpf_synchronize(ctx);
     if (rc != RPF_OK) return rc;
-    CU(ctx, cudaMemcpyFromSymbol(out8, g_phase_cycles, 8 * sizeof(unsigned long long)));
+    CU(ctx, cudaMemcpyFromSymbol(out8, rpf::g_phase_cycles, 8 * sizeof(unsigned long long)));
     unsigned long long z[8] = {};
-    CU(ctx, cudaMemcpyToSymbol(g_phase_cycles, z, sizeof z));
+    CU(ctx, cudaMemcpyToSymbol(rpf::g_phase_cycles, z, sizeof z));
     return RPF_OK;
 }
 #endif

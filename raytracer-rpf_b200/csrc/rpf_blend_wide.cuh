@@ -8,10 +8,9 @@
 // i (up to 64 at a time) and every TQ-th neighbour of the chunk, reads it from shared memory (a broadcast among the
 // threads of one neighbour) and keeps four accumulators. 64 registers, four CTAs per SM. The sums over q are folded in
 // a fixed order, so the result is reproducible. Same weight arithmetic as blend_kernel.
-#pragma once
-#include "rpf_general.cuh"
+// Reference layout only (RPF_FULL in rpf_layouts.cuh): wider channel layouts take the general path.
 
-namespace rpf {
+namespace RPF_NS {
 
 constexpr int KW_THREADS = 256, KW_SEG_WORDS = 128;
 constexpr int KW_ZS = 21;  // doubles per staged neighbour: 17 scaled channels + 3 raw colours + 1 pad (odd: bank spread)
@@ -27,7 +26,7 @@ __global__ void __launch_bounds__(KW_THREADS, 4) blend_wide_kernel(const General
     const int tid = threadIdx.x;
     const int W = p.f.W, H = p.f.H, P = p.f.P, B = p.box;
     const size_t S = p.f.S;
-    const int pl = blockIdx.x;
+    const int pl = strip_order(blockIdx.x, p.f.W, p.nrows);
     const int py = p.row0 + pl / W, px = pl - (pl / W) * W;
     const size_t pix = static_cast<size_t>(py) * W + px;
     const uint32_t base = static_cast<uint32_t>(pix * P);
@@ -159,4 +158,4 @@ __global__ void __launch_bounds__(KW_THREADS, 4) blend_wide_kernel(const General
     }
 }
 
-}  // namespace rpf
+}  // namespace RPF_NS

@@ -15,13 +15,14 @@
 // mean and sigma (ops.h:111-144), whose rounding decides bin boundaries -- is done in KA by one lane per channel
 // walking the accepted samples in that order (ordered_stats_kernel); everything else is order independent (integer counts) or differs
 // from the CPU at the 1e-15 level (sums of logs, sums of weights).
-#pragma once
-#include "rpf_kernels.cuh"
+// RE-INCLUDABLE (once per channel layout, rpf_layouts.cuh).
 
-namespace rpf {
+namespace RPF_NS {
 
-constexpr int REC_M = 0, REC_SD = 19, REC_RLO = 38, REC_RHI = 57, REC_N = 76, REC_ALPHA = 77, REC_BETA = 80, REC_WRC = 92;
-constexpr int REC_DOUBLES = 96;  // per-pixel record in HBM scratch
+// per-pixel record in HBM scratch: M, SD, raw min, raw max of every channel, N, alpha[3], beta[NF], W_r_c
+constexpr int REC_M = 0, REC_SD = NCH, REC_RLO = 2 * NCH, REC_RHI = 3 * NCH, REC_N = 4 * NCH, REC_ALPHA = REC_N + 1,
+              REC_BETA = REC_ALPHA + NC, REC_WRC = REC_BETA + NF;
+constexpr int REC_DOUBLES = (REC_WRC + 1 + 7) & ~7;  // 96 for the reference layout
 constexpr int KB_MAX_WARPS = 32, KB_GSM = 512;
 constexpr int KC_THREADS = 128, KC_WPT = 2, KC_SEG_WORDS = KC_WPT * KC_THREADS, KC_IC = 8;  // KC_WPT mask words per thread and segment
 
@@ -71,7 +72,7 @@ struct GeneralParams {
     const double *col_in;
     double *col_out;
     const double *pstat;
-    const float4 *rec16;   // [S][4]: the 16 non-colour channels of each sample, slot order (rpf_kernels.cuh)
+    const float4 *rec16;   // [S][NQ4]: the non-colour channels of each sample, slot order (rpf_kernels.cuh)
     const double4 *col4;   // [S]: current colours {r, g, b, 0}
     const double *rec19;   // [S][REC19]: all 19 channels as doubles, channel order (ordered_stats_kernel)
     // Fixed-point entropy tables (unit 2^-43): gq[k] = round(((k+1)ln(k+1) - k ln k) * 2^43), hq[n] = gq[0]+...+gq[n-1]
@@ -98,18 +99,30 @@ struct GeneralParams {
 
 // 256-bit gathers (LDG.E.256 on sm_100): a sample's 64-byte feature record in two requests instead of four, its
 // {r, g, b, 0} double4 in one instead of two. Addresses are 32-byte aligned (cudaMalloc base + multiples of 32).
-struct Rec16 { float4 q[4]; };
+struct Rec16 { float4 q[NQ4]; };
 __device__ __forceinline__ void ldg256(const float4 *p, float4 &a, float4 &b) {
     asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
         : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(p));
 }
 __device__ __forceinline__ Rec16 load_rec16(const float4 *rec16, uint32_t g) {
-    const float4 *p = rec16 + static_cast<size_t>(g) * 4;
+    const float4 *p = rec16 + static_cast<size_t>(g) * NQ4;
     Rec16 r;
-    ldg256(p, r.q[0], r.q[1]);
-    ldg256(p + 2, r.q[2], r.q[3]);
+#pragma unroll
+    for (int q = 0; q < NQ4; q += 2) ldg256(p + q, r.q[q], r.q[q + 1]);
     return r;
 }
+// the same record as plain 128-bit loads into a flat array (blend kernels: fewer live registers than the 256-bit form)
+__device__ __forceinline__ void load_slots(const float4 *rec16, uint32_t g, float (&fs)[NQ4 * 4]) {
+    const float4 *p = rec16 + static_cast<size_t>(g) * NQ4;
+#pragma unroll
+    for (int q = 0; q < (NSLOT + 3) / 4; ++q) {
+        const float4 f = __ldg(p + q);
+        fs[4 * q] = f.x; fs[4 * q + 1] = f.y; fs[4 * q + 2] = f.z; fs[4 * q + 3] = f.w;
+    }
+}
+// Weight-space channel order is colour (3), features (NF), position (2) -- most selective first. Slot (rpf_common.cuh) of
+// weight channel k >= 3: feature k - 3 sits behind the 2 positions and the NR random parameters, position k - 3 - NF in slot 0 / 1.
+__host__ __device__ constexpr int weight_slot(int k) { return k < 3 + NF ? k + NR - 1 : k - (3 + NF); }
 __device__ __forceinline__ double4 load_col4(const double4 *col4, uint32_t g) {
     double4 c;
     asm("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(c.x), "=d"(c.y), "=d"(c.z), "=d"(c.w) : "l"(col4 + g));  // constant per launch
@@ -134,6 +147,21 @@ __device__ __forceinline__ float warp_max_f(float v) {
     for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
     return v;
 }
+
+// Work order of the general path. Work item w of a chunk of nrows rows -> chunk-local pixel number (row-major, the index of
+// the pixel's mask and record in the scratch). The items run through COLUMN STRIPS of STRIP_W pixels, row-major inside a
+// strip: the pixels in flight at any time then gather from a window of box rows x (STRIP_W + box) columns, about 13 MB of
+// gather records at 8 spp, which stays L2-resident. Row-major over a full-HD row the window is box rows x 1920 columns =
+// 81 MB: it falls out of L2 before the next row comes round, and every row of pixels re-reads its whole window from HBM
+// (measured: 26 GB of DRAM traffic per dependency_kernel launch, profiles/r2/traffic.json v25).
+constexpr int STRIP_W = 256;
+__device__ __forceinline__ int strip_order_n(int w, int W, int nrows, int strip) {
+    const int per = strip * nrows, s = w / per, r = w - s * per;
+    const int x0 = s * strip, sw = min(strip, W - x0);
+    const int y = r / sw;
+    return y * W + x0 + (r - y * sw);
+}
+__device__ __forceinline__ int strip_order(int w, int W, int nrows) { return strip_order_n(w, W, nrows, STRIP_W); }
 
 // candidate t -> global sample index, or false when the neighbour pixel is out of bounds (rpf.cpp:569)
 __device__ __forceinline__ bool candidate_sample(const CandDecode &cd, int t, int px, int py, int B, int P, int W, int H, uint32_t &g,
@@ -225,7 +253,7 @@ __device__ __forceinline__ int bin_value(double x, int c, const KBSmall &ks, int
 }
 
 // Per-pixel constants of the dependency kernels: the slot permutation step, and per channel the normalised extremes and
-// the FMA bin estimate te = x*A + Bc with its (absolute) trust tolerance. Threads 0..18 own a channel, thread 32 the permutation.
+// the FMA bin estimate te = x*A + Bc with its (absolute) trust tolerance. Threads 0..NCH-1 own a channel, thread 32 the permutation.
 __device__ __forceinline__ void kb_prepare_pixel(KBSmall &ks, const double *rec, int N, double dnb, int tid) {
     if (tid == 32) {
         // slot -> sample permutation step: adjacent slots hold samples far apart in enumeration order, so the lanes
@@ -268,16 +296,19 @@ __device__ __forceinline__ void cf_weights_from_mi(KBSmall &ks, int flags, doubl
     };
     if (tid < NF) {
         const int i = tid;
-        const double drf = (0.0 + ks.mi[4 * i]) + ks.mi[4 * i + 1];          // rpf.cpp:421
-        const double dpf = (0.0 + ks.mi[4 * i + 2]) + ks.mi[4 * i + 3];      // rpf.cpp:425
+        double drf = 0.0, dpf = 0.0, dcf = 0.0;  // every sum starts at 0 and adds in index order, as the reference's loops do
+        for (int q = 0; q < NR; ++q) drf += ks.mi[NPCOL * i + q];            // rpf.cpp:421
+        for (int q = 0; q < NP; ++q) dpf += ks.mi[NPCOL * i + NR + q];       // rpf.cpp:425
         ks.wrf[i] = ratio(drf, drf + dpf);                                   // rpf.cpp:465
-        ks.dcf[i] = ((0.0 + ks.mi[52 + i]) + ks.mi[68 + i]) + ks.mi[84 + i]; // P1: sum over colours of MI(c_i, f_j)
+        for (int c = 0; c < NC; ++c) dcf += ks.mi[T0_COL + NCCOL * c + NPCOL + i];  // P1: sum over colours of MI(c_i, f_j)
+        ks.dcf[i] = dcf;
     } else if (tid >= 32 && tid < 32 + NC) {
-        const int i = tid - 32, t = 48 + 16 * i;
-        const double drc = (0.0 + ks.mi[t]) + ks.mi[t + 1];                  // rpf.cpp:432
-        const double dpc = (0.0 + ks.mi[t + 2]) + ks.mi[t + 3];              // rpf.cpp:436
+        const int i = tid - 32, t = T0_COL + NCCOL * i;
+        double drc = 0.0, dpc = 0.0;
+        for (int q = 0; q < NR; ++q) drc += ks.mi[t + q];                    // rpf.cpp:432
+        for (int q = 0; q < NP; ++q) dpc += ks.mi[t + NR + q];               // rpf.cpp:436
         double dfc = 0.0;
-        for (int j = 0; j < NF; ++j) dfc += ks.mi[t + 4 + j];                // rpf.cpp:440
+        for (int j = 0; j < NF; ++j) dfc += ks.mi[t + NPCOL + j];            // rpf.cpp:440
         ks.dsum[i] = dfc;
         ks.dsum[3 + i] = drc;
         ks.dsum[6 + i] = dpc;
@@ -299,12 +330,25 @@ __device__ __forceinline__ void cf_weights_from_mi(KBSmall &ks, int flags, doubl
     __syncthreads();
 }
 
-// The 24 pair groups: one row channel a against four column channels. Group g < 12: feature g against
-// {r0, r1, p0, p1}; g >= 12: colour (g-12)/4 against quarter (g-12)%4 of {r0, r1, p0, p1, f0..f11}.
-// Task index (rpf_common.cuh task_channels) of member j: t0 + j.
-__device__ __forceinline__ void group_channels(int g, int &a, int &t0) {
-    if (g < 12) { a = CH_FEAT + g; t0 = 4 * g; }
-    else { const int u = g - 12; a = CH_COL + (u >> 2); t0 = 48 + 16 * (u >> 2) + 4 * (u & 3); }
+// Units of work of the joint phase: one row channel a against up to G column channels (G tables that share the row index).
+// A feature has NPCOL partners, a colour NCCOL; each list is cut into chunks of G, the last one possibly shorter. With the
+// reference layout and G = 4 these are the 24 groups {feature g: r0, r1, p0, p1} and {colour c, quarter q of its 16 partners}.
+// Task index (rpf_common.cuh task_channels) of member j of unit u: t0 + j, j < g.
+__host__ __device__ inline int unit_count(int G) { return NF * ((NPCOL + G - 1) / G) + NC * ((NCCOL + G - 1) / G); }
+__device__ __forceinline__ void unit_lookup(int u, int G, int &a, int &t0, int &g) {
+    const int cf = (NPCOL + G - 1) / G;
+    if (u < NF * cf) {
+        const int i = u / cf, c = u - i * cf;
+        a = CH_FEAT + i;
+        t0 = NPCOL * i + c * G;
+        g = min(G, NPCOL - c * G);
+    } else {
+        u -= NF * cf;
+        const int cc = (NCCOL + G - 1) / G, i = u / cc, c = u - i * cc;
+        a = CH_COL + i;
+        t0 = T0_COL + NCCOL * i + c * G;
+        g = min(G, NCCOL - c * G);
+    }
 }
 
 
@@ -327,18 +371,20 @@ __device__ __forceinline__ void joint_phase(const GeneralParams &p, KBSmall &ks,
     const int tw = (NT / 32) / teams, team = warp / tw;
     const int tn = tw * 32, tt = tid - team * tn;
     const int nfull = N >> 2, ntail = N & 3;
-    constexpr int SUBS = 4 / G;
+    // every unit holds exactly G tables when G divides both partner counts (always so for the reference layout): the
+    // `j < ge` tests below then fold away at compile time
+    constexpr bool FULL_UNITS = (NPCOL % G == 0) && (NCCOL % G == 0);
     int set = 0;
-    for (int u = team; u < 24 * SUBS; u += teams) {
-        const int grp = u / SUBS, sub = (u - grp * SUBS) * G;
-        int a, t0;
-        group_channels(grp, a, t0);
+    for (int u = team; u < unit_count(G); u += teams) {
+        int a, t0, g;
+        unit_lookup(u, G, a, t0, g);
+        const int ge = FULL_UNITS ? G : g;
         if (ks.flat[a]) continue;  // a constant channel has MI exactly 0 with everything; Sab stays unused
         unsigned *th = region + (team * sets + set) * G * hwn;
         const uint32_t *ba = bins + a * nq;
         const uint32_t *bb[G];
 #pragma unroll
-        for (int j = 0; j < G; ++j) { int aa, b; task_channels(t0 + sub + j, aa, b); bb[j] = bins + b * nq; }
+        for (int j = 0; j < G; ++j) { int aa, b; task_channels(t0 + min(j, ge - 1), aa, b); bb[j] = bins + b * nq; }
         // the packed bins of the next round are requested before this round's atomics go out: when the bins live in the
         // L2-resident scratch (large neighbourhoods) their latency is what the loop would otherwise wait for
         uint32_t wa_n = 0u, wb_n[G];
@@ -364,8 +410,10 @@ __device__ __forceinline__ void joint_phase(const GeneralParams &p, KBSmall &ks,
                 const unsigned ca = ((wa >> (8 * k)) & 255u) * nb;
 #pragma unroll
                 for (int j = 0; j < G; ++j) {
-                    const unsigned cell = ca + ((wb[j] >> (8 * k)) & 255u);
-                    atomicAdd(&th[j * hwn + (cell >> 1)], 1u << ((cell & 1u) << 4));
+                    if (j < ge) {
+                        const unsigned cell = ca + ((wb[j] >> (8 * k)) & 255u);
+                        atomicAdd(&th[j * hwn + (cell >> 1)], 1u << ((cell & 1u) << 4));
+                    }
                 }
             }
         }
@@ -375,8 +423,10 @@ __device__ __forceinline__ void joint_phase(const GeneralParams &p, KBSmall &ks,
                 const unsigned ca = ((wa >> (8 * k)) & 255u) * nb;
 #pragma unroll
                 for (int j = 0; j < G; ++j) {
-                    const unsigned cell = ca + ((bb[j][nfull] >> (8 * k)) & 255u);
-                    atomicAdd(&th[j * hwn + (cell >> 1)], 1u << ((cell & 1u) << 4));
+                    if (j < ge) {
+                        const unsigned cell = ca + ((bb[j][nfull] >> (8 * k)) & 255u);
+                        atomicAdd(&th[j * hwn + (cell >> 1)], 1u << ((cell & 1u) << 4));
+                    }
                 }
             }
         }
@@ -391,6 +441,7 @@ __device__ __forceinline__ void joint_phase(const GeneralParams &p, KBSmall &ks,
         // sweep: sum n ln n over the cells, zero them. Counts 0 and 1 contribute nothing (n ln n = 0) and skip the lookup.
 #pragma unroll
         for (int j = 0; j < G; ++j) {
+            if (j >= ge) break;
             uint4 *r4 = reinterpret_cast<uint4 *>(th + j * hwn);
             unsigned long long acc = 0ull;
             const int nk = hwn >> 2;
@@ -421,7 +472,7 @@ __device__ __forceinline__ void joint_phase(const GeneralParams &p, KBSmall &ks,
                 }
             }
             acc = warp_sum_u64(acc);
-            if (lane == 0 && acc) atomicAdd(&ks.Sab[t0 + sub + j], acc);
+            if (lane == 0 && acc) atomicAdd(&ks.Sab[t0 + j], acc);
         }
         if (sets == 1) team_sync(team, tn);
         else set ^= 1;
@@ -480,7 +531,6 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
     __shared__ KBSmall ks;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int W = p.f.W, H = p.f.H, P = p.f.P, B = p.box;
-    const size_t S = p.f.S;
     const GeneralPlan &L = p.pl;
     unsigned long long *gsm = reinterpret_cast<unsigned long long *>(smem + L.off_gsm);
     unsigned *marg = reinterpret_cast<unsigned *>(smem + L.off_marg);  // [19][nbs]
@@ -497,8 +547,8 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
         __syncthreads();
         if (tid == 0) ks.pixel = atomicAdd(p.work_counter, 1u);
         __syncthreads();
-        const int pl = static_cast<int>(ks.pixel);
-        if (pl >= npix) break;
+        if (static_cast<int>(ks.pixel) >= npix) break;
+        const int pl = strip_order(static_cast<int>(ks.pixel), W, p.nrows);
         const int py = p.row0 + pl / W, px = pl - (pl / W) * W;
         const size_t pix = static_cast<size_t>(py) * W + px;
         const uint32_t *mask = p.mask + static_cast<size_t>(pl) * L.mw;
@@ -575,12 +625,12 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
                 put(CH_COL + 1, cc.y);
                 put(CH_COL + 2, cc.z);
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
+                for (int q = 0; q < NQ4; ++q) {
                     const float4 f = r16.q[q];
-                    put(slot_channel(4 * q + 0), f.x);
-                    put(slot_channel(4 * q + 1), f.y);
-                    put(slot_channel(4 * q + 2), f.z);
-                    put(slot_channel(4 * q + 3), f.w);
+                    if (4 * q + 0 < NSLOT) put(slot_channel(4 * q + 0), f.x);
+                    if (4 * q + 1 < NSLOT) put(slot_channel(4 * q + 1), f.y);
+                    if (4 * q + 2 < NSLOT) put(slot_channel(4 * q + 2), f.z);
+                    if (4 * q + 3 < NSLOT) put(slot_channel(4 * q + 3), f.w);
                 }
             }
         }
@@ -594,7 +644,7 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
             s = warp_sum_u64(s);
             if (lane == 0) ks.Sm[c] = s;
         }
-        // ---- 96 joint histograms ----------------------------------------------------------------------------------
+        // ---- the N_JOINT joint histograms (96 for the reference layout) ----------------------------------------------------------------------------------
         // The histogram region (idx16 is dead now) is cut into slots of the ACTUAL table size (nb*nb u16 cells).
         {
             const int hwn = (((nb * nb + 1) >> 1) + 3) & ~3;
@@ -687,24 +737,24 @@ __global__ void __launch_bounds__(KC_THREADS, 4) blend_kernel(const GeneralParam
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int W = p.f.W, H = p.f.H, P = p.f.P, B = p.box;
     const size_t S = p.f.S;
-    const int pl = blockIdx.x;
+    const int pl = strip_order(blockIdx.x, W, p.nrows);
     const int py = p.row0 + pl / W, px = pl - (pl / W) * W;
     const size_t pix = static_cast<size_t>(py) * W + px;
     const uint32_t base = static_cast<uint32_t>(pix * P);
     const uint32_t *mask = p.mask + static_cast<size_t>(pl) * p.pl.mw;
     const double *rec = p.rec + static_cast<size_t>(pl) * REC_DOUBLES;
-    double *zi = reinterpret_cast<double *>(smem);  // [P][18]: order colour(3), features(12), position(2), pad
+    double *zi = reinterpret_cast<double *>(smem);  // [P][ZS]: order colour(3), features(NF), position(2), pad
 
     // channel order inside z: k = 0..2 colour, 3..14 features, 15..16 position (most selective first)
     if (tid < NWZ) {
         const int k = tid;
-        const int c = k < 3 ? CH_COL + k : (k < 15 ? CH_FEAT + (k - 3) : CH_POS + (k - 15));
+        const int c = k < 3 ? CH_COL + k : (k < 3 + NF ? CH_FEAT + (k - 3) : CH_POS + (k - (3 + NF)));
         const double wrc = rec[REC_WRC];
         const double sigma_p = static_cast<double>(B / 4);                       // rpf.cpp:531 integer division
         const double s2 = p.seed * p.seed / (1.0 - wrc) / (1.0 - wrc);           // rpf.cpp:662
         double coef;
         if (k < 3) coef = rec[REC_ALPHA + k] / (2.0 * s2);
-        else if (k < 15) coef = rec[REC_BETA + (k - 3)] / (2.0 * s2);
+        else if (k < 3 + NF) coef = rec[REC_BETA + (k - 3)] / (2.0 * s2);
         else coef = 1.0 / (2.0 * (sigma_p * sigma_p));
         const double sd = rec[REC_SD + c];
         ks.scl[k] = sd == 0.0 ? 0.0 : sqrt(coef) / sd;
@@ -712,15 +762,14 @@ __global__ void __launch_bounds__(KC_THREADS, 4) blend_kernel(const GeneralParam
     }
     __syncthreads();
     auto load_z = [&](uint32_t g, double *z, double *col) {
-        const float4 *r16 = p.rec16 + static_cast<size_t>(g) * 4;
-        const float4 f0 = __ldg(r16), f1 = __ldg(r16 + 1), f2 = __ldg(r16 + 2), f3 = __ldg(r16 + 3);
+        float fs[NQ4 * 4];
+        load_slots(p.rec16, g, fs);
         const double4 cc = load_col4(p.col4, g);
-        const float fs[16] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w, f2.x, f2.y, f2.z, f2.w, f3.x, f3.y, f3.z, f3.w};
         col[0] = cc.x; col[1] = cc.y; col[2] = cc.z;
 #pragma unroll
         for (int k = 0; k < NWZ; ++k) {
             // z order: colour, features (slots 4..15), position (slots 0, 1)
-            const double x = k < 3 ? col[k] : static_cast<double>(k < 15 ? fs[k + 1] : fs[k - 15]);
+            const double x = k < 3 ? col[k] : static_cast<double>(fs[weight_slot(k)]);
             z[k] = scaled(x, ks.mz[k], ks.scl[k]);
         }
     };
@@ -728,8 +777,9 @@ __global__ void __launch_bounds__(KC_THREADS, 4) blend_kernel(const GeneralParam
         double z[NWZ], col[NC];
         load_z(base + n, z, col);
 #pragma unroll
-        for (int k = 0; k < NWZ; ++k) zi[n * 18 + k] = z[k];
-        zi[n * 18 + 17] = 0.0;
+        for (int k = 0; k < NWZ; ++k) zi[n * ZS + k] = z[k];
+#pragma unroll
+        for (int k = NWZ; k < ZS; ++k) zi[n * ZS + k] = 0.0;
     }
     __syncthreads();
 
@@ -775,7 +825,7 @@ __global__ void __launch_bounds__(KC_THREADS, 4) blend_kernel(const GeneralParam
 #pragma unroll
                 for (int ii = 0; ii < KC_IC; ++ii) {
                     if (i0 + ii < P) {
-                        const double *zr = zi + (i0 + ii) * 18;
+                        const double *zr = zi + (i0 + ii) * ZS;
                         double arg = 0.0;
 #pragma unroll
                         for (int k = 0; k < 3; ++k) {
@@ -792,18 +842,17 @@ __global__ void __launch_bounds__(KC_THREADS, 4) blend_kernel(const GeneralParam
                 if (pass == 0u) continue;
                 // the 64-byte feature record is fetched only now: at the reference's sigma almost every neighbour is cut by its
                 // colour terms alone, and its 32-byte colour record is then all that ever leaves L2
-                const float4 *r16 = p.rec16 + static_cast<size_t>(g) * 4;
-                const float4 f0 = __ldg(r16), f1 = __ldg(r16 + 1), f2 = __ldg(r16 + 2), f3 = __ldg(r16 + 3);
-                const float fs[16] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w, f2.x, f2.y, f2.z, f2.w, f3.x, f3.y, f3.z, f3.w};
+                float fs[NQ4 * 4];
+                load_slots(p.rec16, g, fs);
 #pragma unroll
                 for (int k = 3; k < NWZ; ++k) {
-                    const double x = static_cast<double>(k < 15 ? fs[k + 1] : fs[k - 15]);
+                    const double x = static_cast<double>(fs[weight_slot(k)]);
                     zj[k] = scaled(x, ks.mz[k], ks.scl[k]);
                 }
 #pragma unroll
                 for (int ii = 0; ii < KC_IC; ++ii) {
                     if ((pass >> ii) & 1u) {
-                        const double *zr = zi + (i0 + ii) * 18;
+                        const double *zr = zi + (i0 + ii) * ZS;
                         double arg = 0.0;
 #pragma unroll
                         for (int k = 0; k < NWZ; ++k) {
@@ -846,4 +895,4 @@ __global__ void __launch_bounds__(KC_THREADS, 4) blend_kernel(const GeneralParam
     }
 }
 
-}  // namespace rpf
+}  // namespace RPF_NS

@@ -10,11 +10,12 @@
 // explicit round-to-nearest intrinsics so nvcc cannot contract a*b+c into FMA (gcc's x86-64 build of the
 // reference has no FMA). Joint histograms are exact integer counts. Only log/exp and summation order in
 // MI, weights and blend differ from the CPU at the 1e-15 level.
-#pragma once
-#include "rpf_common.cuh"
+// RE-INCLUDABLE (once per channel layout, rpf_layouts.cuh); the layout-independent kernels (colour conversion, spike removal,
+// Film reconstruction) are compiled for the reference layout only (RPF_FULL).
 
-namespace rpf {
+namespace RPF_NS {
 
+#if RPF_FULL
 // ---------------------------------------------------------------------------------------------------
 // K0: float -> double colour planes (upload)
 __global__ void colors_to_f64_kernel(const float *__restrict__ planes, size_t S, double *__restrict__ col) {
@@ -22,6 +23,7 @@ __global__ void colors_to_f64_kernel(const float *__restrict__ planes, size_t S,
     if (i >= 3 * S) return;
     col[i] = static_cast<double>(planes[static_cast<size_t>(CH_COL) * S + i]);
 }
+#endif
 
 // ---------------------------------------------------------------------------------------------------
 // K1: per-pixel feature mean and 3*sigma (FillMeanAndStddev, rpf.cpp:302-353; getMean/getStdDev ops.h:111-144).
@@ -43,14 +45,15 @@ __global__ void pixel_stats_kernel(FrameView f, int y0, int y1, double *__restri
     const double n = static_cast<double>(f.P);
     const double mu = __ddiv_rn(sum, n);
     const double sd = __dsqrt_rn(__dsub_rn(__ddiv_rn(sq, n), __dmul_rn(mu, mu)));  // no clamp: NaN is meaningful
-    pstat[pix * 24 + k] = mu;
+    pstat[pix * (2 * NF) + k] = mu;
     double sd3 = __dmul_rn(sd, 3.0);  // rpf.cpp:579 multiplyArray(stdDev, 3)
-    const bool world_pos = (k >= 3 && k < 6) || k >= 9;  // p0, p1 of sd.h:62-94
+    const bool world_pos = feature_is_world_pos(k);  // p0, p1 of sd.h:62-94
     if (world_pos && pos_sigmas > 0.0) sd3 = __dmul_rn(sd, pos_sigmas);
     if (min_sigma > 0.0 && sd3 < min_sigma) sd3 = min_sigma;
-    pstat[pix * 24 + NF + k] = sd3;
+    pstat[pix * (2 * NF) + NF + k] = sd3;
 }
 
+#if RPF_FULL
 // Paper-mode spike removal (rpf_hdr_clamp; not in the reference): one thread per pixel of rows [y0,y1). Per channel the
 // sequential mean and population sigma of the pixel's samples; a sample with |c - mean| > k * sigma in any channel
 // takes the mean in all three channels. In place on colours [3][S].
@@ -84,6 +87,8 @@ __global__ void hdr_clamp_kernel(double *__restrict__ col, size_t S, int W, int 
     }
 }
 
+#endif  // RPF_FULL
+
 // ---------------------------------------------------------------------------------------------------
 // Gather-friendly copies for the general path. The planes are structure-of-arrays (one coalesced stream per channel
 // when neighbouring pixels are read together); the general path instead gathers scattered accepted samples, where a
@@ -91,12 +96,12 @@ __global__ void hdr_clamp_kernel(double *__restrict__ col, size_t S, int W, int 
 // once per upload), col4[g] = {r, g, b, 0} of the current colours as doubles (32 B, rebuilt per pass).
 __global__ void pack_features_kernel(const float *__restrict__ planes, size_t S, float4 *__restrict__ rec16) {
     const size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
-    if (i >= 4 * S) return;
-    const size_t g = i >> 2;
-    const int q = static_cast<int>(i & 3);
+    if (i >= NQ4 * S) return;
+    const size_t g = i / NQ4;
+    const int q = static_cast<int>(i - g * NQ4);
     float v[4];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) v[k] = planes[static_cast<size_t>(slot_channel(4 * q + k)) * S + g];
+    for (int k = 0; k < 4; ++k) v[k] = 4 * q + k < NSLOT ? planes[static_cast<size_t>(slot_channel(4 * q + k)) * S + g] : 0.f;
     rec16[i] = make_float4(v[0], v[1], v[2], v[3]);
 }
 // rec19[g] = all 19 channels of sample g as doubles in channel order (+1 pad, 160 B): ordered_stats_kernel gives lane c
@@ -174,9 +179,10 @@ struct PixelSmall {
     int N, nb;
 };
 
-}  // namespace rpf
+}  // namespace RPF_NS
 
-namespace rpf {
+#if RPF_FULL
+namespace RPF_NS {
 
 // double -> float colours for the host (the Film takes Float RGB, sd.h:104-112)
 __global__ void colors_to_f32_kernel(const double *__restrict__ col, size_t n, float *__restrict__ out) {
@@ -277,4 +283,5 @@ __global__ void film_reconstruct_kernel(const FilmParams p) {
     for (int k = 0; k < 3; ++k) p.rgb[static_cast<size_t>(t) * 3 + k] = __fmul_rn(__fadd_rn(rgb[k], 0.f), p.scale);  // splats are zero
 }
 
-}  // namespace rpf
+}  // namespace RPF_NS
+#endif  // RPF_FULL

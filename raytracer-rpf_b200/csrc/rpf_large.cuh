@@ -10,10 +10,9 @@
 // (one row channel against four column channels, the pair groups of rpf.cpp:416-442) are built per pass.
 //
 // Fixed-point entropy sums use the unit 2^-38 here (n ln n of 2^20 samples must stay below 2^64).
-#pragma once
-#include "rpf_general.cuh"
+// Reference layout only (RPF_FULL in rpf_layouts.cuh): wider channel layouts take the general path.
 
-namespace rpf {
+namespace RPF_NS {
 
 constexpr int KL_THREADS = 1024;
 constexpr double KL_UNIT = 1.0 / 274877906944.0;  // 2^-38
@@ -105,8 +104,8 @@ __global__ void __launch_bounds__(KL_THREADS, 1) dependency_large_kernel(const G
         __syncthreads();
         if (tid == 0) ks.pixel = atomicAdd(p.work_counter, 1u);
         __syncthreads();
-        const int pl = static_cast<int>(ks.pixel);
-        if (pl >= npix) break;
+        if (static_cast<int>(ks.pixel) >= npix) break;
+        const int pl = strip_order(static_cast<int>(ks.pixel), W, p.nrows);
         const int py = p.row0 + pl / W, px = pl - (pl / W) * W;
         const size_t pix = static_cast<size_t>(py) * W + px;
         const uint32_t *mask = p.mask + static_cast<size_t>(pl) * L.mw;
@@ -184,8 +183,8 @@ __global__ void __launch_bounds__(KL_THREADS, 1) dependency_large_kernel(const G
         G = G >= 4 ? 4 : (G >= 2 ? 2 : 1);
         const int slab_rows = cells <= L.region_words ? nb : L.region_words / nb;
         for (int grp = 0; grp < 24; ++grp) {
-            int a, t0;
-            group_channels(grp, a, t0);
+            int a, t0, g4;
+            unit_lookup(grp, 4, a, t0, g4);  // reference layout: 24 units of exactly four tables
             if (ks.flat[a]) continue;
             const uint16_t *ba = sc.bins + a * cs;
             for (int sub = 0; sub < 4; sub += G) {
@@ -258,4 +257,4 @@ __global__ void __launch_bounds__(KL_THREADS, 1) dependency_large_kernel(const G
     }
 }
 
-}  // namespace rpf
+}  // namespace RPF_NS

@@ -11,10 +11,9 @@
 //                         decides histogram bin boundaries later), so one WARP per pixel walks the mask in order with
 //                         one lane per channel and two dependent FP64 add chains per lane; 64 warps per SM hide the
 //                         add latency.
-#pragma once
-#include "rpf_general.cuh"
+// RE-INCLUDABLE (once per channel layout, rpf_layouts.cuh).
 
-namespace rpf {
+namespace RPF_NS {
 
 constexpr int KM_MAX_THREADS = 128;
 
@@ -27,7 +26,7 @@ __host__ __device__ inline void membership_tile(int box, int &tx, int &ty) {
 
 struct MembershipParams {
     FrameView f;
-    const double *pstat;   // [W*H][24] per-pixel feature mean[12], 3 sigma[12]
+    const double *pstat;   // [W*H][2 NF] per-pixel feature mean[NF], 3 sigma[NF]
     uint32_t *mask;        // [chunk pixels][mw]
     int box, row0, nrows, mw;
     int tx, ty, tiles_x;   // tile shape and tiles per row
@@ -46,7 +45,11 @@ __global__ void __launch_bounds__(KM_MAX_THREADS) membership_kernel(const Member
     const int tid = threadIdx.x;
     const int W = p.f.W, H = p.f.H, P = p.f.P, B = p.box, bd = (B - 1) / 2;
     const size_t S = p.f.S;
-    const int tile_x = blockIdx.x % p.tiles_x, tile_y = blockIdx.x / p.tiles_x;
+    // tiles in the same column strips as the other kernels of the path (strip_order, rpf_general.cuh): a strip's window of
+    // feature rows stays L2-resident from one row of tiles to the next
+    const int tiles_y = (p.nrows + p.ty - 1) / p.ty;
+    const int tl = strip_order_n(blockIdx.x, p.tiles_x, tiles_y, STRIP_W / p.tx);
+    const int tile_x = tl % p.tiles_x, tile_y = tl / p.tiles_x;
     const int x0 = tile_x * p.tx, y0 = p.row0 + tile_y * p.ty;
     const int lx = tid % p.tx, ly = tid / p.tx;
     const int px = x0 + lx, py = y0 + ly;
@@ -54,7 +57,7 @@ __global__ void __launch_bounds__(KM_MAX_THREADS) membership_kernel(const Member
 
     double mu[NF], sd3[NF];
     if (live) {
-        const double *ps = p.pstat + (static_cast<size_t>(py) * W + px) * 24;
+        const double *ps = p.pstat + (static_cast<size_t>(py) * W + px) * (2 * NF);
 #pragma unroll
         for (int k = 0; k < NF; ++k) { mu[k] = ps[k]; sd3[k] = ps[NF + k]; }
     } else {
@@ -143,8 +146,8 @@ constexpr int KO_GROUP = 16;  // mask words decoded per round
 __global__ void __launch_bounds__(KO_WARPS * 32) ordered_stats_kernel(const GeneralParams p) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int W = p.f.W, P = p.f.P, B = p.box, bd = (B - 1) / 2;
-    const int pl = blockIdx.x * KO_WARPS + warp;
-    if (pl >= p.nrows * W) return;
+    if (blockIdx.x * KO_WARPS + warp >= p.nrows * W) return;
+    const int pl = strip_order(blockIdx.x * KO_WARPS + warp, W, p.nrows);
     const int py = p.row0 + pl / W, px = pl - (pl / W) * W;
     const size_t pix = static_cast<size_t>(py) * W + px;
     const uint32_t base = static_cast<uint32_t>(pix * P);
@@ -237,4 +240,4 @@ __global__ void __launch_bounds__(KO_WARPS * 32) ordered_stats_kernel(const Gene
     }
 }
 
-}  // namespace rpf
+}  // namespace RPF_NS

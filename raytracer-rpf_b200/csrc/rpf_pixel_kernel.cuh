@@ -7,10 +7,9 @@
 //   5 MI          96 joint + 19 marginal histograms, thread-private, no atomics  [mi.cpp:23-42,65-87]
 //   6 alpha/beta  dependency sums and fractional contributions                   [rpf.cpp:416-487]
 //   7 weights     cross-bilateral weights and blend                              [rpf.cpp:637-717]
-#pragma once
-#include "rpf_kernels.cuh"
+// Reference layout only (RPF_FULL in rpf_layouts.cuh): wider channel layouts take the general path.
 
-namespace rpf {
+namespace RPF_NS {
 
 // Histogram cell address: lane-private column of a [words][32 lanes] array, four u8 cells per 32-bit word.
 __device__ __forceinline__ uint8_t *cell_u8(unsigned char *colbase, int c) { return colbase + (c >> 2) * 128 + (c & 3); }
@@ -506,4 +505,4 @@ __global__ void __launch_bounds__(THREADS, 4) rpf_pixel_kernel(const FilterParam
     }
 }
 
-}  // namespace rpf
+}  // namespace RPF_NS

@@ -79,9 +79,18 @@ void sample_degenerate(const Rng &r, int gx, int gy, int s, float out[19]) {
 
 }  // namespace
 
-extern "C" int rpf_synth_planes(int width, int height, int spp, unsigned long long seed, int kind, int x_off, int y_off,
-                                float *planes) {
-    if (width <= 0 || height <= 0 || spp <= 0 || !planes || kind < 0 || kind > 1) return RPF_ERR_INVALID;
+// Wider records: the 19 reference channels are generated exactly as above and land in their slots of
+// the layout position | colour | random | features; the extra random parameters (time, light sample u / v, ...) are fresh
+// uniforms, the extra features (a texture colour, ...) smooth functions of the pixel plus noise and a dependence on the
+// extra random parameters, like the reference features. kind 2: like kind 0 but every EXTRA random parameter is the
+// constant 0.5 -- a channel that carries no information, so the filter's result must equal the reference layout's.
+extern "C" int rpf_synth_planes_layout(int width, int height, int spp, unsigned long long seed, int kind, int x_off, int y_off,
+                                       int n_random, int n_features, float *planes) {
+    if (n_random == 0) n_random = 2;
+    if (n_features == 0) n_features = 12;
+    if (width <= 0 || height <= 0 || spp <= 0 || !planes || kind < 0 || kind > 2 || n_random < 2 || n_features < 12 || n_random + n_features > 27)
+        return RPF_ERR_INVALID;
+    const int nch = 5 + n_random + n_features, ch_feat = 5 + n_random;
     const size_t S = static_cast<size_t>(width) * height * spp;
     unsigned nt = std::thread::hardware_concurrency();
     if (nt < 1) nt = 1;
@@ -91,18 +100,36 @@ extern "C" int rpf_synth_planes(int width, int height, int spp, unsigned long lo
         for (int y = t; y < height; y += static_cast<int>(nt))
             for (int x = 0; x < width; ++x)
                 for (int s = 0; s < spp; ++s) {
-                    float v[19];
+                    float v[19], w[32];
                     const int gx = x + x_off, gy = y + y_off;
                     Rng r(seed, gx, gy, s);
-                    if (kind == 0) sample_noisy(r, gx, gy, v); else sample_degenerate(r, gx, gy, s, v);
+                    if (kind == 1) sample_degenerate(r, gx, gy, s, v); else sample_noisy(r, gx, gy, v);
+                    for (int c = 0; c < 7; ++c) w[c] = v[c];                       // position, colour, pLens
+                    for (int k = 0; k < 12; ++k) w[ch_feat + k] = v[7 + k];        // n0, p0, n1, p1
+                    double extra = 0.0;
+                    for (int q = 2; q < n_random; ++q) {
+                        const double u = kind == 2 ? 0.5 : r.uniform(40 + q);
+                        w[5 + q] = static_cast<float>(u);
+                        extra += u;
+                    }
+                    for (int k = 12; k < n_features; ++k)
+                        w[ch_feat + k] = kind == 1 ? (v[7] != 0.f ? 0.25f * (k - 11) : 0.f)
+                                                   : static_cast<float>(0.5 + 0.4 * std::sin(0.09 * gx + 0.7 * k) * std::cos(0.05 * gy) + 0.1 * r.normal(30 + k) +
+                                                                        (kind == 2 ? 0.0 : 0.15 * extra));
                     const size_t i = (static_cast<size_t>(y) * width + x) * spp + s;
-                    for (int c = 0; c < 19; ++c) planes[c * S + i] = v[c];
+                    for (int c = 0; c < nch; ++c) planes[c * S + i] = w[c];
                 }
     };
     for (unsigned t = 1; t < nt; ++t) th.emplace_back(work, static_cast<int>(t));
     work(0);
     for (auto &t : th) t.join();
     return RPF_OK;
+}
+
+extern "C" int rpf_synth_planes(int width, int height, int spp, unsigned long long seed, int kind, int x_off, int y_off,
+                                float *planes) {
+    if (kind < 0 || kind > 1) return RPF_ERR_INVALID;
+    return rpf_synth_planes_layout(width, height, spp, seed, kind, x_off, y_off, 2, 12, planes);
 }
 
 // Film constructor's filter table (reference core/film.cpp:69-77) for the box and gaussian filters

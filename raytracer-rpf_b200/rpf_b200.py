@@ -29,6 +29,7 @@ ABI_SYMBOLS = [
     "rpf_set_paper_mode", "rpf_filter_sigmas", "rpf_hdr_clamp", "rpf_fused_max_candidates",
     "rpf_band_plan", "rpf_band_unique_id", "rpf_band_attach", "rpf_host_alloc", "rpf_host_free",
     "rpf_set_debug_pixel", "rpf_download_debug_mi", "rpf_reset_colors",
+    "rpf_num_channels", "rpf_num_pairs", "rpf_layout_supported", "rpf_synth_planes_layout",
 ]
 
 
@@ -38,7 +39,8 @@ class RPFError(RuntimeError):
 
 class Config(C.Structure):
     _fields_ = [("width", C.c_int), ("height", C.c_int), ("spp", C.c_int), ("device", C.c_int),
-                ("flags", C.c_int), ("debug", C.c_int), ("n_gpus", C.c_int), ("device_ids", C.c_int * 8), ("max_box", C.c_int)]
+                ("flags", C.c_int), ("debug", C.c_int), ("n_gpus", C.c_int), ("device_ids", C.c_int * 8), ("n_random", C.c_int),
+                ("n_features", C.c_int), ("max_box", C.c_int)]
 
 
 class Stats(C.Structure):
@@ -126,6 +128,7 @@ def hostio():
             raise RPFError(f"{path} is not built (run `python -c 'import __graft_entry__ as g; g.build()'`)")
         L = C.CDLL(path)
         L.rpf_synth_planes.argtypes = [C.c_int, C.c_int, C.c_int, C.c_ulonglong, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        L.rpf_synth_planes_layout.argtypes = [C.c_int, C.c_int, C.c_int, C.c_ulonglong, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
         _hostio = L
     return _hostio
 
@@ -172,6 +175,9 @@ def lib():
         L.rpf_host_free.argtypes = [vp]
         L.rpf_host_free.restype = None
         L.rpf_reset_colors.argtypes = [vp]
+        L.rpf_num_channels.argtypes = [vp]
+        L.rpf_num_pairs.argtypes = [vp]
+        L.rpf_layout_supported.argtypes = [i, i]
         L.rpf_set_debug_pixel.argtypes = [vp, i, i]
         L.rpf_download_debug_mi.argtypes = [vp, vp, C.POINTER(i), C.POINTER(i), vp, i]
         _lib = L
@@ -200,11 +206,13 @@ def nccl_unique_id():
     return bytes(buf)
 
 
-def synth_planes(width, height, spp, seed=1234, kind=0, x_off=0, y_off=0, out=None):
-    """Synthetic feature buffer of SURVEY.md 8(d): float32 [19, W*H*spp] (host side, deterministic)."""
-    planes = out if out is not None else np.empty((NCH, width * height * spp), np.float32)
-    assert planes.dtype == np.float32 and planes.flags.c_contiguous and planes.size == NCH * width * height * spp
-    rc = hostio().rpf_synth_planes(width, height, spp, seed, kind, x_off, y_off, _p(planes))
+def synth_planes(width, height, spp, seed=1234, kind=0, x_off=0, y_off=0, out=None, n_random=2, n_features=12):
+    """Synthetic feature buffer of SURVEY.md 8(d): float32 [5 + n_random + n_features, W*H*spp] (host side, deterministic);
+    19 planes for the reference's record."""
+    nch = 5 + n_random + n_features
+    planes = out if out is not None else np.empty((nch, width * height * spp), np.float32)
+    assert planes.dtype == np.float32 and planes.flags.c_contiguous and planes.size == nch * width * height * spp
+    rc = hostio().rpf_synth_planes_layout(width, height, spp, seed, kind, x_off, y_off, n_random, n_features, _p(planes))
     if rc != 0:
         raise RPFError(f"rpf_synth_planes failed ({rc})")
     return planes
@@ -214,7 +222,7 @@ class RPFFilter:
     """One device context = one SamplingFilm (reference src/custom/sample_film.h:28-45) resident in HBM."""
 
     def __init__(self, width, height, spp, device=0, flags=FLAGS_DEFINED, debug=False, force_general=False, force_large=False,
-                 devices=None, max_box=0):
+                 devices=None, max_box=0, n_random=0, n_features=0):
         """devices: list of CUDA ordinals -> one process, one row band per device (rpf_config.n_gpus / device_ids)."""
         if force_general:
             flags |= FLAG_FORCE_GENERAL
@@ -225,10 +233,12 @@ class RPFFilter:
         self._h = C.c_void_p()
         devs = list(devices) if devices else []
         cfg = Config(width, height, spp, device, flags, 1 if debug else 0, len(devs) if len(devs) > 1 else 0,
-                     (C.c_int * 8)(*(devs + [0] * (8 - len(devs)))), max_box)
+                     (C.c_int * 8)(*(devs + [0] * (8 - len(devs)))), n_random, n_features, max_box)
         rc = lib().rpf_create(C.byref(self._h), C.byref(cfg))
         if rc != 0:
             raise RPFError(f"rpf_create failed ({rc}): {lib().rpf_last_error(None).decode()}")
+        self.nch, self.n_pairs = lib().rpf_num_channels(self._h), lib().rpf_num_pairs(self._h)
+        self.nf = (n_features or 12)
 
     def _check(self, rc):
         if rc != 0:
@@ -247,14 +257,14 @@ class RPFFilter:
 
     # -- data movement --------------------------------------------------------------------------
     def upload(self, planes):
-        """planes: float32 [19, S] host array (pinned or pageable)."""
-        assert planes.dtype == np.float32 and planes.shape == (NCH, self.S) and planes.flags.c_contiguous
-        ptrs = (C.c_void_p * NCH)(*[planes[c].ctypes.data for c in range(NCH)])
+        """planes: float32 [nch, S] host array (pinned or pageable); nch = 19 for the reference's record."""
+        assert planes.dtype == np.float32 and planes.shape == (self.nch, self.S) and planes.flags.c_contiguous
+        ptrs = (C.c_void_p * self.nch)(*[planes[c].ctypes.data for c in range(self.nch)])
         self._check(lib().rpf_upload(self._h, ptrs))
 
     def upload_device(self, dev_ptr):
         """dev_ptr: integer device address of a contiguous float32 [19, S] buffer."""
-        ptrs = (C.c_void_p * NCH)(*[dev_ptr + 4 * self.S * c for c in range(NCH)])
+        ptrs = (C.c_void_p * self.nch)(*[dev_ptr + 4 * self.S * c for c in range(self.nch)])
         self._check(lib().rpf_upload_device(self._h, ptrs))
 
     def reset_colors(self):
@@ -278,7 +288,7 @@ class RPFFilter:
 
     def download_debug(self):
         n = self.W * self.H
-        N, al, be, w = np.zeros(n, np.int32), np.zeros((n, 3)), np.zeros((n, 12)), np.zeros(n)
+        N, al, be, w = np.zeros(n, np.int32), np.zeros((n, 3)), np.zeros((n, self.nf)), np.zeros(n)
         self._check(lib().rpf_download_debug(self._h, _p(N), _p(al), _p(be), _p(w)))
         return dict(N=N, alpha=al, beta=be, wrc=w)
 
@@ -287,8 +297,8 @@ class RPFFilter:
 
     def download_debug_mi(self, bins_cap=1024):
         """-> dict(mi [96], N, bins, marginals [19, bins]) of the pixel chosen with set_debug_pixel."""
-        mi, n, nb = np.zeros(96), C.c_int(), C.c_int()
-        marg = np.zeros((NCH, bins_cap), np.uint32)
+        mi, n, nb = np.zeros(self.n_pairs), C.c_int(), C.c_int()
+        marg = np.zeros((self.nch, bins_cap), np.uint32)
         self._check(lib().rpf_download_debug_mi(self._h, _p(mi), C.byref(n), C.byref(nb), _p(marg), bins_cap))
         return dict(mi=mi, N=n.value, bins=nb.value, marginals=marg[:, :nb.value].copy())
 

@@ -23,6 +23,7 @@ class OracleArgs(C.Structure):
         ("subsample_keep_q24", C.c_uint), ("subsample_seed", C.c_ulonglong), ("global_row0", C.c_int),
         ("w_epsilon", C.c_double), ("min_sigma", C.c_double), ("world_pos_sigmas", C.c_double),
         ("sigma_seeds", C.c_void_p), ("hdr_clamp_sigmas", C.c_double),
+        ("n_random", C.c_int), ("n_features", C.c_int),
     ]
 
 
@@ -80,19 +81,22 @@ def _p(a):
 
 
 def oracle_filter(planes, W, H, P, boxes, seed=0.002, flags=DEFINED, colors=None, threads=0,
-                  rows=None, cols=None, debug=False, subsample=None, paper=None):
+                  rows=None, cols=None, debug=False, subsample=None, paper=None, layout=None):
+    # layout = (n_random, n_features) of a wider record or None = the reference's (2, 12)
     # paper = dict(w_epsilon=, min_sigma=, world_pos_sigmas=, sigma_seeds=[per iteration], hdr_clamp_sigmas=) or None
     # subsample = (keep probability, rng seed, global row of local row 0) or None
     """planes: float32 [19, W*H*P]. Returns dict(colors=[3,S] float64, N, alpha, beta, wrc, nan_count)."""
     planes = np.ascontiguousarray(planes, dtype=np.float32)
     S = W * H * P
-    assert planes.shape == (NCH, S)
+    nr, nf = layout or (2, 12)
+    assert planes.shape == (5 + nr + nf, S)
     col = np.ascontiguousarray(planes[2:5].astype(np.float64) if colors is None else colors, dtype=np.float64).copy()
     bx = np.asarray(boxes, dtype=np.int32)
     a = OracleArgs()
     a.width, a.height, a.spp = W, H, P
     a.planes, a.colors, a.box_sizes = _p(planes), _p(col), _p(bx)
     a.n_iter, a.sigma_fc_seed, a.flags, a.n_threads = len(bx), seed, flags, threads
+    a.n_random, a.n_features = nr, nf
     a.y0, a.y1 = rows if rows else (0, 0)
     a.x0, a.x1 = cols if cols else (0, 0)
     if subsample is not None:
@@ -112,7 +116,7 @@ def oracle_filter(planes, W, H, P, boxes, seed=0.002, flags=DEFINED, colors=None
     if debug:
         out["N"] = np.zeros(W * H, np.int32)
         out["alpha"] = np.zeros((W * H, 3))
-        out["beta"] = np.zeros((W * H, 12))
+        out["beta"] = np.zeros((W * H, nf))
         out["wrc"] = np.zeros(W * H)
         a.nbh_size, a.alpha, a.beta, a.wrc = _p(out["N"]), _p(out["alpha"]), _p(out["beta"]), _p(out["wrc"])
     rc = oracle().rpf_oracle_filter(C.byref(a))
@@ -208,7 +212,7 @@ def oracle_film(W, H, P, pfilm, colors, ray_weight, table, rx, ry, bounds, scale
     return rgb
 
 
-def oracle_pixel_probe(planes, W, H, P, box, px, py, seed=0.002, flags=DEFINED, colors=None, bins_cap=1024):
+def oracle_pixel_probe(planes, W, H, P, box, px, py, seed=0.002, flags=DEFINED, colors=None, bins_cap=1024, layout=None):
     """One pixel of one pass: dict(mi [96], N, bins, marginals [19, bins], z [N, 19])."""
     planes = np.ascontiguousarray(planes, dtype=np.float32)
     bx = np.asarray([box], dtype=np.int32)
@@ -217,13 +221,16 @@ def oracle_pixel_probe(planes, W, H, P, box, px, py, seed=0.002, flags=DEFINED, 
     col = None if colors is None else np.ascontiguousarray(colors, np.float64)
     a.planes, a.colors, a.box_sizes = _p(planes), (None if col is None else _p(col)), _p(bx)
     a.n_iter, a.sigma_fc_seed, a.flags = 1, seed, flags
+    nr, nf = layout or (2, 12)
+    a.n_random, a.n_features = nr, nf
+    nch, npairs = 5 + nr + nf, nf * (nr + 2) + 3 * (nr + 2 + nf)
     lib = oracle()
     lib.rpf_oracle_pixel_probe.argtypes = [C.POINTER(OracleArgs), C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int),
                                            C.c_void_p, C.c_int, C.c_void_p, C.c_int]
-    mi, n, nb = np.zeros(96), C.c_int(), C.c_int()
-    marg = np.zeros((NCH, bins_cap), np.int32)
+    mi, n, nb = np.zeros(npairs), C.c_int(), C.c_int()
+    marg = np.zeros((nch, bins_cap), np.int32)
     ncap = box * box * P
-    z = np.zeros((ncap, NCH))
+    z = np.zeros((ncap, nch))
     rc = lib.rpf_oracle_pixel_probe(C.byref(a), px, py, _p(mi), C.byref(n), C.byref(nb), _p(marg), bins_cap, _p(z), ncap)
     assert rc == 0, rc
     return dict(mi=mi, N=n.value, bins=nb.value, marginals=marg[:, :nb.value].copy(), z=z[:n.value].copy())
