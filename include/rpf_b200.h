@@ -269,11 +269,12 @@ typedef struct rpf_buffer_info {
     int width, height, spp;
     int sample_x0, sample_y0; /* sampleBounds.pMin */
     int has_ray_weight;       /* out of rpf_buffer_info_read; ignored by rpf_buffer_write */
+    int n_random, n_features; /* channel layout of the file: 5 + n_random + n_features planes (0 / 0 on write: the reference's 2 / 12) */
 } rpf_buffer_info;
 int rpf_buffer_write(const char *path, const rpf_buffer_info *info, const float *const planes[RPF_NUM_CHANNELS],
                      const float *ray_weight /* may be NULL */);
 int rpf_buffer_info_read(const char *path, rpf_buffer_info *info);
-/* planes: [19][width*height*spp] contiguous; ray_weight: [width*height*spp] or NULL (filled with 1 if the file has none) */
+/* planes: [5 + n_random + n_features][width*height*spp] contiguous (19 planes for the reference's record); ray_weight: [width*height*spp] or NULL (filled with 1 if the file has none) */
 int rpf_buffer_read(const char *path, float *planes, float *ray_weight);
 
 #ifdef __cplusplus

@@ -74,6 +74,17 @@ static bool run(SamplingFilm &film, const RPFB200Options &opt, const rpf_film_de
                 return false;
             }
     const size_t S = static_cast<size_t>(W) * H * spp;
+    const int xr = opt.wide ? opt.wide->nRandom : 0, xf = opt.wide ? opt.wide->nFeatures : 0, xs = xr + xf;
+    const int nch = RPF_NUM_CHANNELS + xs;
+    if (opt.wide && (xr < 0 || xf < 0 || opt.wide->values.size() != S * xs)) {
+        if (error) *error = "RPFB200WideRecord: values must hold (extra random + extra features) floats for every sample";
+        return false;
+    }
+    if (opt.wide && !rpf_layout_supported(2 + xr, 12 + xf)) {
+        if (error) *error = "this build of librpf_b200 has no kernels for " + std::to_string(2 + xr) + " random parameters and " +
+                            std::to_string(12 + xf) + " features";
+        return false;
+    }
     if (fdesc && opt.devices.size() > 1) {
         if (error) *error = "Film reconstruction on the device needs a single-GPU context (RPFB200Options::devices)";
         return false;
@@ -87,6 +98,7 @@ static bool run(SamplingFilm &film, const RPFB200Options &opt, const rpf_film_de
     cfg.device = opt.device;
     cfg.flags = opt.flags;
     cfg.debug = opt.debugStats ? 1 : 0;
+    if (opt.wide) { cfg.n_random = 2 + xr; cfg.n_features = 12 + xf; }
     if (opt.devices.size() > 1) {
         if (opt.devices.size() > RPF_MAX_GPUS) {
             if (error) *error = "RPFB200Options::devices lists more than RPF_MAX_GPUS devices";
@@ -106,18 +118,27 @@ static bool run(SamplingFilm &film, const RPFB200Options &opt, const rpf_film_de
     // doubles (sd.h:62-94), so narrowing to float is exact for a fresh film. The container is samples[x][y] (x-major,
     // sample_film.cpp:16-22); one task per image row writes contiguous runs of every plane into page-locked memory.
     auto t0 = std::chrono::steady_clock::now();
-    Pinned<float> planes = pinned<float>(static_cast<size_t>(RPF_NUM_CHANNELS) * S, error);
+    Pinned<float> planes = pinned<float>(static_cast<size_t>(nch) * S, error);
     Pinned<double> colours = pinned<double>(3 * S, error);
     if (!planes || !colours) return false;
     float *pl = planes.get();
     double *co = colours.get();
+    const float *wv = opt.wide ? opt.wide->values.data() : nullptr;
     parallel_for(opt, H, [&](int64_t y) {
         for (int x = 0; x < W; ++x) {
             const SampleDataSet &px = film.samples[x][y];
             const size_t base = (static_cast<size_t>(y) * W + x) * spp;
             for (size_t s = 0; s < spp; ++s) {
                 const auto &d = px[s].data;
-                for (int c = 0; c < RPF_NUM_CHANNELS; ++c) pl[c * S + base + s] = static_cast<float>(d[c]);
+                // position, colour, pLens stay where they are; the extra random parameters follow pLens, the extra
+                // features follow p1
+                for (int c = 0; c < 7; ++c) pl[c * S + base + s] = static_cast<float>(d[c]);
+                for (int c = 7; c < RPF_NUM_CHANNELS; ++c) pl[(c + xr) * S + base + s] = static_cast<float>(d[c]);
+                if (xs) {
+                    const float *e = wv + (base + s) * xs;
+                    for (int q = 0; q < xr; ++q) pl[(7 + q) * S + base + s] = e[q];
+                    for (int q = 0; q < xf; ++q) pl[(RPF_NUM_CHANNELS + xr + q) * S + base + s] = e[xr + q];
+                }
                 for (int k = 0; k < 3; ++k) co[k * S + base + s] = d[2 + k];
             }
         }
@@ -127,9 +148,9 @@ static bool run(SamplingFilm &film, const RPFB200Options &opt, const rpf_film_de
     if (opt.keepProbability < 1.0 && rpf_set_subsampling(ctx.get(), opt.keepProbability, opt.rngSeed, 0) != RPF_OK)
         return failed(error, "rpf_set_subsampling", ctx.get());
     t0 = std::chrono::steady_clock::now();
-    const float *ptrs[RPF_NUM_CHANNELS];
-    for (int c = 0; c < RPF_NUM_CHANNELS; ++c) ptrs[c] = pl + c * S;
-    if (rpf_upload(ctx.get(), ptrs) != RPF_OK) return failed(error, "rpf_upload", ctx.get());
+    std::vector<const float *> ptrs(nch);
+    for (int c = 0; c < nch; ++c) ptrs[c] = pl + c * S;
+    if (rpf_upload(ctx.get(), ptrs.data()) != RPF_OK) return failed(error, "rpf_upload", ctx.get());
     // colours re-entering the filter after an earlier pass are doubles (sd.h:205-207): keep every bit
     if (rpf_upload_colors_f64(ctx.get(), co) != RPF_OK) return failed(error, "rpf_upload_colors_f64", ctx.get());
     if (rpf_synchronize(ctx.get()) != RPF_OK) return failed(error, "rpf_synchronize", ctx.get());
@@ -199,7 +220,8 @@ static bool run(SamplingFilm &film, const RPFB200Options &opt, const rpf_film_de
     return true;
 }
 
-bool DumpSamplingFilmB200(const SamplingFilm &film, int sampleX0, int sampleY0, const std::string &path, std::string *error) {
+bool DumpSamplingFilmB200(const SamplingFilm &film, int sampleX0, int sampleY0, const std::string &path, std::string *error,
+                          const RPFB200WideRecord *wide) {
     const int W = film.getWidth(), H = film.getHeight();
     const size_t spp = (W > 0 && H > 0 && !film.samples.empty() && !film.samples[0].empty()) ? film.samples[0][0].size() : 0;
     if (spp == 0) {
@@ -207,7 +229,12 @@ bool DumpSamplingFilmB200(const SamplingFilm &film, int sampleX0, int sampleY0, 
         return false;
     }
     const size_t S = static_cast<size_t>(W) * H * spp;
-    std::vector<float> planes(static_cast<size_t>(RPF_NUM_CHANNELS) * S), rayWeight(S);
+    const int xr = wide ? wide->nRandom : 0, xf = wide ? wide->nFeatures : 0, xs = xr + xf, nch = RPF_NUM_CHANNELS + xs;
+    if (wide && wide->values.size() != S * xs) {
+        if (error) *error = "RPFB200WideRecord does not match the SamplingFilm";
+        return false;
+    }
+    std::vector<float> planes(static_cast<size_t>(nch) * S), rayWeight(S);
     for (int x = 0; x < W; ++x)
         for (int y = 0; y < H; ++y) {
             const SampleDataSet &px = film.samples[x][y];
@@ -217,14 +244,17 @@ bool DumpSamplingFilmB200(const SamplingFilm &film, int sampleX0, int sampleY0, 
             }
             const size_t base = (static_cast<size_t>(y) * W + x) * spp;
             for (size_t s = 0; s < spp; ++s) {
-                for (int c = 0; c < RPF_NUM_CHANNELS; ++c) planes[c * S + base + s] = static_cast<float>(px[s].data[c]);
+                for (int c = 0; c < 7; ++c) planes[c * S + base + s] = static_cast<float>(px[s].data[c]);
+                for (int c = 7; c < RPF_NUM_CHANNELS; ++c) planes[(c + xr) * S + base + s] = static_cast<float>(px[s].data[c]);
+                for (int q = 0; q < xr; ++q) planes[(7 + q) * S + base + s] = wide->values[(base + s) * xs + q];
+                for (int q = 0; q < xf; ++q) planes[(RPF_NUM_CHANNELS + xr + q) * S + base + s] = wide->values[(base + s) * xs + xr + q];
                 rayWeight[base + s] = px[s].rayWeight;
             }
         }
-    const float *ptrs[RPF_NUM_CHANNELS];
-    for (int c = 0; c < RPF_NUM_CHANNELS; ++c) ptrs[c] = planes.data() + c * S;
-    rpf_buffer_info info{W, H, static_cast<int>(spp), sampleX0, sampleY0, 1};
-    if (rpf_buffer_write(path.c_str(), &info, ptrs, rayWeight.data()) != RPF_OK) {
+    std::vector<const float *> ptrs(nch);
+    for (int c = 0; c < nch; ++c) ptrs[c] = planes.data() + c * S;
+    rpf_buffer_info info{W, H, static_cast<int>(spp), sampleX0, sampleY0, 1, 2 + xr, 12 + xf};
+    if (rpf_buffer_write(path.c_str(), &info, ptrs.data(), rayWeight.data()) != RPF_OK) {
         if (error) *error = "cannot write " + path;
         return false;
     }

@@ -18,6 +18,14 @@
 
 namespace pbrt {
 
+// What the reference's 19-double SampleData (sd.h:46) has no room for: more random parameters (time, the
+// light sample) and more features (a texture colour) per sample, kept beside the SamplingFilm. The device record becomes
+// position | colour | pLens, extra random parameters | n0, p0, n1, p1, extra features (rpf_config.n_random / n_features).
+struct RPFB200WideRecord {
+    int nRandom = 0, nFeatures = 0;   // extra random parameters / extra features per sample
+    std::vector<float> values;        // [(y*W + x)*spp + s][nRandom + nFeatures], random parameters first; (x, y) relative to sampleBounds.pMin
+};
+
 struct RPFB200Options {
     std::vector<int> boxSizes{7};  // rpf.cpp:767 ships {7}; the comment there lists {55, 35, 17, 7}
     double sigmaSeed = 0.002;      // rpf.cpp:533
@@ -34,6 +42,7 @@ struct RPFB200Options {
     rpf_paper_opts paper{0.0, 0.0, 0.0};  // epsilon of the W ratios, low-variance guard, sigma factor of p0 / p1
     std::vector<double> sigmaSeeds;       // one per box size when not empty, instead of sigmaSeed for all
     double hdrClampSigmas = 0.0;          // > 0: spike removal after the last pass
+    const RPFB200WideRecord *wide = nullptr;  // not null: filter the wider record (the library must carry that layout)
 };
 
 struct RPFB200Report {
@@ -63,7 +72,8 @@ bool ApplyRPFFilterAndFilmB200(SamplingFilm &samplingFilm, const RPFB200Options 
 
 // Dump hook: writes the SamplingFilm as a feature-buffer file (include/rpf_b200.h rpf_buffer_write;
 // lossless, unlike the debug EXRs of visualizeSF, rpf.cpp:37-101) so a frame rendered once can be filtered anywhere.
-bool DumpSamplingFilmB200(const SamplingFilm &samplingFilm, int sampleX0, int sampleY0, const std::string &path, std::string *error);
+bool DumpSamplingFilmB200(const SamplingFilm &samplingFilm, int sampleX0, int sampleY0, const std::string &path, std::string *error,
+                          const RPFB200WideRecord *wide = nullptr);
 
 // What the GPU needs to know about a pbrt Film, from its public parts: the filter (core/film.h:78, filter.h:47-58), the
 // bounds, and the two private scalars the caller passes in (Film "scale" and "maxsampleluminance" scene parameters,

@@ -29,6 +29,12 @@
 //                                     before filtering -- what visualizeSF's six debug EXRs were for
 //     "bool rpfdumponly" false        stop after the dump: no filtering, the unfiltered samples go to the Film
 //                                     (for machines without a GPU)
+//     "string rpfrecord" "reference"  "reference" = the 19 channels of SampleData (sd.h:46-94); "wide" = north_star's wider
+//                                     feature buffer: the sample's time and the first light sample
+//                                     (u, v) as three more random parameters, the first-hit texture colour (the BSDF's
+//                                     reflectance) as three more features -- 25 channels, kept beside the SamplingFilm
+//                                     because rpf.h leaves no room in it. The sampler requests stay in the reference's
+//                                     order: the first 19 channels of a wide frame are the reference frame bit for bit.
 #include "custom/rpf.h"
 
 #include <chrono>
@@ -67,7 +73,11 @@ struct PluginOptions {
     RPFB200Options filter;
     std::string dumpPath;
     bool dumpOnly = false;
+    bool wideRecord = false;
 };
+
+// The six values per sample of the wide record: time, light sample u, v | texture colour r, g, b.
+constexpr int kWideRandom = 3, kWideFeatures = 3, kWide = kWideRandom + kWideFeatures;
 std::mutex g_optionsMutex;
 std::map<const RPFIntegrator *, PluginOptions> g_options;
 
@@ -76,6 +86,10 @@ PluginOptions optionsOf(const RPFIntegrator *self) {
     auto it = g_options.find(self);
     return it == g_options.end() ? PluginOptions() : it->second;
 }
+
+// FillSampleFilm's signature is the reference's (rpf.h:76-79): where the wide record of the frame being sampled goes is
+// handed over here by Render (one render at a time, as in pbrt).
+RPFB200WideRecord *g_fillWide = nullptr;
 
 std::string withoutExtension(const std::string &name) {
     const std::string::size_type dot = name.rfind('.');
@@ -108,9 +122,30 @@ void visualizeSF(const SamplingFilm &samplingFilm, const std::string &filename) 
 // Path tracing with feature capture: what the reference's Li does (rpf.cpp:808-939, itself pbrt's PathIntegrator::Li
 // minus the light distribution for direct lighting, rpf.cpp:871). The order of sampler requests is the reference's, so a
 // given (pixel, sample index) yields the same path and the same features.
-void RPFIntegrator::Li(const RayDifferential &cameraRay, const Scene &scene, Sampler &sampler, MemoryArena &arena,
-                       SampleData &sample, int /*depth*/) const {
+namespace {
+// Direct lighting from one light chosen uniformly: core/integrator.cpp:85-106 (UniformSampleOneLight without a light
+// distribution, as rpf.cpp:871 calls it) with the same sampler requests in the same order and the same arithmetic, so the
+// estimate is the reference's bit for bit -- restated here only to get at the light sample it draws.
+Spectrum sampleOneLightRecording(const Interaction &it, const Scene &scene, MemoryArena &arena, Sampler &sampler, Point2f *uLightOut) {
+    ProfilePhase p(Prof::DirectLighting);
+    const int nLights = int(scene.lights.size());
+    if (nLights == 0) return Spectrum(0.f);
+    const int lightNum = std::min((int)(sampler.Get1D() * nLights), nLights - 1);
+    const Float lightPdf = Float(1) / nLights;
+    const std::shared_ptr<Light> &light = scene.lights[lightNum];
+    const Point2f uLight = sampler.Get2D();
+    const Point2f uScattering = sampler.Get2D();
+    if (uLightOut) *uLightOut = uLight;
+    return EstimateDirect(it, uScattering, *light, uLight, scene, sampler, arena, false) / lightPdf;
+}
+}  // namespace
+
+// `wide` (optional, 6 floats): [1], [2] = the light sample of the first vertex that samples a light, [3..5] = the
+// reflectance of the first vertex's BSDF ("texture colour"); [0] (time) is the caller's.
+static void traceWithFeatures(const RayDifferential &cameraRay, const Scene &scene, Sampler &sampler, MemoryArena &arena,
+                              SampleData &sample, int maxDepth, Float rrThreshold, const LightDistribution *lightDistribution, float *wide) {
     ProfilePhase phase(Prof::SamplerIntegratorLi);
+    bool haveLightSample = false, haveTexture = false;
     Spectrum radiance(0.f), throughput(1.f);
     RayDifferential ray(cameraRay);
     bool lastWasSpecular = false;
@@ -145,10 +180,26 @@ void RPFIntegrator::Li(const RayDifferential &cameraRay, const Scene &scene, Sam
             --bounces;
             continue;
         }
+        if (wide && !haveTexture) {
+            // hemispherical-directional reflectance of the first surface: the texture's colour for a matte surface
+            // (LambertianReflection::rho returns R, reflection.h:394), an estimate over four fixed directions otherwise.
+            // No sampler request: the sample stream stays the reference's.
+            static const Point2f kRhoSamples[4] = {Point2f(0.125f, 0.375f), Point2f(0.625f, 0.875f), Point2f(0.375f, 0.625f), Point2f(0.875f, 0.125f)};
+            Float rgb[3];
+            isect.bsdf->rho(-ray.d, 4, kRhoSamples, BSDF_ALL).ToRGB(rgb);
+            wide[3] = rgb[0]; wide[4] = rgb[1]; wide[5] = rgb[2];
+            haveTexture = true;
+        }
 
         if (isect.bsdf->NumComponents(BxDFType(BSDF_ALL & ~BSDF_SPECULAR)) > 0) {
             ++totalPaths;
-            const Spectrum direct = throughput * UniformSampleOneLight(isect, scene, arena, sampler, false, nullptr);
+            Point2f uLight;
+            const Spectrum direct = throughput * sampleOneLightRecording(isect, scene, arena, sampler, &uLight);
+            if (wide && !haveLightSample) {
+                wide[1] = uLight.x;
+                wide[2] = uLight.y;
+                haveLightSample = true;
+            }
             if (direct.IsBlack()) ++zeroRadiancePaths;
             CHECK_GE(direct.y(), 0.f);
             radiance += direct;
@@ -195,10 +246,18 @@ void RPFIntegrator::Li(const RayDifferential &cameraRay, const Scene &scene, Sam
     sample.setL(radiance);
 }
 
+void RPFIntegrator::Li(const RayDifferential &cameraRay, const Scene &scene, Sampler &sampler, MemoryArena &arena,
+                       SampleData &sample, int /*depth*/) const {
+    traceWithFeatures(cameraRay, scene, sampler, arena, sample, maxDepth, rrThreshold, lightDistribution.get(), nullptr);
+}
+
 // rpf.cpp:220-299: one task per 16x16 tile on pbrt's pool, a sampler clone per tile seeded with the tile number, every
 // sample of every pixel through Li, the tile merged into the SamplingFilm under its mutex.
 void RPFIntegrator::FillSampleFilm(SamplingFilm &samplingFilm, const Scene &scene, const int tileSize) {
     const Bounds2i sampleBounds = camera->film->GetSampleBounds();
+    RPFB200WideRecord *wideRecord = g_fillWide;
+    const int fullW = sampleBounds.pMax.x - sampleBounds.pMin.x;
+    const int64_t spp = sampler->samplesPerPixel;
     const Vector2i extent = pixelBounds.Diagonal();  // as the reference: tiles are counted over pixelBounds (rpf.cpp:226)
     const Point2i nTiles((extent.x + tileSize - 1) / tileSize, (extent.y + tileSize - 1) / tileSize);
     ProgressReporter progress(nTiles.x * nTiles.y, "Sampling");
@@ -222,7 +281,17 @@ void RPFIntegrator::FillSampleFilm(SamplingFilm &samplingFilm, const Scene &scen
                 ray.ScaleDifferentials(1 / std::sqrt((Float)tileSampler->samplesPerPixel));
                 ++nCameraRays;
                 SampleData sample(cameraSample.pFilm, cameraSample.pLens, 0.f, rayWeight);
-                if (rayWeight > 0) Li(ray, scene, *tileSampler, arena, sample);
+                if (!wideRecord) {
+                    if (rayWeight > 0) Li(ray, scene, *tileSampler, arena, sample);
+                } else {
+                    // the values the 19-double record has no room for, at this sample's place in the frame
+                    const int64_t at = ((int64_t)(pixel.y - sampleBounds.pMin.y) * fullW + (pixel.x - sampleBounds.pMin.x)) * spp +
+                                       tileSampler->CurrentSampleNumber();
+                    float *w = wideRecord->values.data() + at * kWide;
+                    w[0] = cameraSample.time;
+                    if (rayWeight > 0)
+                        traceWithFeatures(ray, scene, *tileSampler, arena, sample, maxDepth, rrThreshold, lightDistribution.get(), w);
+                }
                 samplingTile->addSample(pixel, sample);
                 arena.Reset();
             } while (tileSampler->StartNextSample());
@@ -242,17 +311,34 @@ void RPFIntegrator::Render(const Scene &scene) {
     const int tileSize = 16;  // rpf.cpp:742
 
     SamplingFilm samplingFilm(sampleBounds);
+    RPFB200WideRecord wide;
+    if (opt.wideRecord) {
+        wide.nRandom = kWideRandom;
+        wide.nFeatures = kWideFeatures;
+        wide.values.assign(static_cast<size_t>(sampleExtent.x) * sampleExtent.y * sampler->samplesPerPixel * kWide, 0.f);
+        g_fillWide = &wide;
+    }
     FillSampleFilm(samplingFilm, scene, tileSize);
+    g_fillWide = nullptr;
     for (const auto &column : samplingFilm.samples)
         for (const auto &pixel : column) ReportValue(samplesPerPixel, static_cast<int64_t>(pixel.size()));
 
-    if (!opt.dumpPath.empty()) visualizeSF(samplingFilm, opt.dumpPath);
+    if (!opt.dumpPath.empty()) {
+        if (!opt.wideRecord)
+            visualizeSF(samplingFilm, opt.dumpPath);
+        else {
+            std::string err;
+            if (!DumpSamplingFilmB200(samplingFilm, sampleBounds.pMin.x, sampleBounds.pMin.y, opt.dumpPath, &err, &wide))
+                Error("RPF feature buffer dump to \"%s\" failed: %s", opt.dumpPath.c_str(), err.c_str());
+        }
+    }
 
     if (opt.dumpOnly) {
         Warning("RPF: \"rpfdumponly\" is set -- the samples go to the Film unfiltered");
     } else {
         RPFB200Options fo = opt.filter;
         fo.debugStats = true;
+        if (opt.wideRecord) fo.wide = &wide;
         fo.parallelFor = [](const std::function<void(int64_t)> &body, int64_t count) { ParallelFor(body, count); };
         RPFB200Report rep;
         std::string err;
@@ -347,6 +433,11 @@ RPFIntegrator *CreateRPFIntegrator(const ParamSet &params, std::shared_ptr<Sampl
         opt.filter.hdrClampSigmas = 1.0;
     } else if (mode != "defined")
         Error("\"rpfmode\" must be \"defined\", \"verbatim\" or \"paper\"; got \"%s\". Using \"defined\".", mode.c_str());
+    const std::string record = params.FindOneString("rpfrecord", "reference");
+    if (record == "wide")
+        opt.wideRecord = true;
+    else if (record != "reference")
+        Error("\"rpfrecord\" must be \"reference\" or \"wide\"; got \"%s\". Using \"reference\".", record.c_str());
     opt.dumpPath = params.FindOneString("rpfdump", "");
     opt.dumpOnly = params.FindOneBool("rpfdumponly", false);
 

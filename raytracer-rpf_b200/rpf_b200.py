@@ -78,14 +78,15 @@ def film_filter_table(kind, rx, ry, alpha=2.0):
 
 class BufferInfo(C.Structure):
     _fields_ = [("width", C.c_int), ("height", C.c_int), ("spp", C.c_int), ("sample_x0", C.c_int), ("sample_y0", C.c_int),
-                ("has_ray_weight", C.c_int)]
+                ("has_ray_weight", C.c_int), ("n_random", C.c_int), ("n_features", C.c_int)]
 
 
-def write_buffer(path, planes, width, height, spp, ray_weight=None, sample_origin=(0, 0)):
-    """Feature-buffer file (csrc/rpf_io.cpp): 19 float32 planes + optional ray weights."""
-    assert planes.dtype == np.float32 and planes.shape == (NCH, width * height * spp) and planes.flags.c_contiguous
-    info = BufferInfo(width, height, spp, sample_origin[0], sample_origin[1], 0)
-    ptrs = (C.c_void_p * NCH)(*[planes[c].ctypes.data for c in range(NCH)])
+def write_buffer(path, planes, width, height, spp, ray_weight=None, sample_origin=(0, 0), n_random=2, n_features=12):
+    """Feature-buffer file (csrc/rpf_io.cpp): 5 + n_random + n_features float32 planes + optional ray weights."""
+    nch = 5 + n_random + n_features
+    assert planes.dtype == np.float32 and planes.shape == (nch, width * height * spp) and planes.flags.c_contiguous
+    info = BufferInfo(width, height, spp, sample_origin[0], sample_origin[1], 0, n_random, n_features)
+    ptrs = (C.c_void_p * nch)(*[planes[c].ctypes.data for c in range(nch)])
     rw = None if ray_weight is None else np.ascontiguousarray(ray_weight, np.float32)
     rc = hostio().rpf_buffer_write(path.encode(), C.byref(info), ptrs, None if rw is None else _p(rw))
     if rc != 0:
@@ -99,7 +100,7 @@ def read_buffer(path):
     if rc != 0:
         raise RPFError(f"{path}: not a feature-buffer file ({rc})")
     S = info.width * info.height * info.spp
-    planes, rw = np.empty((NCH, S), np.float32), np.empty(S, np.float32)
+    planes, rw = np.empty((5 + info.n_random + info.n_features, S), np.float32), np.empty(S, np.float32)
     rc = hostio().rpf_buffer_read(path.encode(), _p(planes), _p(rw))
     if rc != 0:
         raise RPFError(f"{path}: truncated or unreadable ({rc})")

@@ -108,3 +108,44 @@ def test_pbrt_renders_b200_filters_film_writes(tmp_path, boxes, seed, ngpus):
     assert np.array_equal(np.isfinite(img), m)
     assert np.abs(img[m] - ref[m]).max() <= tol
     assert np.abs(ref[m] - film_of(planes, planes[2:5].astype(np.float64), W, H, P)[m]).max() > 0 or seed < 0.01
+
+
+@needs_binary
+def test_wide_record_producer_keeps_the_reference_record(tmp_path):
+    """SURVEY.md 8(f) N3, producer side: "string rpfrecord" "wide" adds time, the first light sample and the first-hit
+    texture colour (25 channels) without touching the sampler's request order -- the 19 reference channels of the wide
+    frame are the reference frame bit for bit."""
+    import rpf_b200
+    d19, d25 = tmp_path / "ref.rpfb", tmp_path / "wide.rpfb"
+    r, _ = render(tmp_path, f'Integrator "rpf" "string rpfdump" "{d19}" "bool rpfdumponly" "true"')
+    assert r.returncode == 0, r.stderr[-2000:]
+    r, _ = render(tmp_path, f'Integrator "rpf" "string rpfrecord" "wide" "string rpfdump" "{d25}" "bool rpfdumponly" "true"')
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "unused" not in (r.stdout + r.stderr).lower()
+    a, _, ia = rpf_b200.read_buffer(str(d19))
+    b, _, ib = rpf_b200.read_buffer(str(d25))
+    assert (ia["n_random"], ia["n_features"]) == (2, 12) and (ib["n_random"], ib["n_features"]) == (5, 15) and b.shape[0] == 25
+    assert np.array_equal(b[:7], a[:7]) and np.array_equal(b[10:22], a[7:19])
+    t, lu, lv, tex = b[7], b[8], b[9], b[22:25]
+    assert 0 <= t.min() and t.max() < 1 and t.std() > 0.2                      # the sample's time
+    hit = np.abs(a[7:10]).sum(axis=0) > 0                                      # a first hit exists (n0 != 0)
+    assert lu[hit].std() > 0.2 and lv[hit].std() > 0.2 and lu.max() < 1        # the light sample is a real random parameter
+    assert (tex >= 0).all() and tex[:, hit].max() > 0.3 and (tex[:, ~hit] == 0).all()   # reflectance of what was hit
+
+
+@needs_binary
+@pytest.mark.gpu
+def test_wide_record_through_the_b200(tmp_path):
+    import rpf_b200
+    dump = tmp_path / "wide.rpfb"
+    W, H, P = 64, 48, 8
+    r, out = render(tmp_path, f'Integrator "rpf" "string rpfrecord" "wide" "integer boxsizes" [9 7] "float sigmaseed" [0.5] "string rpfdump" "{dump}"')
+    assert r.returncode == 0, (r.stdout + r.stderr)[-3000:]
+    planes, _, info = rpf_b200.read_buffer(str(dump))
+    assert planes.shape[0] == 25
+    o = ob.oracle_filter(planes, W, H, P, [9, 7], seed=0.5, threads=8, layout=(5, 15))
+    img = read_pfm(out)
+    ref = film_of(planes, o["colors"], W, H, P)
+    m = np.isfinite(ref)
+    assert np.array_equal(np.isfinite(img), m)
+    assert np.abs(img[m] - ref[m]).max() <= 1e-5 * max(1.0, float(np.abs(ref[m]).max()))
