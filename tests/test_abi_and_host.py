@@ -109,7 +109,12 @@ def test_feature_buffer_file_round_trip(tmp_path):
     rpf_b200.write_buffer(path, planes, W, H, P, ray_weight=rw, sample_origin=(-2, 3))
     got, grw, info = rpf_b200.read_buffer(path)
     assert np.array_equal(got, planes) and np.array_equal(grw, rw)
-    assert info == dict(width=W, height=H, spp=P, sample_x0=-2, sample_y0=3, has_ray_weight=1)
+    assert info == dict(width=W, height=H, spp=P, sample_x0=-2, sample_y0=3, has_ray_weight=1, n_random=2, n_features=12)
+    # a wider record carries its channel layout in the header
+    wide = rpf_b200.synth_planes(W, H, P, seed=5, kind=0, n_random=5, n_features=15)
+    rpf_b200.write_buffer(path, wide, W, H, P, n_random=5, n_features=15)
+    got, _, info = rpf_b200.read_buffer(path)
+    assert got.shape == (25, W * H * P) and np.array_equal(got, wide) and (info["n_random"], info["n_features"]) == (5, 15)
     # no ray weights stored -> ones
     rpf_b200.write_buffer(path, planes, W, H, P)
     _, grw, info = rpf_b200.read_buffer(path)
