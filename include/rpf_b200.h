@@ -113,6 +113,10 @@ int rpf_filter(rpf_ctx *ctx, const int *box_sizes, int n_iter, double sigma_fc_s
  * current colours, writes the next colours for those rows; rpf_swap_colors makes them current. Rows outside
  * [y0,y1) of the next buffer are whatever the caller puts there (halo exchange) or stale. */
 int rpf_filter_rows(rpf_ctx *ctx, int box_size, double sigma_fc_seed, int y0, int y1);
+/* Same for two row ranges at once, [y0,y1) and [y2,y3) with y2 >= y1, in ONE set of kernel launches: the rows next to the
+ * upper and the lower edge of a band, which must be finished (and on their way to the neighbouring bands) before the
+ * interior rows -- two thin slabs launched separately would leave most of the GPU idle. */
+int rpf_filter_rows2(rpf_ctx *ctx, int box_size, double sigma_fc_seed, int y0, int y1, int y2, int y3);
 int rpf_swap_colors(rpf_ctx *ctx);
 /* Optional, not in the reference (which takes every sample of the box, rpf.cpp:556-586, README.md:27): random neighbour
  * subsampling as in Sen & Darabi. A neighbour sample that passed the 3-sigma test stays with probability

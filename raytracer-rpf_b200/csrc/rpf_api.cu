@@ -19,7 +19,7 @@ struct rpf_ctx;
 // One channel layout = one compiled copy of the kernels (rpf_layouts.cuh) and of their launch code (rpf_launch.inl).
 struct LayoutOps {
     int nr, nf, nch, n_joint, rec19;
-    int (*launch_rows)(rpf_ctx *, int box, double seed, int y0, int y1);
+    int (*launch_rows)(rpf_ctx *, int box, double seed, int y0, int y1, int y2, int y3);  // rows [y0,y1) and, if y3 > y2, [y2,y3)
     int (*configure)(rpf_ctx *);
 };
 
@@ -360,7 +360,7 @@ extern "C" int rpf_upload(rpf_ctx *ctx, const float *const planes[RPF_NUM_CHANNE
     if (!ctx->shards.empty()) {  // every band takes its rows (own + halo) of every plane: y is the slow index, a band is contiguous
         const size_t row = static_cast<size_t>(ctx->cfg.width) * ctx->cfg.spp;
         for (size_t g = 0; g < ctx->shards.size(); ++g) {
-            const float *sub[RPF_NUM_CHANNELS];
+            const float *sub[32];
             for (int c = 0; c < ctx->ops->nch; ++c) {
                 if (!planes[c]) return fail(ctx, RPF_ERR_INVALID, "rpf_upload: plane %d is null", c);
                 sub[c] = planes[c] + ctx->shard_buf0[g] * row;
@@ -508,7 +508,9 @@ static const LayoutOps *find_layout(int n_random, int n_features) {
     return nullptr;
 }
 
-static int launch_rows(rpf_ctx *ctx, int box, double seed, int y0, int y1) { return ctx->ops->launch_rows(ctx, box, seed, y0, y1); }
+static int launch_rows(rpf_ctx *ctx, int box, double seed, int y0, int y1, int y2 = 0, int y3 = 0) {
+    return ctx->ops->launch_rows(ctx, box, seed, y0, y1, y2, y3);
+}
 
 extern "C" int rpf_num_channels(const rpf_ctx *ctx) { return ctx && ctx->ops ? ctx->ops->nch : RPF_NUM_CHANNELS; }
 extern "C" int rpf_num_pairs(const rpf_ctx *ctx) { return ctx && ctx->ops ? ctx->ops->n_joint : 96; }
@@ -539,6 +541,22 @@ extern "C" int rpf_filter_rows(rpf_ctx *ctx, int box_size, double sigma_fc_seed,
     if (rc != RPF_OK) return rc;
     CU(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
     rc = launch_rows(ctx, box_size, sigma_fc_seed, y0, y1);
+    if (rc != RPF_OK) return rc;
+    CU(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    ctx->timing_pending = true;
+    return RPF_OK;
+}
+
+// Two row ranges [y0,y1) and [y2,y3), y2 >= y1, through ONE set of launches (what the band schedule does with the rows next to
+// the two edges of a band: rpf_bands.inl).
+extern "C" int rpf_filter_rows2(rpf_ctx *ctx, int box_size, double sigma_fc_seed, int y0, int y1, int y2, int y3) {
+    if (!ctx) return RPF_ERR_INVALID;
+    NOT_SHARDED(ctx, "rpf_filter_rows2");
+    CU(ctx, cudaSetDevice(ctx->cfg.device));
+    int rc = finish_timing(ctx);
+    if (rc != RPF_OK) return rc;
+    CU(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    rc = launch_rows(ctx, box_size, sigma_fc_seed, y0, y1, y2, y3);
     if (rc != RPF_OK) return rc;
     CU(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
     ctx->timing_pending = true;
@@ -957,8 +975,11 @@ static int create_sharded(rpf_ctx **out, const rpf_config *cfg, int ndev) {
     }
     const int max_box = cfg->max_box > 0 ? cfg->max_box : 55;
     if ((max_box & 1) == 0) return fail(nullptr, RPF_ERR_INVALID, "rpf_create: max_box must be odd");
+    const LayoutOps *ops = find_layout(cfg->n_random, cfg->n_features);
+    if (!ops) return fail(nullptr, RPF_ERR_UNSUPPORTED, "rpf_create: no kernels for %d random parameters and %d features in this build", cfg->n_random, cfg->n_features);
     rpf_ctx *par = new rpf_ctx;
     par->cfg = *cfg;
+    par->ops = ops;
     par->S = 1ull * cfg->width * cfg->height * cfg->spp;
     par->npix = cfg->width * cfg->height;
     par->halo_rows = b_delta(max_box);

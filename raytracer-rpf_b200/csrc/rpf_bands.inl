@@ -119,8 +119,13 @@ int band_pass(rpf_ctx *c, int box, double seed, int o0, int o1, int d, bool up, 
     const int e = ((d + kEdgeQuantum - 1) / kEdgeQuantum) * kEdgeQuantum;
     const int top1 = up ? std::min(o0 + e, o1) : o0;
     const int bot0 = down ? std::max(o1 - e, top1) : o1;
-    if (top1 > o0 && (rc = launch_rows(c, box, seed, o0, top1)) != RPF_OK) return rc;
-    if (o1 > bot0 && (rc = launch_rows(c, box, seed, bot0, o1)) != RPF_OK) return rc;
+    // both edge slabs in ONE set of launches (a chunk with a gap): two slabs of a few dozen rows each would leave most of
+    // the SMs idle in the tile-granular kernels
+    if (top1 > o0 && o1 > bot0) rc = launch_rows(c, box, seed, o0, top1, bot0, o1);
+    else if (top1 > o0) rc = launch_rows(c, box, seed, o0, top1);
+    else if (o1 > bot0) rc = launch_rows(c, box, seed, bot0, o1);
+    else rc = RPF_OK;
+    if (rc != RPF_OK) return rc;
     if ((rc = hand_over()) != RPF_OK) return rc;
     if (bot0 > top1 && (rc = launch_rows(c, box, seed, top1, bot0)) != RPF_OK) return rc;
     return RPF_OK;

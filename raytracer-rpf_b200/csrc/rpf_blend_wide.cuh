@@ -27,7 +27,7 @@ __global__ void __launch_bounds__(KW_THREADS, 4) blend_wide_kernel(const General
     const int W = p.f.W, H = p.f.H, P = p.f.P, B = p.box;
     const size_t S = p.f.S;
     const int pl = strip_order(blockIdx.x, p.f.W, p.nrows);
-    const int py = p.row0 + pl / W, px = pl - (pl / W) * W;
+    const int py = chunk_row(pl / W, p.row0, p.gap_at, p.gap), px = pl - (pl / W) * W;
     const size_t pix = static_cast<size_t>(py) * W + px;
     const uint32_t base = static_cast<uint32_t>(pix * P);
     const uint32_t *mask = p.mask + static_cast<size_t>(pl) * p.pl.mw;

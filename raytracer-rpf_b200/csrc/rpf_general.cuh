@@ -83,6 +83,7 @@ struct GeneralParams {
     double seed;
     double w_eps;         // paper mode: epsilon of the W ratios (0 = reference)
     int row0, nrows;      // pixel rows of this chunk
+    int gap_at, gap;      // chunk_row(): `gap` context rows are skipped after the chunk's first gap_at rows (none: gap = 0)
     uint32_t *mask;       // [chunk pixels][mw]
     double *rec;          // [chunk pixels][REC_DOUBLES]
     uint8_t *bins_scratch;  // [kb_grid][19][nq*4] when bins do not fit in shared memory
@@ -162,6 +163,10 @@ __device__ __forceinline__ int strip_order_n(int w, int W, int nrows, int strip)
     return y * W + x0 + (r - y * sw);
 }
 __device__ __forceinline__ int strip_order(int w, int W, int nrows) { return strip_order_n(w, W, nrows, STRIP_W); }
+// Context row of chunk-local row r. A chunk may consist of two row ranges with `gap` rows left out after its first gap_at
+// rows: the band schedule filters the rows next to BOTH band edges in one set of launches (rpf_bands.inl), which keeps the
+// grids large enough to fill the GPU.
+__device__ __forceinline__ int chunk_row(int r, int row0, int gap_at, int gap) { return row0 + r + (r >= gap_at ? gap : 0); }
 
 // candidate t -> global sample index, or false when the neighbour pixel is out of bounds (rpf.cpp:569)
 __device__ __forceinline__ bool candidate_sample(const CandDecode &cd, int t, int px, int py, int B, int P, int W, int H, uint32_t &g,
@@ -549,7 +554,7 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
         __syncthreads();
         if (static_cast<int>(ks.pixel) >= npix) break;
         const int pl = strip_order(static_cast<int>(ks.pixel), W, p.nrows);
-        const int py = p.row0 + pl / W, px = pl - (pl / W) * W;
+        const int py = chunk_row(pl / W, p.row0, p.gap_at, p.gap), px = pl - (pl / W) * W;
         const size_t pix = static_cast<size_t>(py) * W + px;
         const uint32_t *mask = p.mask + static_cast<size_t>(pl) * L.mw;
         double *rec = p.rec + static_cast<size_t>(pl) * REC_DOUBLES;
@@ -738,7 +743,7 @@ __global__ void __launch_bounds__(KC_THREADS, 4) blend_kernel(const GeneralParam
     const int W = p.f.W, H = p.f.H, P = p.f.P, B = p.box;
     const size_t S = p.f.S;
     const int pl = strip_order(blockIdx.x, W, p.nrows);
-    const int py = p.row0 + pl / W, px = pl - (pl / W) * W;
+    const int py = chunk_row(pl / W, p.row0, p.gap_at, p.gap), px = pl - (pl / W) * W;
     const size_t pix = static_cast<size_t>(py) * W + px;
     const uint32_t base = static_cast<uint32_t>(pix * P);
     const uint32_t *mask = p.mask + static_cast<size_t>(pl) * p.pl.mw;

@@ -106,7 +106,7 @@ __global__ void __launch_bounds__(KL_THREADS, 1) dependency_large_kernel(const G
         __syncthreads();
         if (static_cast<int>(ks.pixel) >= npix) break;
         const int pl = strip_order(static_cast<int>(ks.pixel), W, p.nrows);
-        const int py = p.row0 + pl / W, px = pl - (pl / W) * W;
+        const int py = chunk_row(pl / W, p.row0, p.gap_at, p.gap), px = pl - (pl / W) * W;
         const size_t pix = static_cast<size_t>(py) * W + px;
         const uint32_t *mask = p.mask + static_cast<size_t>(pl) * L.mw;
         double *rec = p.rec + static_cast<size_t>(pl) * REC_DOUBLES;

@@ -127,7 +127,9 @@ static int ensure_pstat(rpf_ctx *ctx, const FrameView &f, int y0, int y1) {
     return RPF_OK;
 }
 
-static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
+// Rows [y0,y1) and, when y3 > y2, rows [y2,y3) as well (y2 >= y1): both ranges go through ONE set of launches as a chunk
+// with a gap (chunk_row, rpf_general.cuh).
+static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1, int y2 = 0, int y3 = 0) {
     GeneralParams p{};
     const long long ncap = 1ll * box * box * ctx->cfg.spp;
     // Up to 65,535 candidates: dependency_kernel. Beyond: dependency_kernel for the pixels that accept at most 65,535
@@ -161,9 +163,11 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
     if (rc != RPF_OK) return rc;
     const int W = ctx->cfg.width;
     const size_t per_pixel = static_cast<size_t>(p.pl.mw) * 4 + REC_DOUBLES * 8;
+    const int n1 = y1 - y0, n2 = y3 > y2 ? y3 - y2 : 0, nv = n1 + n2;  // rows of the first range, of the second, together
     long long rows = static_cast<long long>(ctx->scratch_budget / (per_pixel * W));
+    if (rows > 8) rows &= ~7ll;  // chunks start on a multiple of the membership tile height, so the gap does too
     if (rows < 1) rows = 1;
-    if (rows > y1 - y0) rows = y1 - y0;
+    if (rows > nv) rows = nv;
     const long long chunk_px = rows * W;
     auto grid_for = [&](GeneralPlan &L) -> int {
         int occ = 0;
@@ -240,9 +244,12 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
     p.dbg_wrc = ctx->d_dbg_wrc;
     p.counters = ctx->d_counters;
     p.probe = DebugProbe{ctx->d_probe_mi ? ctx->probe_pixel : -1, ctx->d_probe_mi, ctx->d_probe_marg};
-    for (int r0 = y0; r0 < y1; r0 += static_cast<int>(rows)) {
-        p.row0 = r0;
-        p.nrows = r0 + rows <= y1 ? static_cast<int>(rows) : y1 - r0;
+    for (int v0 = 0; v0 < nv; v0 += static_cast<int>(rows)) {  // v0: first row of the chunk, counted over both ranges
+        p.nrows = v0 + rows <= nv ? static_cast<int>(rows) : nv - v0;
+        p.row0 = v0 < n1 ? y0 + v0 : y2 + (v0 - n1);
+        const bool straddles = n2 > 0 && v0 < n1 && v0 + p.nrows > n1;
+        p.gap_at = straddles ? n1 - v0 : 0x7fffffff;
+        p.gap = straddles ? y2 - y1 : 0;
         const unsigned npx = static_cast<unsigned>(p.nrows * W);
         CU(ctx, cudaMemsetAsync(ctx->d_work, 0, 2 * sizeof(unsigned int), ctx->stream));
         {
@@ -253,6 +260,8 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
             m.box = box;
             m.row0 = p.row0;
             m.nrows = p.nrows;
+            m.gap_at = p.gap_at;
+            m.gap = p.gap;
             m.mw = p.pl.mw;
             m.sub = ctx->sub;
             membership_tile(box, m.tx, m.ty);
@@ -304,22 +313,28 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
         ctx->launches += 4;
         CU(ctx, cudaGetLastError());
     }
-    ctx->pixels_filtered += 1ll * (y1 - y0) * W;
+    ctx->pixels_filtered += 1ll * nv * W;
     return RPF_OK;
 }
 
-static int launch_rows(rpf_ctx *ctx, int box, double seed, int y0, int y1) {
+static int launch_rows(rpf_ctx *ctx, int box, double seed, int y0, int y1, int y2, int y3) {
     if (!ctx->uploaded) return fail(ctx, RPF_ERR_STATE, "rpf_filter: no samples uploaded");
     if (box < 1 || (box & 1) == 0) return fail(ctx, RPF_ERR_INVALID, "box size %d must be odd and positive (rpf.cpp:561)", box);
     if (y0 < 0 || y1 > ctx->cfg.height || y0 >= y1) return fail(ctx, RPF_ERR_INVALID, "bad row range [%d,%d)", y0, y1);
+    if (y3 > y2 && (y2 < y1 || y3 > ctx->cfg.height)) return fail(ctx, RPF_ERR_INVALID, "bad second row range [%d,%d)", y2, y3);
     if (!(seed > 0.0)) return fail(ctx, RPF_ERR_INVALID, "sigma_fc_seed must be positive");
+    if (y3 > y2 && y2 == y1) { y1 = y3; y2 = y3 = 0; }  // adjacent ranges are one range
 #if !RPF_FULL
-    return launch_general(ctx, box, seed, y0, y1);  // wider layouts: the general path only
+    return launch_general(ctx, box, seed, y0, y1, y2, y3);  // wider layouts: the general path only
 #else
     FilterParams p{};
     // the fused shared-memory-resident kernel serves small neighbourhoods; everything else takes the general path
     if (ctx->force_general || !plan_smem(1ll * box * box * ctx->cfg.spp, ctx->cfg.spp, ctx->max_dyn_smem, p.sm))
-        return launch_general(ctx, box, seed, y0, y1);
+        return launch_general(ctx, box, seed, y0, y1, y2, y3);
+    if (y3 > y2) {  // the fused kernel takes one contiguous range per launch
+        const int rc2 = launch_rows(ctx, box, seed, y2, y3, 0, 0);
+        if (rc2 != RPF_OK) return rc2;
+    }
     int rc = ensure_gtab(ctx, p.sm.ncap);
     if (rc != RPF_OK) return rc;
     p.f = FrameView{ctx->d_planes, ctx->S, ctx->cfg.width, ctx->cfg.height, ctx->cfg.spp};

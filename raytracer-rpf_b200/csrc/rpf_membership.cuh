@@ -29,6 +29,7 @@ struct MembershipParams {
     const double *pstat;   // [W*H][2 NF] per-pixel feature mean[NF], 3 sigma[NF]
     uint32_t *mask;        // [chunk pixels][mw]
     int box, row0, nrows, mw;
+    int gap_at, gap;       // chunk_row() (rpf_general.cuh); gap_at is a multiple of the tile height: no tile straddles the gap
     int tx, ty, tiles_x;   // tile shape and tiles per row
     int col_rows;          // ty + box - 1: neighbour-pixel rows per column of the tile's union
     int rb_rows;           // rows staged in shared memory at a time (col_rows unless spp is very large)
@@ -50,10 +51,10 @@ __global__ void __launch_bounds__(KM_MAX_THREADS) membership_kernel(const Member
     const int tiles_y = (p.nrows + p.ty - 1) / p.ty;
     const int tl = strip_order_n(blockIdx.x, p.tiles_x, tiles_y, STRIP_W / p.tx);
     const int tile_x = tl % p.tiles_x, tile_y = tl / p.tiles_x;
-    const int x0 = tile_x * p.tx, y0 = p.row0 + tile_y * p.ty;
+    const int x0 = tile_x * p.tx, y0 = chunk_row(tile_y * p.ty, p.row0, p.gap_at, p.gap);
     const int lx = tid % p.tx, ly = tid / p.tx;
     const int px = x0 + lx, py = y0 + ly;
-    const bool live = px < W && py < p.row0 + p.nrows;
+    const bool live = px < W && tile_y * p.ty + ly < p.nrows;
 
     double mu[NF], sd3[NF];
     if (live) {
@@ -65,7 +66,7 @@ __global__ void __launch_bounds__(KM_MAX_THREADS) membership_kernel(const Member
         for (int k = 0; k < NF; ++k) { mu[k] = 0.0; sd3[k] = 0.0; }
     }
     const uint64_t ckey = SUBSAMPLED ? rpf_subsample_centre_key(p.sub.seed, B, px, py + p.sub.row_g0) : 0ull;
-    uint32_t *mrow = p.mask + (static_cast<size_t>(py - p.row0) * W + px) * p.mw;
+    uint32_t *mrow = p.mask + (static_cast<size_t>(tile_y * p.ty + ly) * W + px) * p.mw;
     unsigned long long buf = 0ull;
     int nbits = 0, wi = 0;
 
@@ -148,7 +149,7 @@ __global__ void __launch_bounds__(KO_WARPS * 32) ordered_stats_kernel(const Gene
     const int W = p.f.W, P = p.f.P, B = p.box, bd = (B - 1) / 2;
     if (blockIdx.x * KO_WARPS + warp >= p.nrows * W) return;
     const int pl = strip_order(blockIdx.x * KO_WARPS + warp, W, p.nrows);
-    const int py = p.row0 + pl / W, px = pl - (pl / W) * W;
+    const int py = chunk_row(pl / W, p.row0, p.gap_at, p.gap), px = pl - (pl / W) * W;
     const size_t pix = static_cast<size_t>(py) * W + px;
     const uint32_t base = static_cast<uint32_t>(pix * P);
     const uint32_t *mask = p.mask + static_cast<size_t>(pl) * p.pl.mw;

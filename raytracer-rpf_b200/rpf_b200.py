@@ -29,7 +29,7 @@ ABI_SYMBOLS = [
     "rpf_set_paper_mode", "rpf_filter_sigmas", "rpf_hdr_clamp", "rpf_fused_max_candidates",
     "rpf_band_plan", "rpf_band_unique_id", "rpf_band_attach", "rpf_host_alloc", "rpf_host_free",
     "rpf_set_debug_pixel", "rpf_download_debug_mi", "rpf_reset_colors",
-    "rpf_num_channels", "rpf_num_pairs", "rpf_layout_supported", "rpf_synth_planes_layout",
+    "rpf_num_channels", "rpf_num_pairs", "rpf_layout_supported", "rpf_synth_planes_layout", "rpf_filter_rows2",
 ]
 
 
@@ -152,6 +152,7 @@ def lib():
         L.rpf_upload_colors_f64.argtypes = [vp, vp]
         L.rpf_filter.argtypes = [vp, vp, i, d]
         L.rpf_filter_rows.argtypes = [vp, i, d, i, i]
+        L.rpf_filter_rows2.argtypes = [vp, i, d, i, i, i, i]
         L.rpf_set_paper_mode.argtypes = [vp, vp]
         L.rpf_filter_sigmas.argtypes = [vp, vp, vp, i]
         L.rpf_hdr_clamp.argtypes = [vp, d, i, i]
@@ -343,6 +344,10 @@ class RPFFilter:
 
     def filter_rows(self, box, y0, y1, sigma_fc_seed=0.002):
         self._check(lib().rpf_filter_rows(self._h, box, sigma_fc_seed, y0, y1))
+
+    def filter_rows2(self, box, y0, y1, y2, y3, sigma_fc_seed=0.002):
+        """Rows [y0,y1) and [y2,y3) in one set of launches (the two edge slabs of a band)."""
+        self._check(lib().rpf_filter_rows2(self._h, box, sigma_fc_seed, y0, y1, y2, y3))
 
     def set_subsampling(self, keep_probability, rng_seed=0, global_row0=0):
         """Random neighbour subsampling (include/rpf_subsample.h); keep_probability >= 1 switches it off."""

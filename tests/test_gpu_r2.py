@@ -105,6 +105,37 @@ def test_row_ranges_in_any_order(boxes):
     assert np.array_equal(whole, parts)
 
 
+@pytest.mark.parametrize("box,ranges", [(17, (0, 8, 24, 32)), (17, (8, 16, 40, 48)), (7, (0, 8, 40, 48)), (35, (0, 16, 32, 48))])
+def test_two_row_ranges_in_one_set_of_launches(box, ranges, monkeypatch):
+    """The band schedule filters the rows next to both band edges as ONE chunk with a gap (rpf_filter_rows2), then the
+    interior: together bit-identical to the whole frame. A tiny scratch budget puts chunk boundaries and the gap in
+    different places."""
+    import rpf_b200
+    W, H, P = 40, 48, 8
+    planes = rpf_b200.synth_planes(W, H, P, seed=31, kind=0)
+    f = rpf_b200.RPFFilter(W, H, P)
+    f.upload(planes)
+    f.apply([box], 0.5)
+    whole = f.download_colors_f64()
+    f.close()
+    y0, y1, y2, y3 = ranges
+    for budget in (None, "1"):
+        if budget:
+            monkeypatch.setenv("RPF_SCRATCH_MB", budget)
+        f = rpf_b200.RPFFilter(W, H, P)
+        f.upload(planes)
+        f.filter_rows2(box, y0, y1, y2, y3, 0.5)
+        if y0 > 0:
+            f.filter_rows(box, 0, y0, 0.5)
+        f.filter_rows(box, y1, y2, 0.5)
+        if y3 < H:
+            f.filter_rows(box, y3, H, 0.5)
+        f.swap_colors()
+        parts = f.download_colors_f64()
+        f.close()
+        assert np.array_equal(whole, parts), (box, ranges, budget)
+
+
 def _n_gpus():
     import torch
     return torch.cuda.device_count()
