@@ -62,6 +62,8 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--no-calibrate", action="store_true", help="N > 1: keep the geometric equal-work band plan (rpf_band_plan) instead of "
+                                                                "re-cutting the bands from one measured step")
     a = ap.parse_args()
     w, h, p = CONFIGS[a.config]
     a.width, a.height, a.spp = a.width or w, a.height or h, a.spp or p
@@ -321,22 +323,54 @@ def main():
     if args.band:  # one band of a sharded frame alone on this GPU (ncu captures): no neighbours, no exchange
         er, ew = (int(v) for v in args.band.split("/"))
         emulate = bands.make_band(er, ew, H, boxes)
+    def setup(band):
+        """Planes of the band (own + halo rows) in pinned memory, a context holding them, attached to its neighbours."""
+        lh = band.local_height
+        host = torch.empty((19, W * lh * P), dtype=torch.float32, pin_memory=True)
+        planes = host.numpy()
+        frame.rect(0, band.buf0, W, lh, out=planes)
+        ctx = rpf_b200.RPFFilter(W, lh, P, device=local_rank, debug=True)
+        if emulate is None:
+            bands.attach(ctx, band, dist)  # rpf_band_attach: the library exchanges the halos itself (NCCL) from here on
+        else:
+            ctx.attach_band(H, band.buf0, band.buf0, band.buf1, 0, 1)  # global rows for the RNG; every held row "owned" below
+        if args.subsample < 1.0:
+            ctx.set_subsampling(args.subsample, 1234, band.buf0)
+        ctx.upload(planes)
+        ctx.synchronize()
+        return ctx, host, planes
+
+    def gather(obj):
+        if dist is None:
+            return [obj]
+        box = [None] * world
+        dist.all_gather_object(box, obj)
+        return box
+
     band = emulate or bands.make_band(rank, world, H, boxes)
+    ctx, host, planes = setup(band)
+    calibration = None
+    if world > 1 and emulate is None and not args.no_calibrate:
+        # Equal-work bands from MEASURED work (SURVEY.md 8(e)): one untimed step with the geometric plan, every band's device
+        # time spread over its rows as a cost per row, bands re-cut so that each carries the same cost, contexts rebuilt.
+        ctx.reset_colors(); ctx.apply(boxes, args.seed); ctx.synchronize()
+        ctx.reset_colors(); ctx.apply(boxes, args.seed); ctx.synchronize()
+        t_mine = ctx.stats()["last_filter_ms"]
+        seen = gather((band.own0, band.own1, t_mine))
+        weight = np.zeros(H)
+        for a, b, t in seen:
+            weight[a:b] = t / (b - a)
+        ctx.close()
+        del host, planes
+        if dist is not None:
+            dist.barrier()
+        old_rows = [[a, b] for a, b, _ in seen]
+        band = bands.make_band(rank, world, H, boxes, row_weight=weight)
+        ctx, host, planes = setup(band)
+        calibration = {"geometric_plan": old_rows, "measured_ms": [t for _, _, t in seen]}
     lh = band.local_height
     S_loc = W * lh * P
-    host = torch.empty((19, S_loc), dtype=torch.float32, pin_memory=True)
-    planes = host.numpy()
-    frame.rect(0, band.buf0, W, lh, out=planes)
     out_host = torch.empty((3, S_loc), dtype=torch.float32, pin_memory=True)
-    ctx = rpf_b200.RPFFilter(W, lh, P, device=local_rank, debug=True)
-    if emulate is None:
-        bands.attach(ctx, band, dist)  # rpf_band_attach: the library exchanges the halos itself (NCCL) from here on
-    else:
-        ctx.attach_band(H, band.buf0, band.buf0, band.buf1, 0, 1)  # global rows for the RNG; every held row "owned" below
-    if args.subsample < 1.0:
-        ctx.set_subsampling(args.subsample, 1234, band.buf0)
-    ctx.upload(planes)
-    ctx.synchronize()
     o0, o1 = band.local_own
 
     def step():
@@ -382,13 +416,6 @@ def main():
     ktimes = ctx.kernel_times()
     ctx.set_profiling(False)
     kern_mine = {k: {"ms": ms, "launches": n} for k, (ms, n) in ktimes.items() if n}
-
-    def gather(obj):
-        if dist is None:
-            return [obj]
-        box = [None] * world
-        dist.all_gather_object(box, obj)
-        return box
 
     per_rank = gather({"dev_s": my_dev_s, "wall": wall, "kern": kern_mine, "st": st, "rows": [band.own0, band.own1]})
     dev_s = max(r["dev_s"] for r in per_rank)
@@ -494,14 +521,17 @@ def main():
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dev_s / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f64", "data": "rendered" if args.buffer else "synthetic", "config": config_of(args, boxes),
-        "sharding": {"bands": [r["rows"] for r in per_rank], "plan": "equal work (rpf_band_plan)", "halo_rows": band.own0 - band.buf0 if band.rank else band.buf1 - band.own1,
+        "sharding": {"bands": [r["rows"] for r in per_rank],
+                     "plan": "equal work, geometric (rpf_band_plan)" if calibration is None else "equal work, from one measured step (rpf_band_plan_weighted)",
+                     "calibration": calibration, "halo_rows": band.own0 - band.buf0 if band.rank else band.buf1 - band.own1,
                      "exchange": "ncclSend/ncclRecv inside rpf_filter, edge rows first, interior overlapped" if world > 1 else "none",
                      "halo_bytes_per_step": sum(r["st"]["halo_bytes"] for r in per_rank) / args.steps},
         "mean_neighbourhood": nbh_sum / max(1, px_filtered),
         "wall_ms_per_step": wall / args.steps * 1e3, "gpu_launches": int(sum(r["st"]["kernel_launches"] for r in per_rank)),
         "nan_channels": int(sum(r["st"]["nan_channels"] for r in per_rank)) // max(1, args.steps),
         "clocks": sampler.summary(), "roofline": roof, "kernels": kern,
-        "ranks": {"step_ms": spread([r["dev_s"] / args.steps * 1e3 for r in per_rank])},
+        "ranks": {"step_ms": spread([r["dev_s"] / args.steps * 1e3 for r in per_rank]),
+                  "step_ms_each": [round(r["dev_s"] / args.steps * 1e3, 2) for r in per_rank]},
         "checksum": f"{checksum:016x}", "parity": parity,
         "checksum_sigma2": None if checksum_wide is None else f"{checksum_wide:016x}", "parity_sigma2": parity_wide, "e2e": e2e,
     }

@@ -204,6 +204,10 @@ int rpf_film_filter_table(int kind, float radius_x, float radius_y, float alpha,
  * RPF_ERR_INVALID if the frame is too short for that. */
 int rpf_band_plan(int height, int n_bands, const int *box_sizes, int n_iter, int *own0 /* [n_bands + 1] */);
 
+/* Same with a MEASURED weight per row (row_weight[height], e.g. a band's step time divided by its rows, from one untimed
+ * calibration step with the geometric plan) instead of the geometric model; NULL = rpf_band_plan. */
+int rpf_band_plan_weighted(int height, int n_bands, const int *box_sizes, int n_iter, const double *row_weight, int *own0);
+
 /* One band per PROCESS (torchrun-style launch, one process per GPU): this context holds global rows [buf0, buf0 +
  * cfg.height) of a frame of global_height rows and owns rows [own0, own1). After rpf_band_attach, rpf_filter /
  * rpf_filter_sigmas run the band schedule: per pass the rows next to a band edge are filtered first, their colours go

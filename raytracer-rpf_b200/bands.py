@@ -40,7 +40,7 @@ class Band:
         return self.own0 - self.buf0, self.own1 - self.buf0
 
 
-def make_band(rank, world, height, box_sizes):
+def make_band(rank, world, height, box_sizes, row_weight=None):
     """Equal-WORK bands (rpf_band_plan of the C ABI: rows near the top and bottom edge see truncated boxes and weigh
     less); halo = largest b_delta over all passes (feature rows are needed at that depth)."""
     import rpf_b200
@@ -51,7 +51,7 @@ def make_band(rank, world, height, box_sizes):
     if world > 1 and height // world < reach:
         raise ValueError(f"{height} rows over {world} ranks leaves bands of {height // world} rows, thinner than the "
                          f"{reach}-row halo of the later passes: use fewer ranks")
-    plan = rpf_b200.band_plan(height, world, box_sizes)
+    plan = rpf_b200.band_plan(height, world, box_sizes, row_weight)
     own0, own1 = plan[rank], plan[rank + 1]
     return Band(rank, world, height, own0, own1, max(0, own0 - halo), min(height, own1 + halo))
 

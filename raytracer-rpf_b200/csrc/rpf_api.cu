@@ -1026,6 +1026,10 @@ extern "C" int rpf_band_plan(int height, int n_bands, const int *box_sizes, int 
     return band_plan(height, n_bands, box_sizes, n_iter, own0);
 }
 
+extern "C" int rpf_band_plan_weighted(int height, int n_bands, const int *box_sizes, int n_iter, const double *row_weight, int *own0) {
+    return band_plan(height, n_bands, box_sizes, n_iter, own0, row_weight);
+}
+
 extern "C" int rpf_band_unique_id(void *out128) {
     if (!out128) return RPF_ERR_INVALID;
     NcclApi *nc = nccl_api();

@@ -19,7 +19,7 @@ namespace {
 inline int b_delta(int box) { return (box - 1) / 2; }  // rpf.cpp:561
 
 // ---- equal-work plan -------------------------------------------------------------------------------------------------
-int band_plan(int height, int n, const int *boxes, int n_iter, int *own0) {
+int band_plan(int height, int n, const int *boxes, int n_iter, int *own0, const double *row_weight = nullptr) {
     if (height <= 0 || n < 1 || n > height || n_iter < 0 || (n_iter && !boxes) || !own0) return RPF_ERR_INVALID;
     // the exchange after a pass talks to the two adjacent bands only: a band must own at least the rows any LATER pass
     // reaches across its edge, or a pixel would need colours from two bands away
@@ -40,6 +40,7 @@ int band_plan(int height, int n, const int *boxes, int n_iter, int *own0) {
             w += static_cast<double>(boxes[i]) * rows;
         }
         if (n_iter == 0) w = 1.0;
+        if (row_weight) w = row_weight[y] > 0.0 ? row_weight[y] : 0.0;  // measured cost per row instead of the geometric model
         pre[y + 1] = pre[y] + w;
     }
     own0[0] = 0;

@@ -30,6 +30,7 @@ ABI_SYMBOLS = [
     "rpf_band_plan", "rpf_band_unique_id", "rpf_band_attach", "rpf_host_alloc", "rpf_host_free",
     "rpf_set_debug_pixel", "rpf_download_debug_mi", "rpf_reset_colors",
     "rpf_num_channels", "rpf_num_pairs", "rpf_layout_supported", "rpf_synth_planes_layout", "rpf_filter_rows2",
+    "rpf_band_plan_weighted",
 ]
 
 
@@ -171,6 +172,7 @@ def lib():
         L.rpf_max_neighbourhood.argtypes = []
         L.rpf_synth_planes.argtypes = [i, i, i, C.c_ulonglong, i, i, i, vp]
         L.rpf_band_plan.argtypes = [i, i, vp, i, vp]
+        L.rpf_band_plan_weighted.argtypes = [i, i, vp, i, vp, vp]
         L.rpf_band_unique_id.argtypes = [vp]
         L.rpf_band_attach.argtypes = [vp, C.POINTER(Band), vp]
         L.rpf_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
@@ -190,11 +192,17 @@ def _p(a):
     return a.ctypes.data_as(C.c_void_p)
 
 
-def band_plan(height, n_bands, box_sizes):
-    """rpf_band_plan: first owned row of each of n_bands equal-work row bands, [n_bands + 1] ints (host only)."""
+def band_plan(height, n_bands, box_sizes, row_weight=None):
+    """rpf_band_plan(_weighted): first owned row of each of n_bands equal-work row bands, [n_bands + 1] ints (host only).
+    row_weight: measured cost per row ([height] doubles) instead of the geometric model."""
     bx = np.asarray(box_sizes, np.int32)
     out = np.zeros(n_bands + 1, np.int32)
-    rc = lib().rpf_band_plan(height, n_bands, _p(bx), len(bx), _p(out))
+    if row_weight is None:
+        rc = lib().rpf_band_plan(height, n_bands, _p(bx), len(bx), _p(out))
+    else:
+        w = np.ascontiguousarray(row_weight, np.float64)
+        assert w.shape == (height,)
+        rc = lib().rpf_band_plan_weighted(height, n_bands, _p(bx), len(bx), _p(w), _p(out))
     if rc != 0:
         raise RPFError(f"rpf_band_plan({height} rows, {n_bands} bands, boxes {list(box_sizes)}) failed ({rc})")
     return [int(v) for v in out]
