@@ -154,7 +154,13 @@ int rpf_color_device_ptr(rpf_ctx *ctx, int which, double **out);
 int rpf_stream(rpf_ctx *ctx, void **out);
 int rpf_synchronize(rpf_ctx *ctx);
 
-/* Replaces reading samplingFilm.samples back at rpf.cpp:780-786. Any pointer may be NULL. */
+/* Replaces reading samplingFilm.samples back at rpf.cpp:780-786. Any pointer may be NULL.
+ * rpf_download_colors, rpf_reconstruct_box and rpf_reconstruct_film use the NEXT colour buffer as conversion scratch: in the
+ * row protocol (rpf_filter_rows ... rpf_swap_colors) call them only after rpf_swap_colors, never between a rpf_filter_rows and
+ * its swap, or the freshly filtered rows are overwritten. rpf_download_colors_f64 has no such restriction.
+ * rpf_upload / rpf_upload_colors_f64 return once the copies are ENQUEUED on the context's stream: from pageable memory that
+ * is after the data has left the host buffer, from page-locked memory (rpf_host_alloc) the buffer must stay untouched until
+ * rpf_synchronize or any download has returned. */
 int rpf_download_colors(rpf_ctx *ctx, float *r, float *g, float *b);
 int rpf_download_colors_f64(rpf_ctx *ctx, double *rgb); /* [3][width*height*spp] */
 /* Per-pixel (index y*width+x) diagnostics of the last pass; needs cfg.debug. Any pointer may be NULL.
@@ -198,8 +204,8 @@ int rpf_film_filter_table(int kind, float radius_x, float radius_y, float alpha,
  * band edge move to the neighbouring band.
  *
  * rpf_band_plan (host only, no device): first owned row of each of n_bands bands, own0[0..n_bands] with own0[n_bands] =
- * height, so that every band carries about the same WORK: a row's weight is sum over passes of box^2 * (rows of the
- * box inside the frame) / box -- rows near the top and bottom edge see truncated boxes and are cheaper. Every band owns
+ * height, so that every band carries about the same WORK: a row's weight is sum over passes of box * (0.9 box + 0.1 rows
+ * of the box inside the frame) -- rows near the top and bottom edge see truncated boxes and are slightly cheaper. Every band owns
  * at least b_delta(largest box after the first pass) rows, so the exchange after a pass talks to adjacent bands only;
  * RPF_ERR_INVALID if the frame is too short for that. */
 int rpf_band_plan(int height, int n_bands, const int *box_sizes, int n_iter, int *own0 /* [n_bands + 1] */);

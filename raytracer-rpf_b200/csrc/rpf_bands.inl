@@ -30,14 +30,16 @@ int band_plan(int height, int n, const int *boxes, int n_iter, int *own0, const 
     }
     const int min_rows = std::max(1, reach);
     if (n > 1 && 1ll * n * min_rows > height) return RPF_ERR_INVALID;
-    // weight of a row: sum over passes of box * (rows of the box inside the frame) ~ candidates per pixel of that row
+    // weight of a row: sum over passes of box * (0.9 box + 0.1 rows of the box inside the frame). Pixels near the top and
+    // bottom edge see cut boxes, but measured on B200 (profiles/r2/scaling/scale_n8_v29_calibrated.json) a cut box saves
+    // little: most of a pixel's cost does not shrink with its candidates. bench.py re-cuts the bands from a measured step.
     std::vector<double> pre(height + 1, 0.0);
     for (int y = 0; y < height; ++y) {
         double w = 0.0;
         for (int i = 0; i < n_iter; ++i) {
             const int d = b_delta(boxes[i]);
             const int rows = std::min(height - 1, y + d) - std::max(0, y - d) + 1;
-            w += static_cast<double>(boxes[i]) * rows;
+            w += static_cast<double>(boxes[i]) * (0.9 * boxes[i] + 0.1 * rows);
         }
         if (n_iter == 0) w = 1.0;
         if (row_weight) w = row_weight[y] > 0.0 ? row_weight[y] : 0.0;  // measured cost per row instead of the geometric model
