@@ -87,7 +87,7 @@ def config_of(args, boxes):
 
 def measured_traffic(kernel, key):
     """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture (profiles/r2/traffic.json,
-    written by tools/traffic_from_ncu.py): dram__bytes_read.sum + dram__bytes_write.sum averaged over its launches of one
+    written by tools/traffic_r2.py): dram__bytes_read.sum + dram__bytes_write.sum averaged over its launches of one
     step. None when no capture exists for this workload / band shape."""
     for rnd in ("r2", "r1"):
         try:

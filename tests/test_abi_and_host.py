@@ -237,3 +237,26 @@ def test_headers_are_plain_c_and_link_against_the_library(tmp_path):
     r = subprocess.run([str(exe)], capture_output=True, text=True, env=env)
     assert r.returncode == 0, (r.returncode, r.stderr)
     assert r.stdout.split() == ["512", str(1 << 20)]
+
+
+def test_band_plan_from_measured_work():
+    """rpf_band_plan_weighted: bands of equal MEASURED cost. A uniform cost gives equal heights; a band that measured slower
+    gets fewer rows; the constraint (every band owns the rows later passes reach) still holds."""
+    import numpy as np
+    rpf_b200 = _lib_or_skip()
+    H, boxes = 1080, [55, 35, 17, 7]
+    assert rpf_b200.band_plan(H, 8, boxes, np.ones(H)) == [0, 135, 270, 405, 540, 675, 810, 945, 1080]
+    w = np.ones(H)
+    w[:135] = 1.1                                   # the first band measured 10 % slower per row
+    plan = rpf_b200.band_plan(H, 8, boxes, w)
+    assert plan[0] == 0 and plan[-1] == H and plan[1] < 135 and all(b - a >= 17 for a, b in zip(plan, plan[1:]))
+    cost = [w[a:b].sum() for a, b in zip(plan, plan[1:])]
+    assert max(cost) - min(cost) <= 2.2             # within two rows' worth of cost
+    # degenerate weights cannot break the adjacency constraint
+    w2 = np.zeros(H)
+    w2[500:520] = 1.0
+    plan = rpf_b200.band_plan(H, 8, boxes, w2)
+    assert plan[0] == 0 and plan[-1] == H and all(b - a >= 17 for a, b in zip(plan, plan[1:]))
+    # the geometric plan: the two edge bands a little taller at most
+    g = rpf_b200.band_plan(H, 8, boxes)
+    assert g[0] == 0 and g[-1] == H and all(130 <= b - a <= 140 for a, b in zip(g, g[1:]))
