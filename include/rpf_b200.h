@@ -266,6 +266,26 @@ int rpf_max_neighbourhood(void);
  * overrides. Both paths implement rpf.cpp:556-723 with the same results. */
 int rpf_fused_max_candidates(void);
 
+/* One filter pass that ALLOCATES NOTHING -- no counterpart in the reference; added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it). It is ApplyRPFFilter's per-pixel body (rpf.cpp:527-723) for ONE box size through the fused kernel, with all
+ * device scratch (per-pixel feature mean / 3 sigma, the n ln n tables, the counters) in file-scope static __device__
+ * arrays of the library: 12 MiB that every GPU which loads the library holds until the process exits.
+ *   d_planes      [19][width*height*spp] float32, DEVICE memory of the CURRENT device, the layout of rpf_upload
+ *   d_colors_in   [3][width*height*spp] float64, the colours entering the pass (first pass: planes 2..4 as doubles)
+ *   d_colors_out  [3][width*height*spp] float64, the colours leaving it (must not alias d_colors_in: Jacobi pass)
+ *   flags         as rpf_config.flags (0 = RPF_FLAGS_DEFINED);  cuda_stream: a cudaStream_t (NULL = the default stream)
+ * The call only enqueues three kernels on cuda_stream and returns; results equal rpf_filter's for the same box bit for bit.
+ * Limits: width*height <= RPF_NOALLOC_MAX_PIXELS and box*box*spp <= rpf_fused_max_candidates(); beyond either the call
+ * returns RPF_ERR_UNSUPPORTED with a message (rpf_last_error(NULL)) and launches nothing. It calls no cudaMalloc,
+ * cudaFree or allocating library routine; the first call on each device also fetches the arrays' device addresses,
+ * uploads two constant tables (21 KiB, synchronous) and sets the kernel's shared-memory attribute -- make that call
+ * outside a graph capture. All calls on one device share the arrays, which keep the last call's contents (the call
+ * rewrites what it reads): calls that OVERLAP on the GPU (different streams without an ordering event) race. */
+#define RPF_NOALLOC_MAX_PIXELS 65536
+int rpf_filter_pass_noalloc(const float *d_planes, const double *d_colors_in, double *d_colors_out, int width, int height,
+                            int spp, int box, double sigma_fc_seed, int flags, void *cuda_stream);
+
 /* Deterministic synthetic feature buffer, host side, float32 values.
  * kind 0: all-noisy; kind 1: degenerate (flat normals, black background, duplicated samples).
  * (x_off,y_off) shift the generator so a row band of a larger frame can be generated on its own. */

@@ -8,6 +8,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <algorithm>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -1075,6 +1076,120 @@ extern "C" int rpf_host_alloc(void **out, size_t bytes) {
 
 extern "C" void rpf_host_free(void *p) {
     if (p) cudaFreeHost(p);
+}
+
+// =====================================================================================================
+// rpf_filter_pass_noalloc: one pass of the fused kernel with every byte of device scratch in file-scope arrays, for callers
+// that may not allocate (CUDA graph capture, tight serving loops). No counterpart in the reference.
+// Shares nothing with the context-based path above: same kernels (pixel_stats_kernel,
+// rpf_pixel_kernel<false>), own scratch.
+//
+// The arrays below exist once per GPU that loads this library, until the process exits (12 MiB + 21 KiB). Every call on a
+// device uses the SAME arrays: calls that overlap on the GPU (two streams) race; successive calls on one stream, or calls
+// ordered by events, are fine. Nothing is kept between calls except the two constant tables.
+static constexpr int kNoAllocMaxPixels = RPF_NOALLOC_MAX_PIXELS;
+static constexpr int kNoAllocTable = kFusedHardMax + 2;  // g[k], k <= candidates + 1
+static __device__ __align__(256) double g_noalloc_pstat[static_cast<size_t>(kNoAllocMaxPixels) * 2 * rpf::NF];  // per-pixel mean[12], 3 sigma[12]
+static __device__ __align__(256) double g_noalloc_gtab[kNoAllocTable];       // (k+1) ln (k+1) - k ln k
+static __device__ __align__(256) double g_noalloc_gpre[kNoAllocTable + 1];   // its sequential prefix sums
+static __device__ __align__(256) unsigned long long g_noalloc_counters[4];   // sum N, NaN channels, min N, max N of the last call
+
+// device code names the array directly; only the host needs cudaGetSymbolAddress
+__global__ void noalloc_reset_kernel() {
+    if (threadIdx.x < 4) g_noalloc_counters[threadIdx.x] = threadIdx.x == 2 ? ~0ull : 0ull;
+}
+
+namespace {
+constexpr int kNoAllocMaxDevices = 64;
+struct NoAllocDevice {
+    bool ready = false;
+    double *pstat = nullptr, *gtab = nullptr, *gpre = nullptr;  // DEVICE addresses of the arrays above on this device
+    unsigned long long *counters = nullptr;
+};
+NoAllocDevice g_noalloc_dev[kNoAllocMaxDevices];
+std::mutex g_noalloc_mutex;
+double g_noalloc_host_g[kNoAllocTable], g_noalloc_host_pre[kNoAllocTable + 1];  // static: no heap either
+}  // namespace
+
+// Once per device, with that device current: the arrays' device addresses (in host code the array names are host-side
+// stand-ins, not device addresses), the constant tables, the kernel's shared-memory opt-in. None of it allocates.
+static int noalloc_setup(int device, NoAllocDevice **out) {
+    if (device < 0 || device >= kNoAllocMaxDevices) return fail(nullptr, RPF_ERR_INVALID, "rpf_filter_pass_noalloc: device %d out of range", device);
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    NoAllocDevice &d = g_noalloc_dev[device];
+    *out = &d;
+    if (d.ready) return RPF_OK;
+    cudaDeviceProp prop;
+    CU(nullptr, cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) return fail(nullptr, RPF_ERR_NO_DEVICE, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+    CU(nullptr, cudaGetSymbolAddress(reinterpret_cast<void **>(&d.pstat), g_noalloc_pstat));
+    CU(nullptr, cudaGetSymbolAddress(reinterpret_cast<void **>(&d.gtab), g_noalloc_gtab));
+    CU(nullptr, cudaGetSymbolAddress(reinterpret_cast<void **>(&d.gpre), g_noalloc_gpre));
+    CU(nullptr, cudaGetSymbolAddress(reinterpret_cast<void **>(&d.counters), g_noalloc_counters));
+    // the same tables as ensure_gtab (extended precision, sequentially summed prefix)
+    double acc = 0.0;
+    g_noalloc_host_pre[0] = 0.0;
+    for (int k = 0; k < kNoAllocTable; ++k) {
+        const long double a = k + 1, b = k;
+        g_noalloc_host_g[k] = static_cast<double>(a * logl(a) - (k ? b * logl(b) : 0.0L));
+        acc += g_noalloc_host_g[k];
+        g_noalloc_host_pre[k + 1] = acc;
+    }
+    CU(nullptr, cudaMemcpy(d.gtab, g_noalloc_host_g, sizeof g_noalloc_host_g, cudaMemcpyHostToDevice));
+    CU(nullptr, cudaMemcpy(d.gpre, g_noalloc_host_pre, sizeof g_noalloc_host_pre, cudaMemcpyHostToDevice));
+    CU(nullptr, cudaFuncSetAttribute(rpf::rpf_pixel_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
+    d.ready = true;
+    return RPF_OK;
+}
+
+extern "C" int rpf_filter_pass_noalloc(const float *d_planes, const double *d_colors_in, double *d_colors_out, int width, int height,
+                                       int spp, int box, double sigma_fc_seed, int flags, void *cuda_stream) {
+    if (!d_planes || !d_colors_in || !d_colors_out) return fail(nullptr, RPF_ERR_INVALID, "rpf_filter_pass_noalloc: null buffer");
+    if (d_colors_in == d_colors_out) return fail(nullptr, RPF_ERR_INVALID, "rpf_filter_pass_noalloc: a pass reads its neighbours' colours; in and out must differ");
+    if (width <= 0 || height <= 0 || spp <= 0) return fail(nullptr, RPF_ERR_INVALID, "rpf_filter_pass_noalloc: bad frame %dx%dx%d", width, height, spp);
+    if (box < 1 || !(box & 1)) return fail(nullptr, RPF_ERR_INVALID, "rpf_filter_pass_noalloc: box size %d must be odd and positive", box);
+    if (!(sigma_fc_seed > 0.0)) return fail(nullptr, RPF_ERR_INVALID, "sigma_fc_seed must be positive");
+    if (1ll * width * height > kNoAllocMaxPixels)
+        return fail(nullptr, RPF_ERR_UNSUPPORTED, "rpf_filter_pass_noalloc: %d x %d = %lld pixels exceed the static scratch of %d pixels (RPF_NOALLOC_MAX_PIXELS); "
+                    "filter in tiles or use rpf_create / rpf_filter", width, height, 1ll * width * height, kNoAllocMaxPixels);
+    rpf::FilterParams p{};
+    const long long ncap = 1ll * box * box * spp;
+    if (!rpf::plan_smem(ncap, spp, kSmemLimit, p.sm))
+        return fail(nullptr, RPF_ERR_UNSUPPORTED, "rpf_filter_pass_noalloc: box %d x %d spp = %lld candidates exceed the fused kernel's %d (rpf_fused_max_candidates); "
+                    "larger neighbourhoods need the scratch of rpf_create / rpf_filter", box, spp, ncap, rpf_fused_max_candidates());
+    int device = 0;
+    CU(nullptr, cudaGetDevice(&device));
+    cudaPointerAttributes at;
+    CU(nullptr, cudaPointerGetAttributes(&at, d_planes));
+    if (at.type != cudaMemoryTypeDevice || at.device != device)
+        return fail(nullptr, RPF_ERR_INVALID, "rpf_filter_pass_noalloc: d_planes is not memory of the current device %d", device);
+    NoAllocDevice *d = nullptr;
+    int rc = noalloc_setup(device, &d);
+    if (rc != RPF_OK) return rc;
+    cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+    const size_t S = static_cast<size_t>(width) * height * spp;
+    p.f = rpf::FrameView{d_planes, S, width, height, spp};
+    p.col_in = d_colors_in;
+    p.col_out = d_colors_out;
+    p.pstat = d->pstat;
+    p.gtab = d->gtab;
+    p.gpre = d->gpre;
+    p.counters = d->counters;
+    p.box = box;
+    p.y0 = 0;
+    p.y1 = height;
+    p.flags = flags == 0 ? RPF_FLAGS_DEFINED : flags;  // as rpf_config.flags
+    p.seed = sigma_fc_seed;
+    p.probe = rpf::DebugProbe{-1, nullptr, nullptr};
+    p.sub = rpf::SubsampleParams{0ull, RPF_SUBSAMPLE_ALL, 0};
+    // the scratch keeps the last call's contents: the counters start over, the per-pixel statistics are rewritten for
+    // every pixel this call reads (all width x height of them)
+    noalloc_reset_kernel<<<1, 32, 0, stream>>>();
+    const long long n = 1ll * width * height * rpf::NF;
+    rpf::pixel_stats_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, stream>>>(p.f, 0, height, d->pstat, 0.0, 0.0);
+    rpf::rpf_pixel_kernel<false><<<static_cast<unsigned>(width * height), rpf::THREADS, p.sm.total, stream>>>(p);
+    CU(nullptr, cudaGetLastError());
+    return RPF_OK;
 }
 
 #ifdef RPF_PHASE_TIMERS

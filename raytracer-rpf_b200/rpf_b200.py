@@ -30,7 +30,7 @@ ABI_SYMBOLS = [
     "rpf_band_plan", "rpf_band_unique_id", "rpf_band_attach", "rpf_host_alloc", "rpf_host_free",
     "rpf_set_debug_pixel", "rpf_download_debug_mi", "rpf_reset_colors",
     "rpf_num_channels", "rpf_num_pairs", "rpf_layout_supported", "rpf_synth_planes_layout", "rpf_filter_rows2",
-    "rpf_band_plan_weighted",
+    "rpf_band_plan_weighted", "rpf_filter_pass_noalloc",
 ]
 
 
@@ -184,6 +184,7 @@ def lib():
         L.rpf_layout_supported.argtypes = [i, i]
         L.rpf_set_debug_pixel.argtypes = [vp, i, i]
         L.rpf_download_debug_mi.argtypes = [vp, vp, C.POINTER(i), C.POINTER(i), vp, i]
+        L.rpf_filter_pass_noalloc.argtypes = [vp, vp, vp, i, i, i, i, d, i, vp]
         _lib = L
     return _lib
 
@@ -206,6 +207,17 @@ def band_plan(height, n_bands, box_sizes, row_weight=None):
     if rc != 0:
         raise RPFError(f"rpf_band_plan({height} rows, {n_bands} bands, boxes {list(box_sizes)}) failed ({rc})")
     return [int(v) for v in out]
+
+
+NOALLOC_MAX_PIXELS = 65536  # RPF_NOALLOC_MAX_PIXELS (include/rpf_b200.h)
+
+
+def filter_pass_noalloc(d_planes, d_colors_in, d_colors_out, width, height, spp, box, seed, flags=0, stream=0):
+    """rpf_filter_pass_noalloc: one pass over DEVICE buffers (raw addresses) with the library's static scratch -- no
+    allocation anywhere in the call. Only enqueues on `stream` (a cudaStream_t value, 0 = default stream)."""
+    rc = lib().rpf_filter_pass_noalloc(d_planes, d_colors_in, d_colors_out, width, height, spp, box, float(seed), flags, stream or None)
+    if rc != 0:
+        raise RPFError(f"rpf_filter_pass_noalloc failed ({rc}): {lib().rpf_last_error(None).decode()}")
 
 
 def nccl_unique_id():
