@@ -33,6 +33,7 @@ struct rpf_ctx {
     double *d_col[2] = {nullptr, nullptr};  // [3][S] each: current / next
     int cur = 0;
     double *d_pstat = nullptr;      // [npix][2 nf]
+    float *d_pbound = nullptr;      // [npix][2 nf]: the same test as float intervals (membership_kernel)
     int pstat_y0 = 0, pstat_y1 = 0; // rows with valid per-pixel statistics
     double *d_gtab = nullptr, *d_gpre = nullptr, *d_hln = nullptr;
     unsigned long long *d_gq = nullptr, *d_hq = nullptr;
@@ -151,6 +152,7 @@ extern "C" void rpf_destroy(rpf_ctx *ctx) {
     cudaFree(ctx->d_col[0]);
     cudaFree(ctx->d_col[1]);
     cudaFree(ctx->d_pstat);
+    cudaFree(ctx->d_pbound);
     cudaFree(ctx->d_gtab);
     cudaFree(ctx->d_gpre);
     cudaFree(ctx->d_hln);
@@ -310,6 +312,7 @@ extern "C" int rpf_create(rpf_ctx **out, const rpf_config *cfg) {
     CUC(cudaMalloc(&ctx->d_col[0], 3 * ctx->S * sizeof(double)));
     CUC(cudaMalloc(&ctx->d_col[1], 3 * ctx->S * sizeof(double)));
     CUC(cudaMalloc(&ctx->d_pstat, 2ull * ops->nf * ctx->npix * sizeof(double)));
+    CUC(cudaMalloc(&ctx->d_pbound, 2ull * ops->nf * ctx->npix * sizeof(float)));
     CUC(cudaMalloc(&ctx->d_counters, 4 * sizeof(unsigned long long)));
     if (cfg->debug) {
         CUC(cudaMalloc(&ctx->d_dbg_n, ctx->npix * sizeof(int)));

@@ -30,7 +30,39 @@ __global__ void colors_to_f64_kernel(const float *__restrict__ planes, size_t S,
 // One thread per (pixel, feature); sums run sequentially in sample order like the reference.
 // Paper mode (rpf_set_paper_mode; not in the reference, both 0 by default): world-position features take pos_sigmas
 // instead of 3, and the threshold never drops below min_sigma (low-variance guard). A NaN sigma stays NaN (accepts).
-__global__ void pixel_stats_kernel(FrameView f, int y0, int y1, double *__restrict__ pstat, double min_sigma, double pos_sigmas) {
+// The 3-sigma test of rpf.cpp:579-586 on a float feature f is  !(|fl(f - mu)| >= sd3)  in double arithmetic. fl(f - mu) is monotone
+// in f, so for one pixel and feature the floats that pass form an INTERVAL [lo, hi] of floats: found here once per pixel by
+// bisection over the ordered floats with the reference's own expression as the predicate, it turns the 24,200 tests per pixel of
+// membership_kernel into two float compares each, exactly (pbound[pix] = lo[NF], hi[NF]). Written so that a candidate is rejected
+// iff (f < lo || f > hi): a NaN feature passes (NaN >= x is false in the reference too); a NaN sigma gives [-inf, +inf] (everything
+// passes, infinities included); otherwise infinities fail; sigma 0 gives the empty interval [+inf, -inf].
+__device__ __forceinline__ float ordered_float(long long k) {  // k in [-0x7f800000, 0x7f7fffff] <-> finite floats, ascending
+    const int i = static_cast<int>(k);
+    return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff);
+}
+__device__ inline void three_sigma_interval(double mu, double sd3, float &lo, float &hi) {
+    const float inf = __int_as_float(0x7f800000);
+    if (sd3 != sd3) { lo = -inf; hi = inf; return; }
+    const long long KMIN = -0x7f800000ll, KMAX = 0x7f7fffffll;
+    // hi: the largest float with fl(f - mu) < sd3 (true below, false above)
+    long long a = KMIN - 1, b = KMAX + 1;
+    while (b - a > 1) {
+        const long long m = a + (b - a) / 2;
+        if (__dsub_rn(static_cast<double>(ordered_float(m)), mu) < sd3) a = m; else b = m;
+    }
+    hi = a >= KMIN ? ordered_float(a) : -inf;
+    // lo: the smallest float with fl(f - mu) > -sd3 (false below, true above)
+    a = KMIN - 1; b = KMAX + 1;
+    while (b - a > 1) {
+        const long long m = a + (b - a) / 2;
+        if (__dsub_rn(static_cast<double>(ordered_float(m)), mu) > -sd3) b = m; else a = m;
+    }
+    lo = b <= KMAX ? ordered_float(b) : inf;
+    if (!(lo <= hi)) { lo = inf; hi = -inf; }
+}
+
+__global__ void pixel_stats_kernel(FrameView f, int y0, int y1, double *__restrict__ pstat, double min_sigma, double pos_sigmas,
+                                   float *__restrict__ pbound = nullptr) {
     const long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
     const int k = static_cast<int>(t % NF);
     const long long pix = t / NF + static_cast<long long>(y0) * f.W;
@@ -51,6 +83,12 @@ __global__ void pixel_stats_kernel(FrameView f, int y0, int y1, double *__restri
     if (world_pos && pos_sigmas > 0.0) sd3 = __dmul_rn(sd, pos_sigmas);
     if (min_sigma > 0.0 && sd3 < min_sigma) sd3 = min_sigma;
     pstat[pix * (2 * NF) + NF + k] = sd3;
+    if (pbound) {
+        float lo, hi;
+        three_sigma_interval(mu, sd3, lo, hi);
+        pbound[pix * (2 * NF) + k] = lo;
+        pbound[pix * (2 * NF) + NF + k] = hi;
+    }
 }
 
 #if RPF_FULL

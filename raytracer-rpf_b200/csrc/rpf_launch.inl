@@ -118,7 +118,7 @@ static int ensure_pstat(rpf_ctx *ctx, const FrameView &f, int y0, int y1) {
     const long long n = 1ll * ctx->cfg.height * ctx->cfg.width * NF;  // one thread per (pixel, feature)
     prof_begin(ctx, RPF_K_PIXEL_STATS);
     pixel_stats_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, ctx->stream>>>(f, 0, ctx->cfg.height, ctx->d_pstat, ctx->min_sigma,
-                                                                                         ctx->pos_sigmas);
+                                                                                         ctx->pos_sigmas, ctx->d_pbound);
     prof_end(ctx);
     ctx->launches++;
     CU(ctx, cudaGetLastError());
@@ -255,7 +255,8 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1, in
         {
             MembershipParams m{};
             m.f = p.f;
-            m.pstat = ctx->d_pstat;
+            m.pbound = ctx->d_pbound;
+            m.rec16 = ctx->d_rec16;
             m.mask = ctx->d_mask;
             m.box = box;
             m.row0 = p.row0;
@@ -267,9 +268,9 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1, in
             membership_tile(box, m.tx, m.ty);
             m.tiles_x = (W + m.tx - 1) / m.tx;
             m.col_rows = m.ty + box - 1;
-            const size_t row_bytes = (static_cast<size_t>(ctx->cfg.spp) * NF + 2) * sizeof(double);
+            const size_t row_bytes = static_cast<size_t>(membership_row_floats(ctx->cfg.spp)) * sizeof(float);
             m.rb_rows = m.col_rows;
-            const size_t memb_kb = getenv("RPF_MEMB_SMEM_KB") ? static_cast<size_t>(atoi(getenv("RPF_MEMB_SMEM_KB"))) : 40;  // 40 KB per CTA: five CTAs per SM (82 vs 87 ms at box 55)
+            const size_t memb_kb = getenv("RPF_MEMB_SMEM_KB") ? static_cast<size_t>(atoi(getenv("RPF_MEMB_SMEM_KB"))) : 32;  // per CTA: six CTAs per SM
             while (m.rb_rows > 1 && m.rb_rows * row_bytes > memb_kb * 1024) m.rb_rows = (m.rb_rows + 1) / 2;
             const unsigned tiles = static_cast<unsigned>(m.tiles_x) * static_cast<unsigned>((p.nrows + m.ty - 1) / m.ty);
             prof_begin(ctx, RPF_K_MEMBERSHIP);

@@ -3,9 +3,10 @@
 //   membership_kernel     3-sigma membership of every candidate of every pixel (rpf.cpp:556-586, ops.h:100-107) ->
 //                         per-pixel acceptance bit mask in HBM, bit t = candidate t in reference enumeration order
 //                         (xn ascending, yn ascending, sample: rpf.cpp:562-573). A CTA owns a TX x TY tile of pixels,
-//                         one THREAD per pixel with that pixel's mean / 3 sigma in registers; the union of the tile's
-//                         boxes streams through shared memory one column of neighbour pixels at a time, so a sample's
-//                         12 features are fetched from L2 once per tile instead of once per pixel.
+//                         one THREAD per pixel with that pixel's test in registers as one float interval per feature
+//                         (three_sigma_interval, rpf_kernels.cuh: exactly the reference's double-precision test); the
+//                         union of the tile's boxes streams through shared memory one column of neighbour pixels at a time,
+//                         so a sample's 12 features are fetched from L2 once per tile instead of once per pixel.
 //   ordered_stats_kernel  neighbourhood mean / sigma / min / max of all 19 channels (rpf.cpp:596-601). The sums must
 //                         follow the reference's order (ops.h:111-144 sums sequentially; the rounding of mean and sigma
 //                         decides histogram bin boundaries later), so one WARP per pixel walks the mask in order with
@@ -16,6 +17,9 @@
 namespace RPF_NS {
 
 constexpr int KM_MAX_THREADS = 128;
+#ifndef RPF_KM_MINB
+#define RPF_KM_MINB 6  // CTAs per SM the register allocation aims at
+#endif
 
 // Tile of pixels per CTA for a box size: large boxes amortise the halo over 128 pixels, small ones waste less on it.
 __host__ __device__ inline void membership_tile(int box, int &tx, int &ty) {
@@ -26,7 +30,8 @@ __host__ __device__ inline void membership_tile(int box, int &tx, int &ty) {
 
 struct MembershipParams {
     FrameView f;
-    const double *pstat;   // [W*H][2 NF] per-pixel feature mean[NF], 3 sigma[NF]
+    const float *pbound;   // [W*H][2 NF] per-pixel acceptance interval of every feature: lo[NF], hi[NF] (pixel_stats_kernel)
+    const float4 *rec16;   // [S][NQ4] gather records: a pixel's samples are contiguous, a sample's features adjacent
     uint32_t *mask;        // [chunk pixels][mw]
     int box, row0, nrows, mw;
     int gap_at, gap;       // chunk_row() (rpf_general.cuh); gap_at is a multiple of the tile height: no tile straddles the gap
@@ -36,16 +41,40 @@ struct MembershipParams {
     SubsampleParams sub;
 };
 
+constexpr int KM_NFP = (NF + 3) & ~3;         // floats per staged sample (whole float4s)
+constexpr int KM_SLOT0 = NP + NR;             // slot of feature 0 in the gather record (channel_slot(CH_FEAT))
+constexpr bool KM_VEC = KM_SLOT0 % 4 == 0 && NF % 4 == 0;  // the features are whole float4s of the record (reference layout)
+__host__ __device__ inline int membership_row_floats(int spp) { return spp * KM_NFP + 4; }  // + 4: the 2-4 rows a warp reads at once
+                                                                                             // fall into different banks, 16-byte aligned
+
+// a candidate is outside iff some feature lies outside the pixel's [lo, hi]: features 0..3, then the rest
+__device__ __forceinline__ bool outside_head(const float4 a, const float (&lo)[NF], const float (&hi)[NF]) {
+    bool out = a.x < lo[0] || a.x > hi[0];
+    if (NF > 1) out = out || a.y < lo[1 % NF] || a.y > hi[1 % NF];
+    if (NF > 2) out = out || a.z < lo[2 % NF] || a.z > hi[2 % NF];
+    if (NF > 3) out = out || a.w < lo[3 % NF] || a.w > hi[3 % NF];
+    return out;
+}
+__device__ __forceinline__ bool outside_tail(const float4 *cp, bool out, const float (&lo)[NF], const float (&hi)[NF]) {
+#pragma unroll
+    for (int q = 1; q < KM_NFP / 4; ++q) {
+        const float4 b = cp[q];
+        const float v[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (4 * q + j < NF) out = out || v[j] < lo[(4 * q + j) % NF] || v[j] > hi[(4 * q + j) % NF];
+    }
+    return out;
+}
+
 template <bool SUBSAMPLED>  // neighbour subsampling (include/rpf_subsample.h) compiled out of the default path
-__global__ void __launch_bounds__(KM_MAX_THREADS) membership_kernel(const MembershipParams p) {
+__global__ void __launch_bounds__(KM_MAX_THREADS, RPF_KM_MINB) membership_kernel(const MembershipParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
-    // [col_rows][P][12] features of one column of neighbour pixels; rows padded by two doubles so that the 2-4 rows a
-    // warp reads at once fall into different banks
-    double *col = reinterpret_cast<double *>(smem);
-    const int RS = p.f.P * NF + 2;
+    float *col = reinterpret_cast<float *>(smem);  // [rb_rows][P][KM_NFP] features of one column of neighbour pixels, as floats
+    const int RS = membership_row_floats(p.f.P);
+    constexpr int QS = KM_NFP / 4;  // float4s per staged sample
     const int tid = threadIdx.x;
     const int W = p.f.W, H = p.f.H, P = p.f.P, B = p.box, bd = (B - 1) / 2;
-    const size_t S = p.f.S;
     // tiles in the same column strips as the other kernels of the path (strip_order, rpf_general.cuh): a strip's window of
     // feature rows stays L2-resident from one row of tiles to the next
     const int tiles_y = (p.nrows + p.ty - 1) / p.ty;
@@ -56,19 +85,21 @@ __global__ void __launch_bounds__(KM_MAX_THREADS) membership_kernel(const Member
     const int px = x0 + lx, py = y0 + ly;
     const bool live = px < W && tile_y * p.ty + ly < p.nrows;
 
-    double mu[NF], sd3[NF];
+    // the pixel's test in registers: a candidate fails iff some feature lies outside [lo, hi] (three_sigma_interval, rpf_kernels.cuh)
+    float lo[NF], hi[NF];
     if (live) {
-        const double *ps = p.pstat + (static_cast<size_t>(py) * W + px) * (2 * NF);
+        const float *pb = p.pbound + (static_cast<size_t>(py) * W + px) * (2 * NF);
 #pragma unroll
-        for (int k = 0; k < NF; ++k) { mu[k] = ps[k]; sd3[k] = ps[NF + k]; }
+        for (int k = 0; k < NF; ++k) { lo[k] = pb[k]; hi[k] = pb[NF + k]; }
     } else {
 #pragma unroll
-        for (int k = 0; k < NF; ++k) { mu[k] = 0.0; sd3[k] = 0.0; }
+        for (int k = 0; k < NF; ++k) { lo[k] = 0.f; hi[k] = 0.f; }
     }
     const uint64_t ckey = SUBSAMPLED ? rpf_subsample_centre_key(p.sub.seed, B, px, py + p.sub.row_g0) : 0ull;
     uint32_t *mrow = p.mask + (static_cast<size_t>(tile_y * p.ty + ly) * W + px) * p.mw;
     unsigned long long buf = 0ull;
     int nbits = 0, wi = 0;
+    const int warp = tid >> 5, lane = tid & 31, nwarps = blockDim.x >> 5;
 
     const int nrows = p.col_rows;  // rows of neighbour pixels a column holds for this tile: yn = y0 - bd + r
     for (int xn = x0 - bd; xn <= x0 + p.tx - 1 + bd; ++xn) {
@@ -76,18 +107,29 @@ __global__ void __launch_bounds__(KM_MAX_THREADS) membership_kernel(const Member
         // every pixel's candidates in enumeration order
         for (int r0 = 0; r0 < nrows; r0 += p.rb_rows) {
             const int rbn = min(p.rb_rows, nrows - r0);
-            const int nsamp = rbn * P;
             __syncthreads();  // previous block fully consumed
             if (xn >= 0 && xn < W) {
-                for (int i = tid; i < nsamp * NF; i += blockDim.x) {
-                    const int k = i / nsamp, j = i - k * nsamp;  // feature-major: consecutive threads, consecutive samples
-                    const int r = j / P, s = j - r * P;
+                // one warp per row of the column: the P samples of a neighbour pixel are P consecutive gather records (64 P bytes)
+                for (int r = warp; r < rbn; r += nwarps) {
                     const int yn = y0 - bd + r0 + r;
-                    double v = 0.0;
-                    if (yn >= 0 && yn < H)
-                        v = static_cast<double>(__ldg(p.f.planes + static_cast<size_t>(CH_FEAT + k) * S +
-                                                      (static_cast<size_t>(yn) * W + xn) * P + s));
-                    col[r * RS + s * NF + k] = v;
+                    const bool in = yn >= 0 && yn < H;
+                    const size_t g0 = (static_cast<size_t>(in ? yn : 0) * W + xn) * P;
+                    if (KM_VEC) {
+                        constexpr int Q = NF / 4;
+                        float4 *dst = reinterpret_cast<float4 *>(col + r * RS);
+                        const float4 *src = p.rec16 + g0 * NQ4 + KM_SLOT0 / 4;
+                        for (int e = lane; e < P * Q; e += 32) {
+                            const int s = e / Q, q = e - s * Q;
+                            dst[e] = in ? __ldg(src + s * NQ4 + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+                        }
+                    } else {
+                        float *dst = col + r * RS;
+                        const float *src = reinterpret_cast<const float *>(p.rec16 + g0 * NQ4) + KM_SLOT0;
+                        for (int e = lane; e < P * KM_NFP; e += 32) {
+                            const int s = e / KM_NFP, k = e - s * KM_NFP;
+                            dst[e] = in && k < NF ? __ldg(src + s * (4 * NQ4) + k) : 0.f;
+                        }
+                    }
                 }
             }
             __syncthreads();
@@ -99,28 +141,44 @@ __global__ void __launch_bounds__(KM_MAX_THREADS) membership_kernel(const Member
                     const int yn = py - bd + by;
                     const bool inb = xin && yn >= 0 && yn < H;
                     const bool centre = xn == px && yn == py;
-                    const double *cp = col + (ly + by - r0) * RS;
+                    const float4 *cp = reinterpret_cast<const float4 *>(col + (ly + by - r0) * RS);
                     // a neighbour pixel's P acceptance bits are collected in a register and appended to the 64-bit
                     // bit buffer at once (chunks of 32 samples when spp is larger)
                     for (int s0 = 0; s0 < P; s0 += 32) {
                         const int ns = min(32, P - s0);
                         uint32_t bits = 0u;
-                        for (int s = 0; s < ns; ++s, cp += NF) {
-                            bool acc = inb;
-                            if (inb && !centre) {
-                                // allLessThan(|f - mu|, 3 sigma): reject on >= ; a NaN sigma accepts (ops.h:100-107)
+                        if (!inb) {
+                            cp += ns * QS;  // outside the image: no candidate
+                        } else if (centre) {
+                            bits = ns == 32 ? 0xffffffffu : (1u << ns) - 1u;  // the pixel's own samples always belong (rpf.cpp:558)
+                            cp += ns * QS;
+                        } else {
+                            // allLessThan(|f - mu|, 3 sigma) (ops.h:100-107) as the exact float interval test. Four samples at a
+                            // time: the first float4 of each (most candidates fail there), the other features only if one of
+                            // the four is still in for this pixel.
+                            int s = 0;
+                            for (; s + 4 <= ns; s += 4, cp += 4 * QS) {
+                                bool out[4];
 #pragma unroll
-                                for (int k = 0; k < 4; ++k)
-                                    if (fabs(__dsub_rn(cp[k], mu[k])) >= sd3[k]) acc = false;
-                                // most candidates fail early; skip the rest when no lane running here is still in
-                                if (__ballot_sync(__activemask(), acc)) {
+                                for (int j = 0; j < 4; ++j) out[j] = outside_head(cp[j * QS], lo, hi);
+                                if (NF > 4 && !(out[0] && out[1] && out[2] && out[3])) {
 #pragma unroll
-                                    for (int k = 4; k < NF; ++k)
-                                        if (fabs(__dsub_rn(cp[k], mu[k])) >= sd3[k]) acc = false;
+                                    for (int j = 0; j < 4; ++j) out[j] = outside_tail(cp + j * QS, out[j], lo, hi);
                                 }
-                                if (SUBSAMPLED && acc) acc = rpf_subsample_keep(ckey, p.sub.keep_q24, xn, yn + p.sub.row_g0, s0 + s);
+#pragma unroll
+                                for (int j = 0; j < 4; ++j) {
+                                    bool acc = !out[j];
+                                    if (SUBSAMPLED && acc) acc = rpf_subsample_keep(ckey, p.sub.keep_q24, xn, yn + p.sub.row_g0, s0 + s + j);
+                                    if (acc) bits |= 1u << (s + j);
+                                }
                             }
-                            bits |= static_cast<uint32_t>(acc) << s;
+                            for (; s < ns; ++s, cp += QS) {
+                                bool out = outside_head(cp[0], lo, hi);
+                                if (NF > 4 && !out) out = outside_tail(cp, out, lo, hi);
+                                bool acc = !out;
+                                if (SUBSAMPLED && acc) acc = rpf_subsample_keep(ckey, p.sub.keep_q24, xn, yn + p.sub.row_g0, s0 + s);
+                                if (acc) bits |= 1u << s;
+                            }
                         }
                         buf |= static_cast<unsigned long long>(bits) << nbits;
                         nbits += ns;
