@@ -266,6 +266,13 @@ static int launch_general(rpf_ctx *ctx, int box, double seed, int y0, int y1, in
             m.mw = p.pl.mw;
             m.sub = ctx->sub;
             membership_tile(box, m.tx, m.ty);
+            if (const char *e = getenv("RPF_MEMB_TILE")) {  // tuning: "TXxTY", TY a divisor of 8 (chunks and gaps start on multiples of 8 rows)
+                int tx = 0, ty = 0;
+                if (sscanf(e, "%dx%d", &tx, &ty) == 2 && tx > 0 && ty > 0 && 8 % ty == 0 && STRIP_W % tx == 0 && tx * ty <= KM_MAX_THREADS && (tx * ty) % 32 == 0) {
+                    m.tx = tx;
+                    m.ty = ty;
+                }
+            }
             m.tiles_x = (W + m.tx - 1) / m.tx;
             m.col_rows = m.ty + box - 1;
             const size_t row_bytes = static_cast<size_t>(membership_row_floats(ctx->cfg.spp)) * sizeof(float);

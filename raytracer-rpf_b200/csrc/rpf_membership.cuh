@@ -21,11 +21,12 @@ constexpr int KM_MAX_THREADS = 128;
 #define RPF_KM_MINB 6  // CTAs per SM the register allocation aims at
 #endif
 
-// Tile of pixels per CTA for a box size: large boxes amortise the halo over 128 pixels, small ones waste less on it.
+// Tile of pixels per CTA for a box size. A thread is idle while the column being streamed lies outside its own box: 8 columns
+// of pixels keep 55 of the 62 columns of a box-55 tile's union busy (16 x 8: 55 of 70; 56.4 -> 54.2 ms at box 55, 26.7 -> 23.3
+// at box 35, profiles/r2/ab_v37.txt), small boxes waste less on the halo with four rows.
 __host__ __device__ inline void membership_tile(int box, int &tx, int &ty) {
-    if (box >= 33) { tx = 16; ty = 8; }
-    else if (box >= 13) { tx = 8; ty = 8; }
-    else { tx = 8; ty = 4; }
+    tx = 8;
+    ty = box >= 13 ? 8 : 4;
 }
 
 struct MembershipParams {
@@ -200,7 +201,14 @@ __global__ void __launch_bounds__(KM_MAX_THREADS, RPF_KM_MINB) membership_kernel
 
 // =====================================================================================================
 constexpr int KO_WARPS = 4;  // pixels per CTA of the ordered statistics kernel
-constexpr int KO_GROUP = 16;  // mask words decoded per round
+#ifndef RPF_KO_LIST
+#define RPF_KO_LIST 1536
+#endif
+// capacity of a warp's sample list: mask words are decoded 32 at a time (1,024 candidates) until another 1,024 might not fit,
+// then the list is walked -- a few hundred samples per walk at the reference's sigma instead of the few dozen that the 512
+// candidates of a 16-word round used to yield (every walk starts with a batch of loads that nothing overlaps)
+constexpr int KO_LIST = RPF_KO_LIST;
+static_assert(KO_LIST >= 1024 + 32, "the list must hold one group of mask words");
 
 __global__ void __launch_bounds__(KO_WARPS * 32) ordered_stats_kernel(const GeneralParams p) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -225,28 +233,56 @@ __global__ void __launch_bounds__(KO_WARPS * 32) ordered_stats_kernel(const Gene
     };
     auto fetch = [&](uint32_t g) { return __ldg(pr + static_cast<size_t>(g) * REC19); };
 
-    // own samples first, unconditionally and in order (rpf.cpp:558)
-    int N = P;
-    for (int s = 0; s < P; ++s) take(fetch(base + s));
-
-    // then the mask in candidate order, skipping the centre pixel (already taken). Per mask word the 32 lanes decode
-    // one candidate each and compact the accepted sample indices (in order) into a per-warp list; then every lane
-    // walks that list for its own channel, loads batched eight ahead of the dependent adds.
-    // KO_GROUP mask words (KO_GROUP*32 candidates) are decoded per round, so that the dependent gather below runs over a
-    // few dozen samples at a time with two batches of loads in flight instead of the handful one mask word holds.
-    __shared__ uint32_t glist[KO_WARPS][KO_GROUP * 32];
+    // The accepted samples are collected, in the reference's order, in a per-warp list of sample indices; every lane then
+    // walks the list for its own channel, loads batched eight ahead of the dependent adds.
+    __shared__ uint32_t glist[KO_WARPS][KO_LIST];
     uint32_t *gl = glist[warp];
+    auto walk = [&](int cnt) {  // cnt > 0 entries, written by this warp
+        __syncwarp();
+        double v[8], u[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[i] = fetch(gl[min(i, cnt - 1)]);
+        for (int i0 = 0; i0 < cnt; i0 += 16) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) u[i] = fetch(gl[min(i0 + 8 + i, cnt - 1)]);
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                if (i0 + i < cnt) take(v[i]);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = fetch(gl[min(i0 + 16 + i, cnt - 1)]);
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                if (i0 + 8 + i < cnt) take(u[i]);
+        }
+        __syncwarp();  // the list is rewritten next
+    };
+
+    // own samples first, unconditionally and in order (rpf.cpp:558): they open the list
+    int N = 0, cnt = 0;
+    for (int s0 = 0; s0 < P; s0 += KO_LIST - 1024) {
+        if (cnt) {
+            N += cnt;
+            walk(cnt);
+        }
+        cnt = min(KO_LIST - 1024, P - s0);
+        for (int i = lane; i < cnt; i += 32) gl[i] = base + s0 + i;
+    }
+
+    // then the mask in candidate order, skipping the centre pixel (already taken): per mask word the 32 lanes decode one
+    // candidate each and append the accepted sample indices (in order) to the list. The next 32 mask words are already
+    // on their way while a group is decoded.
     const int BP = B * P;
     const int tc0 = (bd * B + bd) * P;  // candidate numbers of the centre pixel: [tc0, tc0 + P)
     const int nwords = (B * BP + 31) >> 5;
-    for (int w0 = 0; w0 < nwords; w0 += KO_GROUP) {
-        const unsigned myw = (lane < KO_GROUP && w0 + lane < nwords) ? mask[w0 + lane] : 0u;
-        if (__ballot_sync(0xffffffffu, myw != 0u) == 0u) continue;
-        int cnt = 0;
-#pragma unroll
-        for (int j = 0; j < KO_GROUP; ++j) {
+    unsigned myw_next = lane < nwords ? mask[lane] : 0u;
+    for (int w0 = 0; w0 < nwords; w0 += 32) {
+        const unsigned myw = myw_next;
+        if (w0 + 32 < nwords) myw_next = w0 + 32 + lane < nwords ? mask[w0 + 32 + lane] : 0u;
+        unsigned live = __ballot_sync(0xffffffffu, myw != 0u);
+        while (live) {  // the non-empty words of the group, in order
+            const int j = __ffs(live) - 1;
+            live &= live - 1u;
             const unsigned bits = __shfl_sync(0xffffffffu, myw, j);
-            if (bits == 0u) continue;  // warp-uniform
             const int t = (w0 + j) * 32 + lane;
             const bool on = ((bits >> lane) & 1u) && !(t >= tc0 && t < tc0 + P);
             const unsigned eff = __ballot_sync(0xffffffffu, on);
@@ -258,26 +294,15 @@ __global__ void __launch_bounds__(KO_WARPS * 32) ordered_stats_kernel(const Gene
             }
             cnt += __popc(eff);
         }
-        __syncwarp();
-        if (cnt) {
-            double v[8], u[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) v[i] = fetch(gl[min(i, cnt - 1)]);
-            for (int i0 = 0; i0 < cnt; i0 += 16) {
-#pragma unroll
-                for (int i = 0; i < 8; ++i) u[i] = fetch(gl[min(i0 + 8 + i, cnt - 1)]);
-#pragma unroll
-                for (int i = 0; i < 8; ++i)
-                    if (i0 + i < cnt) take(v[i]);
-#pragma unroll
-                for (int i = 0; i < 8; ++i) v[i] = fetch(gl[min(i0 + 16 + i, cnt - 1)]);
-#pragma unroll
-                for (int i = 0; i < 8; ++i)
-                    if (i0 + 8 + i < cnt) take(u[i]);
-            }
+        if (cnt > KO_LIST - 1024) {  // another group might not fit
+            N += cnt;
+            walk(cnt);
+            cnt = 0;
         }
+    }
+    if (cnt) {
         N += cnt;
-        __syncwarp();
+        walk(cnt);
     }
 
     double *rec = p.rec + static_cast<size_t>(pl) * REC_DOUBLES;
