@@ -24,7 +24,7 @@ __global__ void __launch_bounds__(KW_THREADS, 4) blend_wide_kernel(const General
     __shared__ KWSmall ks;
     __shared__ unsigned short segidx[KW_SEG_WORDS * 32];
     const int tid = threadIdx.x;
-    const int W = p.f.W, H = p.f.H, P = p.f.P, B = p.box;
+    const int W = p.f.W, P = p.f.P, B = p.box;
     const size_t S = p.f.S;
     const int pl = strip_order(blockIdx.x, p.f.W, p.nrows);
     const int py = chunk_row(pl / W, p.row0, p.gap_at, p.gap), px = pl - (pl / W) * W;
@@ -100,9 +100,7 @@ __global__ void __launch_bounds__(KW_THREADS, 4) blend_wide_kernel(const General
                 const int nc = min(KW_THREADS, total - c0);
                 if (tid < nc) {
                     const int t = seg * (KW_SEG_WORDS * 32) + segidx[c0 + tid];
-                    uint32_t g;
-                    bool centre;
-                    candidate_sample(p.cd, t, px, py, B, P, W, H, g, centre);
+                    const uint32_t g = candidate_index(p.cd, t, px, py, B, P, W);
                     stage(g, chunk + tid * KW_ZS, true);
                 }
                 __syncthreads();

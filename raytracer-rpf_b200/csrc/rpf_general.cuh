@@ -169,16 +169,13 @@ __device__ __forceinline__ int strip_order(int w, int W, int nrows) { return str
 __device__ __forceinline__ int chunk_row(int r, int row0, int gap_at, int gap) { return row0 + r + (r >= gap_at ? gap : 0); }
 
 // candidate t -> global sample index, or false when the neighbour pixel is out of bounds (rpf.cpp:569)
-__device__ __forceinline__ bool candidate_sample(const CandDecode &cd, int t, int px, int py, int B, int P, int W, int H, uint32_t &g,
-                                                 bool &centre) {
+// Sample index of ACCEPTED candidate t of pixel (px, py). Mask bits are only ever set for candidates inside the image
+// (membership_kernel), so there is no bound test; sample indices fit 32 bits (rpf_create checks S).
+__device__ __forceinline__ uint32_t candidate_index(const CandDecode &cd, int t, int px, int py, int B, int P, int W) {
     const int bd = (B - 1) / 2;
     int bx, by, s;
     cand_split(cd, t, bx, by, s);
-    const int xn = px - bd + bx, yn = py - bd + by;
-    centre = (xn == px) && (yn == py);
-    if (xn < 0 || xn >= W || yn < 0 || yn >= H) return false;
-    g = static_cast<uint32_t>((static_cast<size_t>(yn) * W + xn) * P + s);
-    return true;
+    return static_cast<uint32_t>((py - bd + by) * W + (px - bd + bx)) * static_cast<uint32_t>(P) + static_cast<uint32_t>(s);
 }
 
 // =====================================================================================================
@@ -535,7 +532,7 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ KBSmall ks;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int W = p.f.W, H = p.f.H, P = p.f.P, B = p.box;
+    const int W = p.f.W, P = p.f.P, B = p.box;
     const GeneralPlan &L = p.pl;
     unsigned long long *gsm = reinterpret_cast<unsigned long long *>(smem + L.off_gsm);
     unsigned *marg = reinterpret_cast<unsigned *>(smem + L.off_marg);  // [19][nbs]
@@ -616,9 +613,7 @@ __global__ void __launch_bounds__(NT, NT == 1024 ? 1 : 2) dependency_kernel(cons
             for (unsigned m = tid; m < uN; m += NT) {
                 const unsigned slot = (m * Q) % uN;
                 const int t = L.idx_global ? static_cast<int>(idx32[slot]) : idx16[slot];
-                uint32_t g;
-                bool centre;
-                candidate_sample(p.cd, t, px, py, B, P, W, H, g, centre);
+                const uint32_t g = candidate_index(p.cd, t, px, py, B, P, W);
                 const Rec16 r16 = load_rec16(p.rec16, g);
                 const double4 cc = load_col4(p.col4, g);
                 auto put = [&](int c, double x) {
@@ -740,7 +735,7 @@ __global__ void __launch_bounds__(KC_THREADS, 4) blend_kernel(const GeneralParam
     __shared__ KCSmall ks;
     __shared__ unsigned short segidx[KC_SEG_WORDS * 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int W = p.f.W, H = p.f.H, P = p.f.P, B = p.box;
+    const int W = p.f.W, P = p.f.P, B = p.box;
     const size_t S = p.f.S;
     const int pl = strip_order(blockIdx.x, W, p.nrows);
     const int py = chunk_row(pl / W, p.row0, p.gap_at, p.gap), px = pl - (pl / W) * W;
@@ -793,6 +788,7 @@ __global__ void __launch_bounds__(KC_THREADS, 4) blend_kernel(const GeneralParam
         double sw[KC_IC], swc[KC_IC][NC];
 #pragma unroll
         for (int ii = 0; ii < KC_IC; ++ii) { sw[ii] = 0.0; swc[ii][0] = swc[ii][1] = swc[ii][2] = 0.0; }
+        const bool full_round = P - i0 >= KC_IC;
         for (int seg = 0; seg < nseg; ++seg) {
             unsigned wbits[KC_WPT];
             int cnt = 0;
@@ -816,9 +812,7 @@ __global__ void __launch_bounds__(KC_THREADS, 4) blend_kernel(const GeneralParam
             __syncthreads();
             for (int n = tid; n < total; n += KC_THREADS) {
                 const int t = seg * (KC_SEG_WORDS * 32) + segidx[n];
-                uint32_t g;
-                bool centre;
-                candidate_sample(p.cd, t, px, py, B, P, W, H, g, centre);
+                const uint32_t g = candidate_index(p.cd, t, px, py, B, P, W);
                 // colour terms first, for all own samples of this round: at the reference's sigma most neighbours are cut
                 // by every own sample, and then the other 14 channels are never scaled (they are two thirds of the work)
                 const double4 cc = load_col4(p.col4, g);
@@ -827,9 +821,9 @@ __global__ void __launch_bounds__(KC_THREADS, 4) blend_kernel(const GeneralParam
 #pragma unroll
                 for (int k = 0; k < 3; ++k) zj[k] = scaled(cj[k], ks.mz[k], ks.scl[k]);
                 unsigned pass = 0u;
+                if (full_round) {  // the usual case (spp a multiple of KC_IC): no bound test per own sample
 #pragma unroll
-                for (int ii = 0; ii < KC_IC; ++ii) {
-                    if (i0 + ii < P) {
+                    for (int ii = 0; ii < KC_IC; ++ii) {
                         const double *zr = zi + (i0 + ii) * ZS;
                         double arg = 0.0;
 #pragma unroll
@@ -838,6 +832,20 @@ __global__ void __launch_bounds__(KC_THREADS, 4) blend_kernel(const GeneralParam
                             arg = fma(d, d, arg);
                         }
                         if (!(arg > 745.2)) pass |= 1u << ii;  // NaN passes on to exp
+                    }
+                } else {
+#pragma unroll
+                    for (int ii = 0; ii < KC_IC; ++ii) {
+                        if (i0 + ii < P) {
+                            const double *zr = zi + (i0 + ii) * ZS;
+                            double arg = 0.0;
+#pragma unroll
+                            for (int k = 0; k < 3; ++k) {
+                                const double d = zr[k] - zj[k];
+                                arg = fma(d, d, arg);
+                            }
+                            if (!(arg > 745.2)) pass |= 1u << ii;
+                        }
                     }
                 }
                 // A neighbour whose raw colour is Inf or NaN poisons every own sample it is blended into even with weight 0

@@ -89,7 +89,7 @@ __global__ void __launch_bounds__(KL_THREADS, 1) dependency_large_kernel(const G
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ KBSmall ks;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int W = p.f.W, H = p.f.H, P = p.f.P, B = p.box;
+    const int W = p.f.W, P = p.f.P, B = p.box;
     const GeneralPlan &L = p.pl;
     unsigned long long *gsm = reinterpret_cast<unsigned long long *>(smem + L.off_gsm);
     unsigned *marg = reinterpret_cast<unsigned *>(smem + L.off_marg);  // [19][nbs]
@@ -144,9 +144,7 @@ __global__ void __launch_bounds__(KL_THREADS, 1) dependency_large_kernel(const G
             const unsigned long long Q = static_cast<unsigned long long>(ks.Q), uN = static_cast<unsigned long long>(N);
             for (unsigned m = tid; m < static_cast<unsigned>(N); m += KL_THREADS) {
                 const int t = static_cast<int>(sc.idx[(m * Q) % uN]);
-                uint32_t g;
-                bool centre;
-                candidate_sample(p.cd, t, px, py, B, P, W, H, g, centre);
+                const uint32_t g = candidate_index(p.cd, t, px, py, B, P, W);
                 const Rec16 r16 = load_rec16(p.rec16, g);
                 const double4 cc = load_col4(p.col4, g);
                 auto put = [&](int c, double x) {

@@ -286,12 +286,7 @@ __global__ void __launch_bounds__(KO_WARPS * 32) ordered_stats_kernel(const Gene
             const int t = (w0 + j) * 32 + lane;
             const bool on = ((bits >> lane) & 1u) && !(t >= tc0 && t < tc0 + P);
             const unsigned eff = __ballot_sync(0xffffffffu, on);
-            if (on) {
-                int bx, by, s;
-                cand_split(p.cd, t, bx, by, s);
-                gl[cnt + __popc(eff & ((1u << lane) - 1u))] =
-                    static_cast<uint32_t>((static_cast<size_t>(py - bd + by) * W + (px - bd + bx)) * P + s);
-            }
+            if (on) gl[cnt + __popc(eff & ((1u << lane) - 1u))] = candidate_index(p.cd, t, px, py, B, P, W);
             cnt += __popc(eff);
         }
         if (cnt > KO_LIST - 1024) {  // another group might not fit
