@@ -354,6 +354,11 @@ __device__ __forceinline__ void unit_lookup(int u, int G, int &a, int &t0, int &
 }
 
 
+// fire-and-forget add on a 32-bit shared-memory address
+__device__ __forceinline__ void smem_red_add(unsigned addr, unsigned v) {
+    asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+
 __device__ __forceinline__ void team_sync(int team, int nthreads) {
     if (nthreads == 32) __syncwarp();
     else asm volatile("bar.sync %0, %1;" ::"r"(team + 1), "r"(nthreads) : "memory");
@@ -390,6 +395,7 @@ __device__ __forceinline__ void joint_phase(const GeneralParams &p, KBSmall &ks,
         const int ge = FULL_UNITS ? G : g;
         if (ks.flat[a]) continue;  // a constant channel has MI exactly 0 with everything; Sab stays unused
         unsigned *th = region + (team * sets + set) * G * hwn;
+        const unsigned th_s = static_cast<unsigned>(__cvta_generic_to_shared(th)), nb4 = 4u * nb;
         const uint32_t *ba = bins + a * nq;
         const uint32_t *bb[G];
 #pragma unroll
@@ -416,13 +422,24 @@ __device__ __forceinline__ void joint_phase(const GeneralParams &p, KBSmall &ks,
             }
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-                const unsigned ca = ((wa >> (8 * k)) & 255u) * nb;
+                // byte k of a packed word in one PRMT; an update is then PRMT + LEA (row + 4 * bin) + ATOMS
+                const unsigned ca = __byte_perm(wa, 0u, 0x4440u + k) * nb;
+                if (PAIRED) {
 #pragma unroll
-                for (int j = 0; j < G; ++j) {
-                    if (j < ge) {
-                        const unsigned cell = ca + ((wb[j] >> (8 * k)) & 255u);
-                        if (PAIRED) atomicAdd(&th[(j >> 1) * pw + cell], (j & 1) ? 0x10000u : 1u);
-                        else atomicAdd(&th[j * hwn + (cell >> 1)], 1u << ((cell & 1u) << 4));
+                    for (int jp = 0; jp < G / 2; ++jp) {
+                        // 32-bit shared address of the row of the pair's table, one IMAD per (sample, pair)
+                        unsigned row = __byte_perm(wa, 0u, 0x4440u + k) * nb4 + (th_s + jp * pw * 4);
+                        asm volatile("" : "+r"(row));  // keep it: the compiler would otherwise refold (nb * a + b) * 4 + base per update
+                        if (2 * jp < ge) smem_red_add(row + 4u * __byte_perm(wb[2 * jp], 0u, 0x4440u + k), 1u);
+                        if (2 * jp + 1 < ge) smem_red_add(row + 4u * __byte_perm(wb[2 * jp + 1], 0u, 0x4440u + k), 0x10000u);
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < G; ++j) {
+                        if (j < ge) {
+                            const unsigned cell = ca + ((wb[j] >> (8 * k)) & 255u);
+                            atomicAdd(&th[j * hwn + (cell >> 1)], 1u << ((cell & 1u) << 4));
+                        }
                     }
                 }
             }
