@@ -486,8 +486,10 @@ __device__ __forceinline__ void joint_phase(const GeneralParams &p, KBSmall &ks,
 #pragma unroll
                         for (int e = 0; e < 4; ++e) {
                             const unsigned c0 = wv[e] & 0xffffu, c1 = wv[e] >> 16;
-                            if (c0 > 1u) acc0 += hsm[c0];
-                            if (c1 > 1u) acc1 += hsm[c1];
+                            // unconditional: hsm[0] = hsm[1] = 0, and the lanes' addresses are a handful of small ones either
+                            // way (one wavefront); the test per cell cost more than it saved (profiles/r2/ab_v44_sweep_uncond.txt)
+                            acc0 += hsm[c0];
+                            acc1 += hsm[c1];
                         }
                     } else {
                         for (int e = 0; e < 4; ++e) {
@@ -794,7 +796,10 @@ struct KCSmall {
     int wsum[KC_THREADS / 32 + 1];
 };
 
-__global__ void __launch_bounds__(KC_THREADS, 4) blend_kernel(const GeneralParams p) {
+#ifndef RPF_KC_MINB
+#define RPF_KC_MINB 4  // CTAs per SM the register allocation aims at (128 registers)
+#endif
+__global__ void __launch_bounds__(KC_THREADS, RPF_KC_MINB) blend_kernel(const GeneralParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ KCSmall ks;
     __shared__ unsigned short segidx[KC_SEG_WORDS * 32];
